@@ -1,0 +1,91 @@
+"""Thin Python wrappers over the stateless C-ABI kernels.  torch tensors are used purely as
+device-memory containers (`data_ptr()`), never for compute."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+
+def _stream_ptr(stream=None):
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _farr(vals, n):
+    return (C.c_float * n)(*[float(v) for v in vals][:n])
+
+
+def preprocess(src_u8: torch.Tensor, mean, std, layout: str = "nchw", out_channels: int | None = None,
+               resize: tuple[int, int] | None = None, crop: tuple[int, int] | None = None,
+               stream=None) -> torch.Tensor:
+    """uint8 [B,H,W,C] cuda tensor -> bf16 NCHW [B,C,h,w] or NHWC [B,h,w,out_channels]."""
+    lib = L.load()
+    assert src_u8.is_cuda and src_u8.dtype == torch.uint8 and src_u8.dim() == 4
+    b, h, w, c = src_u8.shape
+    assert src_u8.stride(3) == 1 and src_u8.stride(2) == c, "pixels must be dense HWC"
+    rh, rw = resize if resize else (0, 0)
+    full_h, full_w = (rh, rw) if resize else (h, w)
+    oh, ow = crop if crop else (full_h, full_w)
+    if layout == "nchw":
+        oc = c
+        out = torch.empty((b, c, oh, ow), dtype=torch.bfloat16, device=src_u8.device)
+        lay = L.LAYOUT_NCHW
+    else:
+        oc = out_channels or 4
+        out = torch.empty((b, oh, ow, oc), dtype=torch.bfloat16, device=src_u8.device)
+        lay = L.LAYOUT_NHWC
+    L.check(lib.ai4e_preprocess(_ptr(src_u8), b, h, w, c, src_u8.stride(0), src_u8.stride(1), rh, rw, oh, ow,
+                                _farr(mean, c), _farr(std, c), lay, oc, _ptr(out), _stream_ptr(stream)))
+    return out
+
+
+def conv_layer(x_nhwc: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tensor, stride: int, pad: int,
+               residual: torch.Tensor | None = None, relu: bool = True, algo: int = L.CONV_AUTO,
+               stream=None) -> torch.Tensor:
+    """x [B,H,W,Cin] bf16, weight [Cout,kh,kw,Cin] bf16, bias [Cout] fp32 -> [B,P,Q,Cout] bf16."""
+    lib = L.load()
+    assert x_nhwc.is_contiguous() and weight_krsc.is_contiguous() and bias.is_contiguous()
+    assert x_nhwc.dtype == torch.bfloat16 and weight_krsc.dtype == torch.bfloat16 and bias.dtype == torch.float32
+    b, h, w, cin = x_nhwc.shape
+    cout, kh, kw, cin2 = weight_krsc.shape
+    assert cin == cin2
+    p = (h + 2 * pad - kh) // stride + 1
+    q = (w + 2 * pad - kw) // stride + 1
+    out = torch.empty((b, p, q, cout), dtype=torch.bfloat16, device=x_nhwc.device)
+    if residual is not None:
+        assert residual.is_contiguous() and residual.shape == out.shape and residual.dtype == torch.bfloat16
+    L.check(lib.ai4e_conv_layer(_ptr(x_nhwc), b, h, w, cin, _ptr(weight_krsc), _ptr(bias), cout, kh, kw, stride,
+                                pad, _ptr(residual), int(relu), _ptr(out), algo, _stream_ptr(stream)))
+    return out
+
+
+def maxpool(x_nhwc: torch.Tensor, k: int = 3, stride: int = 2, pad: int = 1, stream=None) -> torch.Tensor:
+    lib = L.load()
+    assert x_nhwc.is_contiguous() and x_nhwc.dtype == torch.bfloat16
+    b, h, w, c = x_nhwc.shape
+    p = (h + 2 * pad - k) // stride + 1
+    q = (w + 2 * pad - k) // stride + 1
+    out = torch.empty((b, p, q, c), dtype=torch.bfloat16, device=x_nhwc.device)
+    L.check(lib.ai4e_maxpool(_ptr(x_nhwc), b, h, w, c, k, stride, pad, _ptr(out), _stream_ptr(stream)))
+    return out
+
+
+def head(x_nhwc: torch.Tensor, fc_w: torch.Tensor, fc_b: torch.Tensor, topk: int = L.TOPK, stream=None):
+    """x [B,H,W,C] bf16, fc_w [classes,C] bf16, fc_b fp32 -> (logits fp32, top_idx i32, top_prob fp32)."""
+    lib = L.load()
+    assert x_nhwc.is_contiguous() and fc_w.is_contiguous() and fc_b.is_contiguous()
+    b, h, w, c = x_nhwc.shape
+    classes = fc_w.shape[0]
+    logits = torch.empty((b, classes), dtype=torch.float32, device=x_nhwc.device)
+    idx = torch.empty((b, max(topk, 1)), dtype=torch.int32, device=x_nhwc.device)
+    prob = torch.empty((b, max(topk, 1)), dtype=torch.float32, device=x_nhwc.device)
+    L.check(lib.ai4e_head(_ptr(x_nhwc), b, h * w, c, _ptr(fc_w), _ptr(fc_b), classes, _ptr(logits), _ptr(idx),
+                          _ptr(prob), topk, _stream_ptr(stream)))
+    return logits, idx[:, :topk], prob[:, :topk]

@@ -1,0 +1,77 @@
+// extern "C" stateless entry points of include/ai4e_b200.h (the parity-test boundary).
+#include "../../include/ai4e_b200.h"
+
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace ai4e;
+
+extern "C" {
+
+int ai4e_version(void) { return 100; }  // 0.1.0
+
+const char* ai4e_last_error(void) { return get_last_error(); }
+
+int ai4e_device_count(int* out_count) {
+  AI4E_REQUIRE(out_count, "device_count: null pointer");
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    *out_count = 0;
+    set_last_error("cudaGetDeviceCount failed: %s", cudaGetErrorString(e));
+    return AI4E_ERR_CUDA;
+  }
+  *out_count = n;
+  return AI4E_OK;
+}
+
+int ai4e_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
+                    int64_t src_image_stride, int src_row_stride, int resize_h, int resize_w,
+                    int out_h, int out_w, const float* h_mean, const float* h_std, int layout,
+                    int out_channels, void* d_dst_bf16, void* stream) {
+  const int rc = launch_preprocess(d_src, batch, src_h, src_w, channels, src_image_stride,
+                                   src_row_stride, resize_h, resize_w, out_h, out_w, h_mean, h_std,
+                                   layout, out_channels, d_dst_bf16, (cudaStream_t)stream);
+  return rc < 0 ? rc : AI4E_OK;
+}
+
+int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
+                    const void* d_weight_krsc, const float* d_bias, int cout, int kh, int kw,
+                    int stride, int pad, const void* d_residual_or_null, int relu,
+                    void* d_out_nhwc, int algo, void* stream) {
+  AI4E_REQUIRE(d_in_nhwc && d_weight_krsc && d_bias && d_out_nhwc, "conv: null pointer");
+  AI4E_REQUIRE(batch > 0 && h > 0 && w > 0 && cin > 0 && cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0,
+               "conv: bad geometry");
+  AI4E_REQUIRE(h + 2 * pad >= kh && w + 2 * pad >= kw, "conv: filter larger than padded input");
+  AI4E_REQUIRE(algo == AI4E_CONV_AUTO || algo == AI4E_CONV_IGEMM || algo == AI4E_CONV_DIRECT,
+               "conv: unknown algo %d", algo);
+  const bool can = igemm_supported(cin, cout, kh, kw, stride, pad) != 0;
+  if (algo == AI4E_CONV_DIRECT || (algo == AI4E_CONV_AUTO && !can))
+    return launch_conv_direct(d_in_nhwc, batch, h, w, cin, d_weight_krsc, d_bias, cout, kh, kw, stride,
+                              pad, d_residual_or_null, relu, d_out_nhwc, (cudaStream_t)stream);
+  IgemmPlan plan;
+  int rc = igemm_make_plan(&plan, d_in_nhwc, batch, h, w, cin, d_weight_krsc, d_bias, cout, kh, kw,
+                           stride, pad, d_residual_or_null, relu, d_out_nhwc, 0);
+  if (rc) return rc;
+  return igemm_launch(plan, (cudaStream_t)stream);
+}
+
+int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
+                 void* d_out_nhwc, void* stream) {
+  return launch_maxpool(d_in_nhwc, batch, h, w, c, k, stride, pad, d_out_nhwc, (cudaStream_t)stream);
+}
+
+int ai4e_head(const void* d_in_nhwc, int batch, int hw, int c, const void* d_fc_w,
+              const float* d_fc_b, int classes, float* d_logits, int32_t* d_top_idx,
+              float* d_top_prob, int topk, void* stream) {
+  AI4E_REQUIRE(batch > 0 && c > 0, "head: bad geometry");
+  float* scratch = nullptr;
+  cudaStream_t s = (cudaStream_t)stream;
+  AI4E_CUDA_TRY(cudaMallocAsync(&scratch, (size_t)batch * c * sizeof(float), s));
+  const int rc = launch_head(d_in_nhwc, batch, hw, c, d_fc_w, d_fc_b, classes, scratch, d_logits,
+                             d_top_idx, d_top_prob, topk, s);
+  cudaFreeAsync(scratch, s);
+  return rc;
+}
+
+}  // extern "C"

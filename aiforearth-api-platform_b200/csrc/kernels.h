@@ -1,0 +1,58 @@
+// Host-side launch interface of the kernels in this directory (internal to the library;
+// the public boundary is include/ai4e_b200.h).
+#pragma once
+
+#include "common.cuh"
+
+namespace ai4e {
+
+int sm_count();
+
+// ---- K1 preprocess (preprocess.cu); returns 1 if the streaming LUT kernel ran, 0 generic
+int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
+                      long long src_image_stride, int src_row_stride, int resize_h, int resize_w,
+                      int out_h, int out_w, const float* mean, const float* stdv, int layout,
+                      int out_channels, void* d_dst, cudaStream_t stream);
+
+// ---- direct convolution on CUDA cores (conv_direct.cu)
+int launch_conv_direct(const void* in, int N, int H, int W, int Cin, const void* weight,
+                       const float* bias, int Cout, int R, int S, int stride, int pad,
+                       const void* residual, int relu, void* out, cudaStream_t stream);
+
+// ---- K4 tcgen05 implicit-GEMM convolution (conv_igemm.cu)
+struct IgemmParams {
+  int M, P, Q, PQ;
+  int Cout;
+  int S;           // filter width (taps per filter row)
+  int stride, pad;
+  int cin_blocks;  // Cin / 64
+  int num_k_blocks;
+  int tiles_m, tiles_n, num_tiles;
+  int relu;
+  const float* bias;
+  const bf16* residual;
+  bf16* out;
+};
+
+struct IgemmPlan {
+  CUtensorMap tmap_a, tmap_b;
+  IgemmParams prm;
+  int block_n;
+  int grid;
+};
+
+int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
+int igemm_pick_block_n(int Cout, long long M);
+int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
+                    const void* weight, const float* bias, int Cout, int R, int S, int stride,
+                    int pad, const void* residual, int relu, void* out, int force_block_n);
+int igemm_launch(const IgemmPlan& plan, cudaStream_t stream);
+
+// ---- K3 / K5 (pool_head.cu)
+int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,
+                   cudaStream_t stream);
+int launch_head(const void* in, int N, int HW, int C, const void* fc_w, const float* fc_b,
+                int classes, float* pooled_scratch, float* logits, int32_t* top_idx, float* top_prob,
+                int topk, cudaStream_t stream);
+
+}  // namespace ai4e

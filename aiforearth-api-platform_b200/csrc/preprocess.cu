@@ -1,0 +1,283 @@
+// K1 — preprocessing: uint8 HWC -> normalised bf16 (NCHW planes, or NHWC with the channel
+// count padded for the stem), optional bilinear resize + centre crop fused in.
+//
+// Replaces what a PyTorch CPU container does inside the user callback the reference calls at
+// APIs/1.0/base-py/ai4e_service.py:203 (ToTensor -> Normalize, optionally Resize ->
+// CenterCrop first); restated on the CPU in oracle/preprocess_oracle.py.
+//
+// Two kernels:
+//   * preprocess_lut_kernel     no resize, dense rows, H*W % 16 == 0.  HBM-bound streaming
+//     kernel: each CTA stages 4096-pixel chunks of the interleaved source into shared memory
+//     with 1-D bulk async copies (TMA engine, mbarrier completion, two stages in flight),
+//     every thread converts 16 pixels through a 256-entry-per-channel bf16 look-up table
+//     held in shared memory and writes 16-byte vectors.  The table is built in the prologue
+//     with IEEE-exact, separately rounded fp32 operations ((v/255 - mean)/std), so the
+//     output is bit-identical to the oracle by construction: a byte has only 256 values.
+//   * preprocess_generic_kernel everything else (resize/crop, row strides, ragged sizes):
+//     one thread per output pixel, same fp32 operation order as the oracle, no FMA
+//     contraction.
+#include "common.cuh"
+
+namespace ai4e {
+
+struct PreprocParams {
+  const uint8_t* src;
+  uint16_t* dst;  // bf16 bits
+  int batch, src_h, src_w, channels;
+  long long src_image_stride;  // bytes
+  int src_row_stride;          // bytes
+  int resize_h, resize_w;      // 0 => no resize
+  int crop_top, crop_left;     // offsets into the (resized) image
+  int out_h, out_w;
+  int layout;        // 0 = NCHW, 1 = NHWC
+  int out_channels;  // NHWC: padded channel count (>= channels); NCHW: == channels
+  float mean[4], stdv[4];
+};
+
+constexpr int kPixPerThread = 16;
+constexpr int kLutThreads = 256;
+constexpr int kChunkPix = kPixPerThread * kLutThreads;  // 4096
+
+__device__ __forceinline__ uint16_t norm_to_bf16(float v, float mean, float stdv) {
+  // three separately rounded IEEE operations, exactly as the oracle
+  float x = __fdiv_rn(v, 255.0f);
+  x = __fsub_rn(x, mean);
+  x = __fdiv_rn(x, stdv);
+  return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
+
+template <int C>
+__global__ void __launch_bounds__(kLutThreads)
+preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chunks) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  // layout: [2 stages][kChunkPix*C bytes] | lut[C][256] u16 | 2 mbarriers
+  uint8_t* stage_buf = smem_raw;
+  uint16_t* lut = reinterpret_cast<uint16_t*>(smem_raw + 2 * kChunkPix * C);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * kChunkPix * C + C * 256 * 2);
+
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int c = 0; c < C; ++c) lut[c * 256 + tid] = norm_to_bf16((float)tid, p.mean[c], p.stdv[c]);
+  if (tid == 0) {
+    mbar_init(smem_u32(&bars[0]), 1);
+    mbar_init(smem_u32(&bars[1]), 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  const int hw = p.out_h * p.out_w;
+  auto issue = [&](int chunk, int stage) {
+    const int img = chunk / chunks_per_image;
+    const int cj = chunk - img * chunks_per_image;
+    const int px0 = cj * kChunkPix;
+    const int npx = min(kChunkPix, hw - px0);
+    const uint32_t bytes = (uint32_t)npx * C;
+    const uint8_t* g = p.src + (long long)img * p.src_image_stride + (long long)px0 * C;
+    const uint32_t bar = smem_u32(&bars[stage]);
+    mbar_expect_tx(bar, bytes);
+    bulk_load_1d(smem_u32(stage_buf + stage * kChunkPix * C), g, bytes, bar);
+  };
+
+  int chunk = blockIdx.x;
+  if (tid == 0 && chunk < total_chunks) issue(chunk, 0);
+  uint32_t it = 0;
+  for (; chunk < total_chunks; chunk += gridDim.x, ++it) {
+    const int stage = it & 1;
+    const int next = chunk + gridDim.x;
+    if (tid == 0 && next < total_chunks) issue(next, stage ^ 1);
+    mbar_wait(smem_u32(&bars[stage]), (it >> 1) & 1);
+
+    const int img = chunk / chunks_per_image;
+    const int cj = chunk - img * chunks_per_image;
+    const int px = cj * kChunkPix + tid * kPixPerThread;
+    if (px < hw) {
+      // 16 pixels of C interleaved bytes = C 16-byte vectors; stride 16*C bytes between
+      // lanes is bank-conflict free for C = 3 and C = 4
+      const uint4* s4 = reinterpret_cast<const uint4*>(stage_buf + stage * kChunkPix * C +
+                                                       tid * kPixPerThread * C);
+      uint32_t w[4 * C];
+#pragma unroll
+      for (int i = 0; i < C; ++i) {
+        uint4 v = s4[i];
+        w[4 * i + 0] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+      }
+      auto byte_at = [&](int k) -> uint32_t { return (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu; };
+      if (p.layout == 0) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+          uint32_t o[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t lo = lut[c * 256 + byte_at((2 * j) * C + c)];
+            const uint32_t hi = lut[c * 256 + byte_at((2 * j + 1) * C + c)];
+            o[j] = lo | (hi << 16);
+          }
+          uint4* d = reinterpret_cast<uint4*>(p.dst + ((long long)(img * C + c) * hw + px));
+          d[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          d[1] = make_uint4(o[4], o[5], o[6], o[7]);
+        }
+      } else {
+        // NHWC with channel padding to 4 (C == 3: pad lane is +0.0; C == 4: all real)
+        uint4* d = reinterpret_cast<uint4*>(p.dst + ((long long)img * hw + px) * 4);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {  // two pixels per 16-byte store
+          uint32_t o[4];
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            const int pix = 2 * j + q;
+            const uint32_t c0 = lut[0 * 256 + byte_at(pix * C + 0)];
+            const uint32_t c1 = lut[1 * 256 + byte_at(pix * C + 1)];
+            const uint32_t c2 = lut[2 * 256 + byte_at(pix * C + 2)];
+            const uint32_t c3 = (C == 4) ? lut[3 * 256 + byte_at(pix * C + (C - 1))] : 0u;
+            o[2 * q] = c0 | (c1 << 16);
+            o[2 * q + 1] = c2 | (c3 << 16);
+          }
+          d[j] = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+      }
+    }
+    __syncthreads();  // stage buffer is free for the copy issued next iteration
+  }
+}
+
+__device__ __forceinline__ void bilinear_axis(int dst, int in_size, int out_size, int& i0, int& i1,
+                                              float& l0, float& l1) {
+  const float scale = __fdiv_rn((float)in_size, (float)out_size);
+  float src = __fsub_rn(__fmul_rn(__fadd_rn((float)dst, 0.5f), scale), 0.5f);
+  src = fmaxf(src, 0.0f);
+  i0 = min((int)floorf(src), in_size - 1);
+  i1 = min(i0 + 1, in_size - 1);
+  l1 = __fsub_rn(src, (float)i0);
+  l0 = __fsub_rn(1.0f, l1);
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_generic_kernel(const PreprocParams p) {
+  const long long total = (long long)p.batch * p.out_h * p.out_w;
+  for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(idx % p.out_w);
+    const int y = (int)((idx / p.out_w) % p.out_h);
+    const int n = (int)(idx / ((long long)p.out_w * p.out_h));
+    const uint8_t* img = p.src + (long long)n * p.src_image_stride;
+    const int C = p.channels;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (p.resize_h > 0) {
+      int y0, y1, x0, x1;
+      float ly0, ly1, lx0, lx1;
+      bilinear_axis(y + p.crop_top, p.src_h, p.resize_h, y0, y1, ly0, ly1);
+      bilinear_axis(x + p.crop_left, p.src_w, p.resize_w, x0, x1, lx0, lx1);
+      const uint8_t* r0 = img + (long long)y0 * p.src_row_stride;
+      const uint8_t* r1 = img + (long long)y1 * p.src_row_stride;
+      for (int c = 0; c < C; ++c) {
+        const float p00 = r0[x0 * C + c], p01 = r0[x1 * C + c];
+        const float p10 = r1[x0 * C + c], p11 = r1[x1 * C + c];
+        const float top = __fadd_rn(__fmul_rn(lx0, p00), __fmul_rn(lx1, p01));
+        const float bot = __fadd_rn(__fmul_rn(lx0, p10), __fmul_rn(lx1, p11));
+        v[c] = __fadd_rn(__fmul_rn(ly0, top), __fmul_rn(ly1, bot));
+      }
+    } else {
+      const uint8_t* px = img + (long long)(y + p.crop_top) * p.src_row_stride +
+                          (long long)(x + p.crop_left) * C;
+      for (int c = 0; c < C; ++c) v[c] = (float)px[c];
+    }
+    if (p.layout == 0) {
+      const long long plane = (long long)p.out_h * p.out_w;
+      for (int c = 0; c < C; ++c)
+        p.dst[((long long)n * C + c) * plane + (long long)y * p.out_w + x] =
+            norm_to_bf16(v[c], p.mean[c], p.stdv[c]);
+    } else {
+      uint16_t* d = p.dst + idx * p.out_channels;
+      for (int c = 0; c < p.out_channels; ++c)
+        d[c] = (c < C) ? norm_to_bf16(v[c], p.mean[c], p.stdv[c]) : (uint16_t)0;
+    }
+  }
+}
+
+static int g_sm_count = 0;
+int sm_count() {
+  if (g_sm_count == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
+    if (g_sm_count <= 0) g_sm_count = 148;
+  }
+  return g_sm_count;
+}
+
+// returns 1 if the streaming (LUT) kernel was used, 0 for the generic kernel, <0 on error
+int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
+                      long long src_image_stride, int src_row_stride, int resize_h, int resize_w,
+                      int out_h, int out_w, const float* mean, const float* stdv, int layout,
+                      int out_channels, void* d_dst, cudaStream_t stream) {
+  AI4E_REQUIRE(d_src && d_dst && mean && stdv, "preprocess: null pointer");
+  AI4E_REQUIRE(batch > 0 && src_h > 0 && src_w > 0, "preprocess: empty input (%d x %d x %d)", batch,
+               src_h, src_w);
+  AI4E_REQUIRE(channels == 3 || channels == 4, "preprocess: channels must be 3 or 4, got %d",
+               channels);
+  AI4E_REQUIRE(layout == 0 || layout == 1, "preprocess: layout must be 0 (NCHW) or 1 (NHWC)");
+  if (layout == 0) AI4E_REQUIRE(out_channels == channels, "preprocess: NCHW keeps the channel count");
+  if (layout == 1)
+    AI4E_REQUIRE(out_channels >= channels && out_channels <= 8,
+                 "preprocess: NHWC out_channels %d outside [%d, 8]", out_channels, channels);
+  const bool resize = resize_h > 0 || resize_w > 0;
+  if (resize) AI4E_REQUIRE(resize_h > 0 && resize_w > 0, "preprocess: resize needs both sizes");
+  const int full_h = resize ? resize_h : src_h, full_w = resize ? resize_w : src_w;
+  AI4E_REQUIRE(out_h > 0 && out_w > 0 && out_h <= full_h && out_w <= full_w,
+               "preprocess: crop %dx%d does not fit %dx%d", out_h, out_w, full_h, full_w);
+  if (src_row_stride <= 0) src_row_stride = src_w * channels;
+  if (src_image_stride <= 0) src_image_stride = (long long)src_row_stride * src_h;
+  AI4E_REQUIRE(src_row_stride >= src_w * channels, "preprocess: row stride too small");
+  for (int c = 0; c < channels; ++c)
+    AI4E_REQUIRE(stdv[c] != 0.0f, "preprocess: std[%d] is zero", c);
+
+  PreprocParams p{};
+  p.src = d_src; p.dst = reinterpret_cast<uint16_t*>(d_dst);
+  p.batch = batch; p.src_h = src_h; p.src_w = src_w; p.channels = channels;
+  p.src_image_stride = src_image_stride; p.src_row_stride = src_row_stride;
+  p.resize_h = resize ? resize_h : 0; p.resize_w = resize ? resize_w : 0;
+  // torchvision CenterCrop: int(round((size - crop) / 2.0)), Python round-half-to-even
+  auto centre = [](int full, int crop) {
+    const int d = full - crop;
+    int h = d / 2;
+    if ((d & 1) && (h & 1)) h += 1;  // d/2 = h + 0.5 rounds to the even neighbour
+    return h;
+  };
+  p.crop_top = centre(full_h, out_h); p.crop_left = centre(full_w, out_w);
+  p.out_h = out_h; p.out_w = out_w; p.layout = layout; p.out_channels = out_channels;
+  for (int c = 0; c < 4; ++c) { p.mean[c] = c < channels ? mean[c] : 0.f; p.stdv[c] = c < channels ? stdv[c] : 1.f; }
+
+  const long long hw = (long long)out_h * out_w;
+  const bool dense = !resize && out_h == src_h && out_w == src_w &&
+                     src_row_stride == src_w * channels;
+  const bool fast = dense && (hw % kPixPerThread == 0) && (src_image_stride % 16 == 0) &&
+                    ((reinterpret_cast<uintptr_t>(d_src) & 15) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(d_dst) & 15) == 0) &&
+                    (layout == 0 || out_channels == 4);
+  if (fast) {
+    const int chunks_per_image = (int)((hw + kChunkPix - 1) / kChunkPix);
+    const long long total_chunks = (long long)chunks_per_image * batch;
+    AI4E_REQUIRE(total_chunks < (1ll << 31), "preprocess: batch too large");
+    const size_t smem = 2 * (size_t)kChunkPix * channels + (size_t)channels * 256 * 2 + 16;
+    const int ctas_per_sm = 4;
+    const int grid = (int)std::min<long long>(total_chunks, (long long)sm_count() * ctas_per_sm);
+    if (channels == 3) {
+      static bool attr3 = false;
+      if (!attr3) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr3 = true; }
+      preprocess_lut_kernel<3><<<grid, kLutThreads, smem, stream>>>(p, chunks_per_image, (int)total_chunks);
+    } else {
+      static bool attr4 = false;
+      if (!attr4) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr4 = true; }
+      preprocess_lut_kernel<4><<<grid, kLutThreads, smem, stream>>>(p, chunks_per_image, (int)total_chunks);
+    }
+    AI4E_CUDA_TRY(cudaGetLastError());
+    return 1;
+  }
+  const long long total = (long long)batch * hw;
+  const int grid = (int)std::min<long long>((total + 255) / 256, (long long)sm_count() * 8);
+  preprocess_generic_kernel<<<grid, 256, 0, stream>>>(p);
+  AI4E_CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace ai4e

@@ -1,0 +1,210 @@
+/* libai4e_b200 — C ABI of the B200-native classify engine that sits under the AI for Earth
+ * API Platform's container host shell.
+ *
+ * The reference has NO foreign-function or plugin ABI on this path: its extension point is
+ * the Python callback `r = func(*args, **kwargs)` at
+ * /root/reference/APIs/1.0/base-py/ai4e_service.py:203, invoked from the views that
+ * `APIService.api_sync_func` / `api_async_func` create (ai4e_service.py:72-109).  Everything
+ * a PyTorch CPU container does inside that callback (decode -> preprocess -> model forward
+ * -> softmax/top-5) is what this library replaces; each entry point below names the piece
+ * of that callback it stands in for.  INTEGRATION.md shows the ctypes stub a maintainer adds
+ * on the reference side.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative AI4E_ERR_* code; the message for
+ *     the calling thread is `ai4e_last_error()`;
+ *   - plain pointers and sizes only; outputs are caller-allocated; no exceptions cross;
+ *   - `d_` pointers are device memory on the current CUDA device, `h_` pointers are host
+ *     memory; `stream` is a `cudaStream_t` passed as `void*` (NULL = default stream);
+ *   - activations are NHWC bfloat16; convolution weights are [Cout][kh][kw][Cin] bfloat16
+ *     with BatchNorm already folded in, biases fp32;
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef AI4E_B200_H_
+#define AI4E_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define AI4E_API __attribute__((visibility("default")))
+#else
+#define AI4E_API
+#endif
+
+#define AI4E_OK 0
+#define AI4E_ERR_INVALID (-1)     /* bad argument / unsupported shape */
+#define AI4E_ERR_CUDA (-2)        /* a CUDA runtime or driver call failed */
+#define AI4E_ERR_UNSUPPORTED (-3) /* feature missing on this driver / device */
+#define AI4E_ERR_NOMEM (-4)
+#define AI4E_ERR_STATE (-5)       /* engine closed, unknown ticket, ... */
+#define AI4E_ERR_TIMEOUT (-6)
+
+#define AI4E_LAYOUT_NCHW 0
+#define AI4E_LAYOUT_NHWC 1
+
+#define AI4E_CONV_AUTO 0   /* tcgen05 implicit GEMM when the shape allows, else direct */
+#define AI4E_CONV_IGEMM 1  /* tcgen05 implicit GEMM, error if the shape does not allow it */
+#define AI4E_CONV_DIRECT 2 /* CUDA-core direct convolution (stem / cross-check) */
+
+#define AI4E_OP_CONV 0
+#define AI4E_OP_MAXPOOL 1
+#define AI4E_OP_HEAD 2 /* global average pool -> FC -> softmax -> top-k */
+
+#define AI4E_TOPK 5
+
+/* Library version (major*10000 + minor*100 + patch).  No reference counterpart. */
+AI4E_API int ai4e_version(void);
+
+/* Message of the last error on the calling thread.  The reference reports errors by raising
+ * inside the callback (ai4e_service.py:205-211); this is the C-ABI equivalent. */
+AI4E_API const char* ai4e_last_error(void);
+
+/* Number of CUDA devices (the reference scales by Kubernetes replicas, one GPU per pod:
+ * APIs/Charts/camera-trap/detection-async/prod-values.yaml:18). */
+AI4E_API int ai4e_device_count(int* out_count);
+
+/* ---------------------------------------------------------------------------------------
+ * Stateless kernels (device pointers).  These are the parity-test entry points.
+ * ------------------------------------------------------------------------------------- */
+
+/* K1.  uint8 HWC -> normalised bf16: [optional bilinear resize (align_corners = false, no
+ * antialias) -> centre crop ->] (x/255 - mean)/std.  Stands in for torchvision
+ * Resize/CenterCrop/ToTensor/Normalize inside the callback at ai4e_service.py:203.
+ *   d_src            batch images, `src_image_stride` bytes apart (0 = dense), rows
+ *                    `src_row_stride` bytes apart (0 = src_w*channels)
+ *   channels         3 or 4
+ *   resize_h/w       0,0 = no resize
+ *   out_h/out_w      output size = centre crop of the (resized) image
+ *   h_mean/h_std     host arrays, `channels` entries
+ *   layout           AI4E_LAYOUT_NCHW ([B][C][out_h][out_w], out_channels == channels) or
+ *                    AI4E_LAYOUT_NHWC ([B][out_h][out_w][out_channels], extra channels = 0)
+ * Bit-exact against oracle/preprocess_oracle.py. */
+AI4E_API int ai4e_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
+                    int64_t src_image_stride, int src_row_stride, int resize_h, int resize_w,
+                    int out_h, int out_w, const float* h_mean, const float* h_std, int layout,
+                    int out_channels, void* d_dst_bf16, void* stream);
+
+/* K2/K4.  One convolution layer with folded BatchNorm, optional residual add and ReLU fused:
+ *   out = act(conv(in, w) + bias [+ residual]).  Stands in for Conv2d + BatchNorm2d (+ add)
+ * (+ ReLU) of torchvision's ResNet blocks.  `algo` is one of AI4E_CONV_*.  The tcgen05 path
+ * needs cin % 64 == 0 and cout % 64 == 0. */
+AI4E_API int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
+                    const void* d_weight_krsc, const float* d_bias, int cout, int kh, int kw,
+                    int stride, int pad, const void* d_residual_or_null, int relu,
+                    void* d_out_nhwc, int algo, void* stream);
+
+/* K3.  Max pooling (padding = -inf).  Stands in for torchvision's `maxpool`. */
+AI4E_API int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
+                 void* d_out_nhwc, void* stream);
+
+/* K5.  Global average pool -> FC -> softmax -> top-k.  Stands in for `avgpool`, `fc` and the
+ * `softmax(...).topk(5)` of the callback.  d_in is [batch][hw][c] bf16, d_fc_w is
+ * [classes][c] bf16.  d_logits ([batch][classes] fp32) is always written; top-k outputs
+ * ([batch][topk]) may be NULL when topk == 0.  Allocates batch*c*4 bytes of scratch from the
+ * stream's memory pool. */
+AI4E_API int ai4e_head(const void* d_in_nhwc, int batch, int hw, int c, const void* d_fc_w,
+              const float* d_fc_b, int classes, float* d_logits, int32_t* d_top_idx,
+              float* d_top_prob, int topk, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Engine: one model replica on one GPU (the reference runs one replica per pod).
+ * ------------------------------------------------------------------------------------- */
+typedef struct ai4e_engine ai4e_engine;
+
+typedef struct ai4e_layer_desc {
+  int32_t op;      /* AI4E_OP_* */
+  int32_t in_buf;  /* activation slot read  (slot 0 = preprocessed input) */
+  int32_t out_buf; /* activation slot written (ignored for AI4E_OP_HEAD) */
+  int32_t res_buf; /* slot added before the activation, or -1 */
+  int32_t cin, cout;
+  int32_t kh, kw, stride, pad;
+  int32_t relu;
+  int32_t reserved;
+  int64_t w_off; /* byte offset of the bf16 weights in the blob (256-byte aligned) */
+  int64_t b_off; /* byte offset of the fp32 bias in the blob (256-byte aligned) */
+} ai4e_layer_desc;
+
+typedef struct ai4e_model_desc {
+  int32_t n_layers;
+  int32_t n_bufs;       /* number of activation slots the layer list refers to */
+  int32_t in_h, in_w;   /* network input size (after resize/crop) */
+  int32_t in_c;         /* image channels (3 or 4) */
+  int32_t in_c_pad;     /* channels of slot 0 (stem Cin; 4) */
+  int32_t num_classes;
+  int32_t reserved;
+  float mean[4], std[4];
+  const ai4e_layer_desc* layers;
+} ai4e_model_desc;
+
+typedef struct ai4e_engine_stats {
+  uint64_t images, batches;           /* completed through submit/wait or forward */
+  uint64_t batch_hist[11];            /* batches of size <=1,2,4,...,512,>512 */
+  uint64_t queue_depth;               /* submitted, not yet completed */
+  double gpu_ms_total;                /* device time of all forwards (CUDA events) */
+  double lat_ms_p50, lat_ms_p99;      /* submit -> result ready, last 4096 tasks */
+  int32_t healthy;                    /* 0 after a CUDA error on this replica */
+  int32_t launches_per_forward;       /* kernels one forward launches */
+} ai4e_engine_stats;
+
+/* Builds a replica: copies the weight blob to the device, sizes activation slots for
+ * `max_batch`, starts the micro-batching thread.  Stands in for model construction +
+ * `model.eval()` at container start-up. */
+AI4E_API int ai4e_engine_create(int device, const ai4e_model_desc* desc, const void* h_weights_blob,
+                       uint64_t blob_bytes, int max_batch, int max_wait_us, ai4e_engine** out);
+AI4E_API int ai4e_engine_destroy(ai4e_engine* e);
+
+/* One synchronous batch from HOST memory: H2D copy, preprocess (resize to the model input if
+ * src size differs), forward, top-5, D2H.  h_images is dense [batch][src_h][src_w][in_c].
+ * h_logits_or_null: [batch][num_classes].  This is `model(batch)` of the callback. */
+AI4E_API int ai4e_engine_forward_host(ai4e_engine* e, const uint8_t* h_images, int batch, int src_h,
+                             int src_w, int32_t* h_top_idx, float* h_top_prob,
+                             float* h_logits_or_null);
+
+/* Same with the uint8 batch already resident on the engine's device and results left on the
+ * device (no host copies); returns after the work is enqueued on `stream`. */
+AI4E_API int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h,
+                               int src_w, int32_t* d_top_idx, float* d_top_prob,
+                               float* d_logits_or_null, void* stream);
+
+/* Micro-batched path.  `submit` copies one image into a pinned staging slot and returns a
+ * ticket at once (the caller's buffer is free on return); the engine's batcher closes a batch
+ * at `max_batch` images or `max_wait_us` after the first one.  Thread-safe; call with the GIL
+ * released.  `wait` blocks until the ticket's batch has finished.  Together they replace the
+ * per-task thread + per-image forward of ai4e_service.py:180-183,203. */
+AI4E_API int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride,
+                       uint64_t tag, uint64_t* out_ticket);
+AI4E_API int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
+                     float* logits_or_null);
+AI4E_API int ai4e_engine_flush(ai4e_engine* e);
+AI4E_API int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out);
+
+/* Debug/parity: copy activation slot `buf` of the last forward to the host (bf16 NHWC). */
+AI4E_API int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t bytes);
+
+/* ---------------------------------------------------------------------------------------
+ * Pool: N independent replicas, one per GPU, fed by one dispatcher (least-loaded routing).
+ * The reference's equivalent is Istio ROUND_ROBIN over pods (APIs/Charts/templates/routing.yml:20-28).
+ * No collective is involved.
+ * ------------------------------------------------------------------------------------- */
+typedef struct ai4e_pool ai4e_pool;
+AI4E_API int ai4e_pool_create(const int* devices, int n_devices, const ai4e_model_desc* desc,
+                     const void* h_weights_blob, uint64_t blob_bytes, int max_batch, int max_wait_us,
+                     ai4e_pool** out);
+AI4E_API int ai4e_pool_destroy(ai4e_pool* p);
+AI4E_API int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride,
+                     uint64_t tag, uint64_t* out_ticket);
+AI4E_API int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
+                   float* logits_or_null);
+AI4E_API int ai4e_pool_flush(ai4e_pool* p);
+AI4E_API int ai4e_pool_size(ai4e_pool* p);
+AI4E_API int ai4e_pool_engine(ai4e_pool* p, int i, ai4e_engine** out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AI4E_B200_H_ */

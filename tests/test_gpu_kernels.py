@@ -1,0 +1,240 @@
+"""GPU parity tests of the stateless C-ABI kernels against the CPU oracle.
+
+Integer/byte work (K1 preprocessing) is bit-exact; floating-point kernels carry the
+tolerance written beside each assert."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import preprocess_oracle as pp
+from oracle import resnet_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+def _bits(t: torch.Tensor) -> np.ndarray:
+    return t.contiguous().view(torch.int16).cpu().numpy().view(np.uint16)
+
+
+def _dev(a: np.ndarray, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    return t if dtype is None else t.to(dtype)
+
+
+# ------------------------------------------------------------------ K1 preprocess
+@pytest.mark.parametrize("case", ["a", "b", "c", "d"])
+def test_preprocess_golden_nchw(golden_dir, case):
+    from ai4e_b200 import ops
+    g = np.load(f"{golden_dir}/preprocess.npz")
+    img = g[f"plain_{case}_in"]
+    c = img.shape[-1]
+    mean, std = (ro.MEAN4, ro.STD4) if c == 4 else (ro.IMAGENET_MEAN, ro.IMAGENET_STD)
+    out = ops.preprocess(_dev(img), mean, std, layout="nchw")
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(out), g[f"plain_{case}_out_nchw_bf16"])  # bit-exact
+
+
+def test_preprocess_truth_table(golden_dir):
+    """all 256 byte values x 4 channels: the complete truth table of the LUT."""
+    from ai4e_b200 import ops
+    g = np.load(f"{golden_dir}/preprocess.npz")
+    out = ops.preprocess(_dev(g["ramp_in"]), ro.MEAN4, ro.STD4, layout="nchw")
+    assert np.array_equal(_bits(out), g["ramp_out_nchw_bf16"])
+
+
+@pytest.mark.parametrize("shape", [(3, 224, 224, 3), (2, 256, 256, 4), (5, 48, 80, 3), (1, 7, 9, 3)])
+@pytest.mark.parametrize("layout", ["nchw", "nhwc"])
+def test_preprocess_vs_oracle(shape, layout):
+    from ai4e_b200 import ops
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 256, shape, dtype=np.uint8)
+    c = shape[-1]
+    mean, std = (ro.MEAN4, ro.STD4) if c == 4 else (ro.IMAGENET_MEAN, ro.IMAGENET_STD)
+    out = ops.preprocess(_dev(img), mean, std, layout=layout, out_channels=4)
+    if layout == "nchw":
+        want = pp.bf16_bits(pp.preprocess_nchw(img, mean, std))
+    else:
+        x = pp.preprocess_nhwc(img, mean, std)
+        if c == 3:
+            x = np.concatenate([x, np.zeros(shape[:3] + (1,), np.float32)], axis=-1)
+        want = pp.bf16_bits(x)
+    assert np.array_equal(_bits(out), want)  # bit-exact
+
+
+def test_preprocess_resize_crop_golden(golden_dir):
+    from ai4e_b200 import ops
+    g = np.load(f"{golden_dir}/preprocess.npz")
+    rh, rw, ch, cw = [int(v) for v in g["resize_params"]]
+    out = ops.preprocess(_dev(g["resize_in"]), ro.IMAGENET_MEAN, ro.IMAGENET_STD, layout="nchw",
+                         resize=(rh, rw), crop=(ch, cw))
+    assert np.array_equal(_bits(out), g["resize_out_nchw_bf16"])  # bit-exact (same fp32 op order)
+    img = ro.synthetic_images(1, 256, 256, 3, seed=int(g["resize256_in_seed"][0]))
+    out = ops.preprocess(_dev(img), ro.IMAGENET_MEAN, ro.IMAGENET_STD, layout="nchw", resize=(256, 256),
+                         crop=(224, 224))
+    assert np.array_equal(_bits(out), g["resize256_out_nchw_bf16"])
+
+
+def test_preprocess_strided_rows():
+    """a chip cut out of a larger tile: row stride > w*c (land-cover config)."""
+    from ai4e_b200 import ops
+    rng = np.random.default_rng(3)
+    tile = rng.integers(0, 256, (1, 64, 96, 4), dtype=np.uint8)
+    d = _dev(tile)
+    chip = d[:, 16:48, 32:64, :]
+    out = ops.preprocess(chip, ro.MEAN4, ro.STD4, layout="nchw")
+    want = pp.bf16_bits(pp.preprocess_nchw(np.ascontiguousarray(tile[:, 16:48, 32:64, :]), ro.MEAN4, ro.STD4))
+    assert np.array_equal(_bits(out), want)
+
+
+def test_preprocess_rejects_bad_args():
+    from ai4e_b200 import ops, Ai4eError
+    img = torch.zeros((1, 8, 8, 2), dtype=torch.uint8, device="cuda")
+    with pytest.raises(Ai4eError):
+        ops.preprocess(img, (0.5, 0.5), (0.2, 0.2))
+    img = torch.zeros((1, 8, 8, 3), dtype=torch.uint8, device="cuda")
+    with pytest.raises(Ai4eError):
+        ops.preprocess(img, ro.IMAGENET_MEAN, (0.2, 0.0, 0.2))
+
+
+# ------------------------------------------------------------------ convolutions
+def _conv_case(b, h, w, cin, cout, k, stride, pad, relu, residual, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    x = (torch.randn((b, h, w, cin), generator=g) * 0.7).to(torch.bfloat16)
+    wt = (torch.randn((cout, k, k, cin), generator=g) * (2.0 / (k * k * cin)) ** 0.5).to(torch.bfloat16)
+    bias = torch.randn((cout,), generator=g) * 0.1
+    p = (h + 2 * pad - k) // stride + 1
+    q = (w + 2 * pad - k) // stride + 1
+    res = (torch.randn((b, p, q, cout), generator=g) * 0.5).to(torch.bfloat16) if residual else None
+    y = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), wt.float().permute(0, 3, 1, 2), bias,
+                                   stride, pad).permute(0, 2, 3, 1)
+    if res is not None:
+        y = y + res.float()
+    if relu:
+        y = torch.relu(y)
+    return x, wt, bias, res, y.contiguous()
+
+
+def _check_conv(out: torch.Tensor, want: torch.Tensor):
+    got = out.float().cpu()
+    # fp32 accumulation, one bf16 rounding of the result: |err| <= 2^-8 |want| + accumulation noise
+    tol = 2.0 ** -7 * want.abs() + 2e-3
+    bad = (got - want).abs() > tol
+    assert not bad.any(), f"{int(bad.sum())} of {bad.numel()} outside tolerance; max err {(got - want).abs().max():.4f}"
+
+
+DIRECT_CASES = [
+    (2, 32, 32, 4, 64, 7, 2, 3, True, False),    # stem shape, small image
+    (1, 224, 224, 4, 64, 7, 2, 3, True, False),  # stem at full size
+    (2, 9, 11, 16, 8, 3, 1, 1, False, True),
+]
+
+
+@pytest.mark.parametrize("case", DIRECT_CASES)
+def test_conv_direct_vs_oracle(case):
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, cin, cout, k, stride, pad, relu, residual = case
+    x, wt, bias, res, want = _conv_case(*case)
+    out = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), stride, pad, res.cuda() if res is not None else None,
+                         relu, algo=L.CONV_DIRECT)
+    torch.cuda.synchronize()
+    _check_conv(out, want)
+
+
+# (b, h, w, cin, cout, k, stride, pad, relu, residual): every conv geometry of ResNet-18/50
+# after the stem, at small batch, plus ragged tails (M not a multiple of 128)
+IGEMM_CASES = [
+    (2, 56, 56, 64, 64, 1, 1, 0, True, False),
+    (2, 56, 56, 64, 64, 3, 1, 1, True, False),
+    (2, 56, 56, 64, 256, 1, 1, 0, True, True),
+    (2, 56, 56, 256, 64, 1, 1, 0, True, False),
+    (2, 56, 56, 256, 128, 1, 1, 0, True, False),
+    (2, 56, 56, 128, 128, 3, 2, 1, True, False),
+    (2, 56, 56, 256, 512, 1, 2, 0, False, False),
+    (2, 28, 28, 128, 512, 1, 1, 0, True, True),
+    (2, 28, 28, 512, 128, 1, 1, 0, True, False),
+    (2, 28, 28, 128, 128, 3, 1, 1, True, False),
+    (2, 28, 28, 256, 256, 3, 2, 1, True, False),
+    (2, 28, 28, 512, 1024, 1, 2, 0, False, False),
+    (2, 14, 14, 256, 1024, 1, 1, 0, True, True),
+    (2, 14, 14, 1024, 256, 1, 1, 0, True, False),
+    (2, 14, 14, 256, 256, 3, 1, 1, True, False),
+    (2, 14, 14, 512, 512, 3, 2, 1, True, False),
+    (2, 14, 14, 1024, 2048, 1, 2, 0, False, False),
+    (3, 7, 7, 512, 2048, 1, 1, 0, True, True),
+    (3, 7, 7, 2048, 512, 1, 1, 0, True, False),
+    (3, 7, 7, 512, 512, 3, 1, 1, True, False),
+    (1, 7, 7, 512, 512, 3, 1, 1, True, True),     # M = 49: a single, mostly empty tile
+    (1, 5, 9, 64, 64, 3, 1, 1, False, False),     # tiny, ragged
+    (5, 13, 17, 128, 192, 3, 2, 1, True, True),   # odd sizes, Cout = 3 x 64
+    (1, 64, 64, 64, 128, 3, 1, 1, True, False),   # M = 4096: exact multiple of 128
+    (2, 8, 8, 64, 64, 1, 1, 0, False, False),     # M = 128: exactly one tile
+]
+
+
+@pytest.mark.parametrize("case", IGEMM_CASES, ids=lambda c: "x".join(str(v) for v in c[:8]))
+def test_conv_igemm_vs_oracle(case):
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, cin, cout, k, stride, pad, relu, residual = case
+    x, wt, bias, res, want = _conv_case(*case, seed=sum(case[:8]))
+    out = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), stride, pad, res.cuda() if res is not None else None,
+                         relu, algo=L.CONV_IGEMM)
+    torch.cuda.synchronize()
+    _check_conv(out, want)
+
+
+def test_conv_igemm_many_tiles_multi_wave():
+    """more tiles than SMs, so every CTA loops over several tiles and both TMEM stages cycle."""
+    from ai4e_b200 import ops, _lib as L
+    case = (16, 56, 56, 64, 64, 3, 1, 1, True, True)  # M = 50176 -> 392 tiles
+    x, wt, bias, res, want = _conv_case(*case, seed=5)
+    out = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), 1, 1, res.cuda(), True, algo=L.CONV_IGEMM)
+    torch.cuda.synchronize()
+    _check_conv(out, want)
+
+
+def test_conv_igemm_rejects_unsupported():
+    from ai4e_b200 import ops, _lib as L, Ai4eError
+    x = torch.zeros((1, 8, 8, 48), dtype=torch.bfloat16, device="cuda")
+    wt = torch.zeros((64, 1, 1, 48), dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(Ai4eError):
+        ops.conv_layer(x, wt, torch.zeros(64, device="cuda"), 1, 0, algo=L.CONV_IGEMM)
+
+
+# ------------------------------------------------------------------ pooling + head
+@pytest.mark.parametrize("shape", [(2, 112, 112, 64), (3, 9, 7, 8), (1, 128, 128, 64)])
+def test_maxpool_vs_oracle(shape):
+    from ai4e_b200 import ops
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(shape, generator=g).to(torch.bfloat16)
+    want = torch.nn.functional.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)
+    out = ops.maxpool(x.cuda())
+    assert torch.equal(out.float().cpu(), want.contiguous())  # exact: max of bf16 values
+
+
+@pytest.mark.parametrize("b,hw,c,classes", [(1, 7, 2048, 1000), (9, 7, 512, 1000), (64, 8, 2048, 1000), (3, 2, 64, 10)])
+def test_head_vs_oracle(b, hw, c, classes):
+    from ai4e_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    x = torch.relu(torch.randn((b, hw, hw, c), generator=g)).to(torch.bfloat16)
+    w = (torch.randn((classes, c), generator=g) * 0.02).to(torch.bfloat16)
+    bias = torch.randn((classes,), generator=g) * 0.1
+    logits, idx, prob = ops.head(x.cuda(), w.cuda(), bias.cuda())
+    pooled = x.float().mean(dim=(1, 2))
+    want = pooled @ w.float().t() + bias
+    got = logits.cpu()
+    # fp32 throughout; only the summation order differs
+    assert torch.allclose(got, want, atol=2e-4, rtol=1e-4), (got - want).abs().max()
+    want_idx, want_prob = ro.softmax_top5(got.numpy(), k=min(5, classes))
+    assert np.array_equal(idx.cpu().numpy(), want_idx)
+    assert np.allclose(prob.cpu().numpy(), want_prob, atol=1e-6, rtol=1e-4)
+
+
+def test_head_topk_tie_break():
+    """equal logits resolve to the lower class index, like a stable sort."""
+    from ai4e_b200 import ops
+    x = torch.zeros((2, 1, 1, 64), dtype=torch.bfloat16)
+    w = torch.zeros((40, 64), dtype=torch.bfloat16)
+    bias = torch.zeros(40)
+    bias[[3, 17, 30]] = 1.0
+    _, idx, prob = ops.head(x.cuda(), w.cuda(), bias.cuda())
+    assert idx.cpu().tolist() == [[3, 17, 30, 0, 1]] * 2
