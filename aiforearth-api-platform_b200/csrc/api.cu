@@ -51,9 +51,9 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
                               pad, d_residual_or_null, relu, d_out_nhwc, (cudaStream_t)stream);
   IgemmPlan plan;
   int rc = igemm_make_plan(&plan, d_in_nhwc, batch, h, w, cin, d_weight_krsc, d_bias, cout, kh, kw,
-                           stride, pad, d_residual_or_null, relu, d_out_nhwc, 0);
+                           stride, pad, d_residual_or_null, relu, d_out_nhwc);
   if (rc) return rc;
-  return igemm_launch(plan, (cudaStream_t)stream);
+  return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 
 int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,

@@ -233,9 +233,13 @@ int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad) {
          pad >= 0 && pad < 128 && stride >= 1 && stride <= 8;
 }
 
+// Builds the tensor maps for a layer whose activation tensors hold up to `N` images.  The
+// same plan then serves any batch <= N: only M (hence the tile count) changes per launch;
+// the last tile of a smaller batch reads rows of images >= batch (stale but in-bounds) and
+// the epilogue masks them.
 int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
-                    int pad, const void* residual, int relu, void* out, int force_block_n) {
+                    int pad, const void* residual, int relu, void* out) {
   AI4E_REQUIRE(igemm_supported(Cin, Cout, R, S, stride, pad),
                "conv(igemm): unsupported shape Cin=%d Cout=%d %dx%d s%d p%d (needs Cin%%64==0, Cout%%64==0)",
                Cin, Cout, R, S, stride, pad);
@@ -245,31 +249,33 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
                "conv(igemm): pointers must be 16-byte aligned");
   const int P = (H + 2 * pad - R) / stride + 1, Q = (W + 2 * pad - S) / stride + 1;
   AI4E_REQUIRE(P > 0 && Q > 0, "conv(igemm): empty output");
-  const long long M = (long long)N * P * Q;
-  AI4E_REQUIRE(M < (1ll << 31) - kBlockM, "conv(igemm): M too large");
-  const int bn = force_block_n ? force_block_n : igemm_pick_block_n(Cout, M);
-  AI4E_REQUIRE(bn == 64 || bn == 128 || bn == 256, "conv(igemm): bad BLOCK_N %d", bn);
-  AI4E_REQUIRE(Cout % bn == 0, "conv(igemm): Cout %d not a multiple of BLOCK_N %d", Cout, bn);
+  AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "conv(igemm): M too large");
   IgemmParams& q = plan->prm;
-  q.M = (int)M; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
+  q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks;
-  q.tiles_m = (int)((M + kBlockM - 1) / kBlockM); q.tiles_n = Cout / bn;
-  q.num_tiles = q.tiles_m * q.tiles_n; q.relu = relu; q.bias = bias;
+  q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias;
   q.residual = (const bf16*)residual; q.out = (bf16*)out;
-  plan->block_n = bn;
-  plan->grid = std::min(q.num_tiles, sm_count());
+  plan->max_batch = N;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint64_t ktot = (uint64_t)R * S * Cin;
   const uint64_t dims[2] = {ktot, (uint64_t)Cout};
   const uint64_t strides[1] = {ktot * 2};
-  const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)bn};
   const uint32_t es[2] = {1, 1};
-  return tmap_encode_tiled(&plan->tmap_b, weight, 2, dims, strides, box, es, CU_TENSOR_MAP_SWIZZLE_128B);
+  const int bns[3] = {64, 128, 256};
+  for (int i = 0; i < 3; ++i) {
+    plan->has_bn[i] = Cout % bns[i] == 0;
+    if (!plan->has_bn[i]) continue;
+    const uint32_t box[2] = {(uint32_t)kBlockK, (uint32_t)bns[i]};
+    rc = tmap_encode_tiled(&plan->tmap_b[i], weight, 2, dims, strides, box, es, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  return AI4E_OK;
 }
 
 template <int BN>
-static int igemm_launch_bn(const IgemmPlan& plan, cudaStream_t stream) {
+static int igemm_launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& prm, int grid,
+                           cudaStream_t stream) {
   static unsigned long long attr_done = 0;  // bit per device
   int dev = 0;
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
@@ -278,20 +284,29 @@ static int igemm_launch_bn(const IgemmPlan& plan, cudaStream_t stream) {
                                        IgemmCfg<BN>::kSmemBytes));
     attr_done |= 1ull << dev;
   }
-  conv_igemm_kernel<BN><<<plan.grid, kIgemmThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(
-      plan.tmap_a, plan.tmap_b, plan.prm);
+  conv_igemm_kernel<BN><<<grid, kIgemmThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(ta, tb, prm);
   AI4E_CUDA_TRY(cudaGetLastError());
   return AI4E_OK;
 }
 
-int igemm_launch(const IgemmPlan& plan, cudaStream_t stream) {
-  switch (plan.block_n) {
-    case 64: return igemm_launch_bn<64>(plan, stream);
-    case 128: return igemm_launch_bn<128>(plan, stream);
-    case 256: return igemm_launch_bn<256>(plan, stream);
+int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream_t stream) {
+  AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "conv(igemm): batch %d outside plan (max %d)", batch,
+               plan.max_batch);
+  IgemmParams prm = plan.prm;
+  const long long M = (long long)batch * prm.PQ;
+  const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M);
+  const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
+  AI4E_REQUIRE(bi >= 0 && plan.has_bn[bi], "conv(igemm): BLOCK_N %d not available for Cout %d", bn, prm.Cout);
+  prm.M = (int)M;
+  prm.tiles_m = (int)((M + kBlockM - 1) / kBlockM);
+  prm.tiles_n = prm.Cout / bn;
+  prm.num_tiles = prm.tiles_m * prm.tiles_n;
+  const int grid = std::min(prm.num_tiles, sm_count());
+  switch (bn) {
+    case 64: return igemm_launch_bn<64>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
+    case 128: return igemm_launch_bn<128>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
+    default: return igemm_launch_bn<256>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
   }
-  set_last_error("conv(igemm): bad BLOCK_N %d", plan.block_n);
-  return AI4E_ERR_INVALID;
 }
 
 }  // namespace ai4e

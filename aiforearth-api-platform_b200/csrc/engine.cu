@@ -1,0 +1,734 @@
+// Engine: one model replica on one GPU, plus the micro-batching request queue and the
+// multi-GPU pool (extern "C" entry points `ai4e_engine_*` / `ai4e_pool_*`).
+//
+// What it replaces in the reference: the per-task thread + per-image model call of
+// APIs/1.0/base-py/ai4e_service.py:180-183,203 (one `threading.Thread` per task, no batching;
+// upstream pushes one message at a time, ProcessManager/BackendQueueProcessor/host.json:5-9).
+// Here request threads copy their payload straight into a pinned staging slot and get a
+// ticket; a batcher thread closes the batch on `max_batch` or `max_wait_us`, issues
+// H2D -> preprocess -> forward -> top-5 -> D2H on the batch's own stream, and a completer
+// thread publishes results.  Three batch contexts are in flight so the H2D copy of batch k+1
+// overlaps the forward of batch k (forwards themselves are chained by an event because they
+// share the activation slots).
+#include "../../include/ai4e_b200.h"
+
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+using namespace ai4e;
+using Clock = std::chrono::steady_clock;
+
+namespace {
+
+constexpr int kNumCtx = 3;
+constexpr uint64_t kResultRing = 1ull << 16;
+constexpr uint64_t kLogitRing = 1ull << 12;
+constexpr int kLatRing = 4096;
+
+struct LayerRt {
+  ai4e_layer_desc d;
+  int in_h, in_w, out_h, out_w;
+  bool igemm;
+  IgemmPlan plan;
+};
+
+struct BatchCtx {
+  uint8_t* h_in = nullptr;  // pinned, max_batch * slot_bytes
+  uint8_t* d_in = nullptr;
+  int32_t *h_idx = nullptr, *d_idx = nullptr;
+  float *h_prob = nullptr, *d_prob = nullptr;
+  float *h_logits = nullptr, *d_logits = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev_start = nullptr, ev_fwd = nullptr, ev_done = nullptr;
+  int count = 0, src_h = 0, src_w = 0;
+  uint64_t first_ticket = 0;
+  std::atomic<int> copied{0};
+  Clock::time_point t_first;
+  int launch_rc = 0;
+};
+
+}  // namespace
+
+struct ai4e_engine {
+  int device = 0, max_batch = 0, max_wait_us = 0;
+  ai4e_model_desc desc{};
+  std::vector<LayerRt> layers;
+  std::vector<void*> bufs;
+  std::vector<size_t> buf_elems_per_image;
+  uint8_t* d_blob = nullptr;
+  float* d_pooled = nullptr;
+  size_t slot_bytes = 0;  // staging bytes per image
+  int launches = 0;
+
+  // forwards share activation slots: chain them
+  std::mutex launch_mu;
+  cudaEvent_t ev_chain = nullptr;
+  bool chain_valid = false;
+
+  // synchronous path
+  std::mutex sync_mu;
+  BatchCtx sync_ctx;
+
+  // micro-batcher
+  BatchCtx ctx[kNumCtx];
+  std::mutex mu;
+  std::condition_variable cv_work, cv_free, cv_done, cv_inflight;
+  std::deque<BatchCtx*> free_q, closed_q, inflight_q;
+  BatchCtx* open_ctx = nullptr;
+  uint64_t next_ticket = 0, done_upto = 0;
+  bool stopping = false, flush_req = false, batcher_done = false, completer_done = false;
+  std::atomic<int> healthy{1};
+  std::thread batcher, completer;
+
+  // results
+  std::vector<int32_t> r_idx;
+  std::vector<float> r_prob, r_logits;
+  std::vector<int8_t> r_status;
+  std::vector<Clock::time_point> r_submit;
+  std::vector<float> lat_ms;
+  uint64_t lat_n = 0;
+  ai4e_engine_stats st{};
+};
+
+namespace {
+
+int alloc_ctx(ai4e_engine* e, BatchCtx& c) {
+  const size_t B = e->max_batch;
+  const int K = e->desc.num_classes;
+  AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_in, B * e->slot_bytes, cudaHostAllocDefault));
+  AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_in, B * e->slot_bytes));
+  AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_idx, B * AI4E_TOPK * sizeof(int32_t), cudaHostAllocDefault));
+  AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_prob, B * AI4E_TOPK * sizeof(float), cudaHostAllocDefault));
+  AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_logits, B * K * sizeof(float), cudaHostAllocDefault));
+  AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_idx, B * AI4E_TOPK * sizeof(int32_t)));
+  AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_prob, B * AI4E_TOPK * sizeof(float)));
+  AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_logits, B * K * sizeof(float)));
+  AI4E_CUDA_TRY(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  AI4E_CUDA_TRY(cudaEventCreate(&c.ev_start));
+  AI4E_CUDA_TRY(cudaEventCreate(&c.ev_fwd));
+  AI4E_CUDA_TRY(cudaEventCreateWithFlags(&c.ev_done, cudaEventDisableTiming));
+  return AI4E_OK;
+}
+
+void free_ctx(BatchCtx& c) {
+  if (c.h_in) cudaFreeHost(c.h_in);
+  if (c.d_in) cudaFree(c.d_in);
+  if (c.h_idx) cudaFreeHost(c.h_idx);
+  if (c.h_prob) cudaFreeHost(c.h_prob);
+  if (c.h_logits) cudaFreeHost(c.h_logits);
+  if (c.d_idx) cudaFree(c.d_idx);
+  if (c.d_prob) cudaFree(c.d_prob);
+  if (c.d_logits) cudaFree(c.d_logits);
+  if (c.stream) cudaStreamDestroy(c.stream);
+  if (c.ev_start) cudaEventDestroy(c.ev_start);
+  if (c.ev_fwd) cudaEventDestroy(c.ev_fwd);
+  if (c.ev_done) cudaEventDestroy(c.ev_done);
+  c.h_in = c.d_in = nullptr;
+  c.h_idx = c.d_idx = nullptr;
+  c.h_prob = c.d_prob = c.h_logits = c.d_logits = nullptr;
+  c.stream = nullptr;
+  c.ev_start = c.ev_fwd = c.ev_done = nullptr;
+}
+
+// preprocess + every layer, enqueued on `stream`.  Caller holds e->launch_mu.
+int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
+                    int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream) {
+  const ai4e_model_desc& m = e->desc;
+  const bool resize = src_h != m.in_h || src_w != m.in_w;
+  int rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, 0, resize ? m.in_h : 0,
+                             resize ? m.in_w : 0, m.in_h, m.in_w, m.mean, m.std, AI4E_LAYOUT_NHWC,
+                             m.in_c_pad, e->bufs[0], stream);
+  if (rc < 0) return rc;
+  for (LayerRt& L : e->layers) {
+    const ai4e_layer_desc& d = L.d;
+    if (d.op == AI4E_OP_CONV) {
+      if (L.igemm) {
+        rc = igemm_launch(L.plan, batch, 0, stream);
+      } else {
+        rc = launch_conv_direct(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
+                                (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
+                                d.res_buf >= 0 ? e->bufs[d.res_buf] : nullptr, d.relu, e->bufs[d.out_buf],
+                                stream);
+      }
+    } else if (d.op == AI4E_OP_MAXPOOL) {
+      rc = launch_maxpool(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, d.kh, d.stride, d.pad,
+                          e->bufs[d.out_buf], stream);
+    } else {
+      rc = launch_head(e->bufs[d.in_buf], batch, L.in_h * L.in_w, d.cin, e->d_blob + d.w_off,
+                       (const float*)(e->d_blob + d.b_off), d.cout, e->d_pooled, d_logits, d_idx, d_prob,
+                       AI4E_TOPK, stream);
+    }
+    if (rc) return rc;
+  }
+  return AI4E_OK;
+}
+
+// H2D (already staged in c.h_in, dense) -> forward -> D2H on c.stream
+int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
+  const int K = e->desc.num_classes;
+  const size_t img_bytes = (size_t)c.src_h * c.src_w * e->desc.in_c;
+  AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, c.h_in, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+  {
+    std::lock_guard<std::mutex> lk(e->launch_mu);
+    if (e->chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(c.stream, e->ev_chain, 0));
+    AI4E_CUDA_TRY(cudaEventRecord(c.ev_start, c.stream));
+    int rc = forward_enqueue(e, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream);
+    if (rc) return rc;
+    AI4E_CUDA_TRY(cudaEventRecord(c.ev_fwd, c.stream));
+    AI4E_CUDA_TRY(cudaEventRecord(e->ev_chain, c.stream));
+    e->chain_valid = true;
+  }
+  AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, (size_t)c.count * AI4E_TOPK * sizeof(int32_t),
+                                cudaMemcpyDeviceToHost, c.stream));
+  AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_prob, c.d_prob, (size_t)c.count * AI4E_TOPK * sizeof(float),
+                                cudaMemcpyDeviceToHost, c.stream));
+  if (want_logits)
+    AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_logits, c.d_logits, (size_t)c.count * K * sizeof(float),
+                                  cudaMemcpyDeviceToHost, c.stream));
+  AI4E_CUDA_TRY(cudaEventRecord(c.ev_done, c.stream));
+  return AI4E_OK;
+}
+
+void account_batch(ai4e_engine* e, BatchCtx& c) {  // caller holds e->mu
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, c.ev_start, c.ev_fwd) == cudaSuccess) e->st.gpu_ms_total += ms;
+  e->st.images += c.count;
+  e->st.batches += 1;
+  int b = 0;
+  while ((1 << b) < c.count && b < 10) ++b;
+  e->st.batch_hist[b] += 1;
+}
+
+void batcher_main(ai4e_engine* e) {
+  cudaSetDevice(e->device);
+  std::unique_lock<std::mutex> lk(e->mu);
+  for (;;) {
+    for (;;) {
+      if (!e->closed_q.empty() || e->stopping) break;
+      BatchCtx* o = e->open_ctx;
+      if (o && o->count > 0) {
+        const auto deadline = o->t_first + std::chrono::microseconds(e->max_wait_us);
+        if (e->flush_req || Clock::now() >= deadline) {
+          e->closed_q.push_back(o);
+          e->open_ctx = nullptr;
+          break;
+        }
+        e->cv_work.wait_until(lk, deadline);
+      } else {
+        e->flush_req = false;
+        e->cv_work.wait(lk);
+      }
+    }
+    if (e->closed_q.empty()) {
+      if (e->stopping) {
+        if (e->open_ctx && e->open_ctx->count > 0) {  // drain what was submitted
+          e->closed_q.push_back(e->open_ctx);
+          e->open_ctx = nullptr;
+          continue;
+        }
+        break;
+      }
+      continue;
+    }
+    BatchCtx* c = e->closed_q.front();
+    e->closed_q.pop_front();
+    lk.unlock();
+    while (c->copied.load(std::memory_order_acquire) < c->count) std::this_thread::yield();
+    c->launch_rc = e->healthy.load() ? launch_batch(e, *c, true) : AI4E_ERR_STATE;
+    lk.lock();
+    e->inflight_q.push_back(c);
+    e->cv_inflight.notify_one();
+  }
+  e->batcher_done = true;
+  e->cv_inflight.notify_all();
+}
+
+void completer_main(ai4e_engine* e) {
+  cudaSetDevice(e->device);
+  std::unique_lock<std::mutex> lk(e->mu);
+  for (;;) {
+    e->cv_inflight.wait(lk, [&] { return !e->inflight_q.empty() || e->batcher_done; });
+    if (e->inflight_q.empty()) break;
+    BatchCtx* c = e->inflight_q.front();
+    e->inflight_q.pop_front();
+    lk.unlock();
+    int rc = c->launch_rc;
+    if (rc == AI4E_OK) {
+      cudaError_t ce = cudaEventSynchronize(c->ev_done);
+      if (ce != cudaSuccess) {
+        set_last_error("batch failed on device %d: %s", e->device, cudaGetErrorString(ce));
+        rc = AI4E_ERR_CUDA;
+      }
+    }
+    if (rc != AI4E_OK) e->healthy.store(0);
+    const auto now = Clock::now();
+    lk.lock();
+    const int K = e->desc.num_classes;
+    for (int i = 0; i < c->count; ++i) {
+      const uint64_t t = c->first_ticket + i;
+      const uint64_t r = t % kResultRing;
+      e->r_status[r] = (int8_t)rc;
+      if (rc == AI4E_OK) {
+        memcpy(&e->r_idx[r * AI4E_TOPK], c->h_idx + (size_t)i * AI4E_TOPK, AI4E_TOPK * sizeof(int32_t));
+        memcpy(&e->r_prob[r * AI4E_TOPK], c->h_prob + (size_t)i * AI4E_TOPK, AI4E_TOPK * sizeof(float));
+        memcpy(&e->r_logits[(t % kLogitRing) * K], c->h_logits + (size_t)i * K, K * sizeof(float));
+        e->lat_ms[e->lat_n++ % kLatRing] =
+            std::chrono::duration<float, std::milli>(now - e->r_submit[r]).count();
+      }
+    }
+    if (rc == AI4E_OK) account_batch(e, *c);
+    e->done_upto = c->first_ticket + c->count;
+    c->count = 0;
+    c->copied.store(0);
+    e->free_q.push_back(c);
+    e->cv_free.notify_all();
+    e->cv_done.notify_all();
+  }
+  e->completer_done = true;
+  e->cv_done.notify_all();
+}
+
+int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uint64_t blob_bytes, int max_batch,
+                  int max_wait_us, ai4e_engine** out) {
+  AI4E_REQUIRE(desc && blob && out, "engine_create: null pointer");
+  AI4E_REQUIRE(desc->n_layers > 0 && desc->layers, "engine_create: empty layer list");
+  AI4E_REQUIRE(max_batch >= 1 && max_batch <= 4096, "engine_create: max_batch %d outside [1, 4096]", max_batch);
+  AI4E_REQUIRE(desc->in_c == 3 || desc->in_c == 4, "engine_create: in_c must be 3 or 4");
+  AI4E_REQUIRE(desc->in_c_pad == 4, "engine_create: in_c_pad must be 4");
+  AI4E_REQUIRE(desc->n_bufs >= 2 && desc->n_bufs <= 64, "engine_create: n_bufs outside [2, 64]");
+  AI4E_REQUIRE(desc->num_classes >= AI4E_TOPK, "engine_create: fewer classes than top-k");
+  int ndev = 0;
+  AI4E_CUDA_TRY(cudaGetDeviceCount(&ndev));
+  AI4E_REQUIRE(device >= 0 && device < ndev, "engine_create: device %d of %d", device, ndev);
+  AI4E_CUDA_TRY(cudaSetDevice(device));
+
+  ai4e_engine* e = new ai4e_engine();
+  e->device = device; e->max_batch = max_batch; e->max_wait_us = std::max(0, max_wait_us);
+  e->desc = *desc;
+  e->desc.layers = nullptr;
+  auto fail = [&](int rc) { ai4e_engine_destroy(e); return rc; };
+
+  // ---- shape inference over the slot graph
+  struct Shape { int h = 0, w = 0, c = 0; bool set = false; };
+  std::vector<Shape> shp(desc->n_bufs);
+  shp[0] = {desc->in_h, desc->in_w, desc->in_c_pad, true};
+  e->buf_elems_per_image.assign(desc->n_bufs, 0);
+  e->buf_elems_per_image[0] = (size_t)desc->in_h * desc->in_w * desc->in_c_pad;
+  bool seen_head = false;
+  for (int i = 0; i < desc->n_layers; ++i) {
+    LayerRt L{};
+    L.d = desc->layers[i];
+    const ai4e_layer_desc& d = L.d;
+    if (!(d.in_buf >= 0 && d.in_buf < desc->n_bufs && shp[d.in_buf].set)) {
+      set_last_error("layer %d reads slot %d before it is written", i, d.in_buf);
+      return fail(AI4E_ERR_INVALID);
+    }
+    const Shape in = shp[d.in_buf];
+    L.in_h = in.h; L.in_w = in.w;
+    if (d.cin != in.c) {
+      set_last_error("layer %d: cin %d but slot %d holds %d channels", i, d.cin, d.in_buf, in.c);
+      return fail(AI4E_ERR_INVALID);
+    }
+    if (d.op == AI4E_OP_HEAD) {
+      if (d.w_off < 0 || d.b_off < 0 || (uint64_t)d.w_off + (uint64_t)d.cout * d.cin * 2 > blob_bytes ||
+          (uint64_t)d.b_off + (uint64_t)d.cout * 4 > blob_bytes || d.cout != desc->num_classes || d.cin % 8) {
+        set_last_error("layer %d (head): bad weights/geometry", i);
+        return fail(AI4E_ERR_INVALID);
+      }
+      seen_head = true;
+      e->layers.push_back(L);
+      continue;
+    }
+    if (!(d.out_buf > 0 && d.out_buf < desc->n_bufs && d.out_buf != d.in_buf && d.out_buf != d.res_buf) ||
+        d.kh <= 0 || d.kw <= 0 || d.stride <= 0 || d.pad < 0 || in.h + 2 * d.pad < d.kh || in.w + 2 * d.pad < d.kw) {
+      set_last_error("layer %d: bad slots or geometry", i);
+      return fail(AI4E_ERR_INVALID);
+    }
+    L.out_h = (in.h + 2 * d.pad - d.kh) / d.stride + 1;
+    L.out_w = (in.w + 2 * d.pad - d.kw) / d.stride + 1;
+    int cout = d.cout;
+    if (d.op == AI4E_OP_MAXPOOL) {
+      cout = d.cin;
+      if (d.kh != d.kw || d.cin % 8) { set_last_error("layer %d (maxpool): bad geometry", i); return fail(AI4E_ERR_INVALID); }
+    } else if (d.op == AI4E_OP_CONV) {
+      const uint64_t wbytes = (uint64_t)d.cout * d.kh * d.kw * d.cin * 2;
+      if (d.w_off < 0 || d.b_off < 0 || (d.w_off & 255) || (d.b_off & 255) || (uint64_t)d.w_off + wbytes > blob_bytes ||
+          (uint64_t)d.b_off + (uint64_t)d.cout * 4 > blob_bytes || d.cout % 8) {
+        set_last_error("layer %d (conv): weights outside the blob or misaligned", i);
+        return fail(AI4E_ERR_INVALID);
+      }
+      if (d.res_buf >= 0) {
+        const bool ok = d.res_buf < desc->n_bufs && shp[d.res_buf].set && shp[d.res_buf].h == L.out_h &&
+                        shp[d.res_buf].w == L.out_w && shp[d.res_buf].c == d.cout;
+        if (!ok) { set_last_error("layer %d: residual slot %d does not match the output", i, d.res_buf); return fail(AI4E_ERR_INVALID); }
+      }
+      L.igemm = igemm_supported(d.cin, d.cout, d.kh, d.kw, d.stride, d.pad) != 0;
+    } else {
+      set_last_error("layer %d: unknown op %d", i, d.op);
+      return fail(AI4E_ERR_INVALID);
+    }
+    shp[d.out_buf] = {L.out_h, L.out_w, cout, true};
+    e->buf_elems_per_image[d.out_buf] =
+        std::max(e->buf_elems_per_image[d.out_buf], (size_t)L.out_h * L.out_w * cout);
+    e->layers.push_back(L);
+  }
+  if (!seen_head || e->layers.back().d.op != AI4E_OP_HEAD) {
+    set_last_error("engine_create: the last layer must be the head");
+    return fail(AI4E_ERR_INVALID);
+  }
+
+  // ---- device memory: weights, activation slots, scratch
+#define TRY_OR_FAIL(expr)                                                                    \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess) {                                                                 \
+      set_last_error("%s failed: %s", #expr, cudaGetErrorString(_e));                        \
+      return fail(_e == cudaErrorMemoryAllocation ? AI4E_ERR_NOMEM : AI4E_ERR_CUDA);         \
+    }                                                                                        \
+  } while (0)
+  TRY_OR_FAIL(cudaMalloc((void**)&e->d_blob, blob_bytes));
+  TRY_OR_FAIL(cudaMemcpy(e->d_blob, blob, blob_bytes, cudaMemcpyHostToDevice));
+  e->bufs.assign(desc->n_bufs, nullptr);
+  for (int b = 0; b < desc->n_bufs; ++b) {
+    if (!e->buf_elems_per_image[b]) continue;
+    const size_t bytes = e->buf_elems_per_image[b] * 2 * (size_t)max_batch;
+    TRY_OR_FAIL(cudaMalloc(&e->bufs[b], bytes));
+    TRY_OR_FAIL(cudaMemset(e->bufs[b], 0, bytes));
+  }
+  int head_c = e->layers.back().d.cin;
+  TRY_OR_FAIL(cudaMalloc((void**)&e->d_pooled, (size_t)max_batch * head_c * sizeof(float)));
+  TRY_OR_FAIL(cudaEventCreateWithFlags(&e->ev_chain, cudaEventDisableTiming));
+
+  // ---- tensor maps for the tcgen05 layers (batch-independent, see igemm_make_plan)
+  e->launches = 1;  // preprocess
+  for (LayerRt& L : e->layers) {
+    const ai4e_layer_desc& d = L.d;
+    e->launches += d.op == AI4E_OP_HEAD ? 3 : 1;
+    if (d.op != AI4E_OP_CONV || !L.igemm) continue;
+    int rc = igemm_make_plan(&L.plan, e->bufs[d.in_buf], max_batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
+                             (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
+                             d.res_buf >= 0 ? e->bufs[d.res_buf] : nullptr, d.relu, e->bufs[d.out_buf]);
+    if (rc) return fail(rc);
+  }
+
+  // ---- staging: images up to 1.5x the model input area (covers a 256 -> 224 resize+crop)
+  const size_t in_bytes = (size_t)desc->in_h * desc->in_w * desc->in_c;
+  size_t slot = in_bytes + in_bytes / 2;
+  if (const char* s = getenv("AI4E_B200_MAX_SRC_BYTES")) slot = std::max(in_bytes, (size_t)strtoull(s, nullptr, 10));
+  e->slot_bytes = (slot + 255) & ~(size_t)255;
+  int rc = alloc_ctx(e, e->sync_ctx);
+  if (rc) return fail(rc);
+  for (int i = 0; i < kNumCtx; ++i) {
+    rc = alloc_ctx(e, e->ctx[i]);
+    if (rc) return fail(rc);
+    e->free_q.push_back(&e->ctx[i]);
+  }
+  const int K = desc->num_classes;
+  e->r_idx.assign(kResultRing * AI4E_TOPK, 0);
+  e->r_prob.assign(kResultRing * AI4E_TOPK, 0.f);
+  e->r_logits.assign(kLogitRing * K, 0.f);
+  e->r_status.assign(kResultRing, 0);
+  e->r_submit.assign(kResultRing, Clock::now());
+  e->lat_ms.assign(kLatRing, 0.f);
+  e->batcher = std::thread(batcher_main, e);
+  e->completer = std::thread(completer_main, e);
+  *out = e;
+  return AI4E_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ai4e_engine_create(int device, const ai4e_model_desc* desc, const void* h_weights_blob, uint64_t blob_bytes,
+                       int max_batch, int max_wait_us, ai4e_engine** out) {
+  return engine_create(device, desc, h_weights_blob, blob_bytes, max_batch, max_wait_us, out);
+}
+
+int ai4e_engine_destroy(ai4e_engine* e) {
+  if (!e) return AI4E_OK;
+  cudaSetDevice(e->device);
+  {
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->stopping = true;
+    e->cv_work.notify_all();
+    e->cv_free.notify_all();
+  }
+  if (e->batcher.joinable()) e->batcher.join();
+  {
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->batcher_done = true;
+    e->cv_inflight.notify_all();
+  }
+  if (e->completer.joinable()) e->completer.join();
+  {
+    std::lock_guard<std::mutex> lk(e->mu);
+    e->cv_done.notify_all();
+  }
+  cudaDeviceSynchronize();
+  free_ctx(e->sync_ctx);
+  for (int i = 0; i < kNumCtx; ++i) free_ctx(e->ctx[i]);
+  for (void* b : e->bufs)
+    if (b) cudaFree(b);
+  if (e->d_pooled) cudaFree(e->d_pooled);
+  if (e->d_blob) cudaFree(e->d_blob);
+  if (e->ev_chain) cudaEventDestroy(e->ev_chain);
+  delete e;
+  return AI4E_OK;
+}
+
+int ai4e_engine_forward_host(ai4e_engine* e, const uint8_t* h_images, int batch, int src_h, int src_w,
+                             int32_t* h_top_idx, float* h_top_prob, float* h_logits_or_null) {
+  AI4E_REQUIRE(e && h_images && h_top_idx && h_top_prob, "forward_host: null pointer");
+  AI4E_REQUIRE(batch >= 1 && batch <= e->max_batch, "forward_host: batch %d outside [1, %d]", batch, e->max_batch);
+  AI4E_REQUIRE(src_h > 0 && src_w > 0, "forward_host: empty image");
+  const size_t img_bytes = (size_t)src_h * src_w * e->desc.in_c;
+  AI4E_REQUIRE(img_bytes <= e->slot_bytes, "forward_host: image of %zu bytes exceeds the staging slot (%zu)",
+               img_bytes, e->slot_bytes);
+  if (!e->healthy.load()) { set_last_error("engine on device %d is unhealthy after a CUDA error", e->device); return AI4E_ERR_STATE; }
+  AI4E_CUDA_TRY(cudaSetDevice(e->device));
+  std::lock_guard<std::mutex> lk(e->sync_mu);
+  BatchCtx& c = e->sync_ctx;
+  c.count = batch; c.src_h = src_h; c.src_w = src_w;
+  memcpy(c.h_in, h_images, img_bytes * batch);
+  int rc = launch_batch(e, c, h_logits_or_null != nullptr);
+  if (rc) return rc;
+  cudaError_t ce = cudaEventSynchronize(c.ev_done);
+  if (ce != cudaSuccess) {
+    e->healthy.store(0);
+    set_last_error("forward failed on device %d: %s", e->device, cudaGetErrorString(ce));
+    return AI4E_ERR_CUDA;
+  }
+  memcpy(h_top_idx, c.h_idx, (size_t)batch * AI4E_TOPK * sizeof(int32_t));
+  memcpy(h_top_prob, c.h_prob, (size_t)batch * AI4E_TOPK * sizeof(float));
+  if (h_logits_or_null) memcpy(h_logits_or_null, c.h_logits, (size_t)batch * e->desc.num_classes * sizeof(float));
+  {
+    std::lock_guard<std::mutex> lk2(e->mu);
+    account_batch(e, c);
+  }
+  return AI4E_OK;
+}
+
+int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
+                               int32_t* d_top_idx, float* d_top_prob, float* d_logits_or_null, void* stream) {
+  AI4E_REQUIRE(e && d_images && d_top_idx && d_top_prob, "forward_device: null pointer");
+  AI4E_REQUIRE(batch >= 1 && batch <= e->max_batch, "forward_device: batch %d outside [1, %d]", batch, e->max_batch);
+  if (!e->healthy.load()) { set_last_error("engine on device %d is unhealthy after a CUDA error", e->device); return AI4E_ERR_STATE; }
+  AI4E_CUDA_TRY(cudaSetDevice(e->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  std::lock_guard<std::mutex> lk(e->launch_mu);
+  if (e->chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(s, e->ev_chain, 0));
+  int rc = forward_enqueue(e, d_images, batch, src_h, src_w, d_top_idx, d_top_prob,
+                           d_logits_or_null ? d_logits_or_null : e->sync_ctx.d_logits, s);
+  if (rc) return rc;
+  AI4E_CUDA_TRY(cudaEventRecord(e->ev_chain, s));
+  e->chain_valid = true;
+  return AI4E_OK;
+}
+
+int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
+                       uint64_t* out_ticket) {
+  (void)tag;
+  AI4E_REQUIRE(e && h_hwc && out_ticket, "submit: null pointer");
+  AI4E_REQUIRE(c == e->desc.in_c, "submit: image has %d channels, model takes %d", c, e->desc.in_c);
+  AI4E_REQUIRE(h > 0 && w > 0, "submit: empty image");
+  if (row_stride <= 0) row_stride = w * c;
+  AI4E_REQUIRE(row_stride >= w * c, "submit: row stride too small");
+  const size_t img_bytes = (size_t)h * w * c;
+  AI4E_REQUIRE(img_bytes <= e->slot_bytes, "submit: image of %zu bytes exceeds the staging slot (%zu)", img_bytes,
+               e->slot_bytes);
+  BatchCtx* ctx = nullptr;
+  int slot = 0;
+  {
+    std::unique_lock<std::mutex> lk(e->mu);
+    for (;;) {
+      if (e->stopping) { set_last_error("submit: engine is shutting down"); return AI4E_ERR_STATE; }
+      if (!e->healthy.load()) { set_last_error("submit: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
+      if (!e->open_ctx) {
+        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
+        e->open_ctx = e->free_q.front();
+        e->free_q.pop_front();
+        e->open_ctx->count = 0;
+        e->open_ctx->copied.store(0);
+      }
+      ctx = e->open_ctx;
+      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w)) {  // a batch holds one image size
+        e->closed_q.push_back(ctx);
+        e->open_ctx = nullptr;
+        e->cv_work.notify_one();
+        continue;
+      }
+      break;
+    }
+    if (ctx->count == 0) {
+      ctx->src_h = h; ctx->src_w = w;
+      ctx->t_first = Clock::now();
+      ctx->first_ticket = e->next_ticket;
+    }
+    slot = ctx->count++;
+    *out_ticket = e->next_ticket++;
+    e->r_submit[*out_ticket % kResultRing] = Clock::now();
+    e->r_status[*out_ticket % kResultRing] = 1;  // pending
+    if (ctx->count == e->max_batch) {
+      e->closed_q.push_back(ctx);
+      e->open_ctx = nullptr;
+    }
+    e->cv_work.notify_one();
+  }
+  uint8_t* dst = ctx->h_in + (size_t)slot * img_bytes;
+  if (row_stride == w * c) {
+    memcpy(dst, h_hwc, img_bytes);
+  } else {
+    for (int y = 0; y < h; ++y) memcpy(dst + (size_t)y * w * c, h_hwc + (size_t)y * row_stride, (size_t)w * c);
+  }
+  ctx->copied.fetch_add(1, std::memory_order_release);
+  return AI4E_OK;
+}
+
+int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {
+  AI4E_REQUIRE(e && top_idx5 && top_prob5, "wait: null pointer");
+  std::unique_lock<std::mutex> lk(e->mu);
+  AI4E_REQUIRE(ticket < e->next_ticket, "wait: unknown ticket %llu", (unsigned long long)ticket);
+  e->cv_done.wait(lk, [&] { return e->done_upto > ticket || e->completer_done; });
+  if (e->done_upto <= ticket) { set_last_error("wait: engine shut down before ticket completed"); return AI4E_ERR_STATE; }
+  AI4E_REQUIRE(e->next_ticket - ticket <= kResultRing, "wait: result of ticket %llu has been overwritten",
+               (unsigned long long)ticket);
+  const uint64_t r = ticket % kResultRing;
+  const int rc = e->r_status[r];
+  if (rc != AI4E_OK) { set_last_error("wait: the batch of ticket %llu failed (%d)", (unsigned long long)ticket, rc); return rc < 0 ? rc : AI4E_ERR_STATE; }
+  memcpy(top_idx5, &e->r_idx[r * AI4E_TOPK], AI4E_TOPK * sizeof(int32_t));
+  memcpy(top_prob5, &e->r_prob[r * AI4E_TOPK], AI4E_TOPK * sizeof(float));
+  if (logits_or_null) {
+    AI4E_REQUIRE(e->next_ticket - ticket <= kLogitRing, "wait: logits of ticket %llu have been overwritten",
+                 (unsigned long long)ticket);
+    const int K = e->desc.num_classes;
+    memcpy(logits_or_null, &e->r_logits[(ticket % kLogitRing) * K], K * sizeof(float));
+  }
+  return AI4E_OK;
+}
+
+int ai4e_engine_flush(ai4e_engine* e) {
+  AI4E_REQUIRE(e, "flush: null engine");
+  std::unique_lock<std::mutex> lk(e->mu);
+  const uint64_t target = e->next_ticket;
+  e->flush_req = true;
+  e->cv_work.notify_all();
+  e->cv_done.wait(lk, [&] { return e->done_upto >= target || e->completer_done; });
+  return AI4E_OK;
+}
+
+int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out) {
+  AI4E_REQUIRE(e && out, "stats: null pointer");
+  std::lock_guard<std::mutex> lk(e->mu);
+  *out = e->st;
+  out->queue_depth = e->next_ticket - e->done_upto;
+  out->healthy = e->healthy.load();
+  out->launches_per_forward = e->launches;
+  const uint64_t n = std::min<uint64_t>(e->lat_n, kLatRing);
+  if (n) {
+    std::vector<float> v(e->lat_ms.begin(), e->lat_ms.begin() + n);
+    std::sort(v.begin(), v.end());
+    out->lat_ms_p50 = v[(size_t)((n - 1) * 0.50)];
+    out->lat_ms_p99 = v[(size_t)((n - 1) * 0.99)];
+  }
+  return AI4E_OK;
+}
+
+int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t bytes) {
+  AI4E_REQUIRE(e && h_dst, "read_activation: null pointer");
+  AI4E_REQUIRE(buf >= 0 && buf < (int)e->bufs.size() && e->bufs[buf], "read_activation: no slot %d", buf);
+  AI4E_REQUIRE(bytes <= e->buf_elems_per_image[buf] * 2 * (uint64_t)e->max_batch, "read_activation: too many bytes");
+  AI4E_CUDA_TRY(cudaSetDevice(e->device));
+  AI4E_CUDA_TRY(cudaDeviceSynchronize());
+  AI4E_CUDA_TRY(cudaMemcpy(h_dst, e->bufs[buf], bytes, cudaMemcpyDeviceToHost));
+  return AI4E_OK;
+}
+
+// ---------------------------------------------------------------------------------------- pool
+struct ai4e_pool {
+  std::vector<ai4e_engine*> engines;
+  std::atomic<uint64_t> rr{0};
+};
+
+int ai4e_pool_create(const int* devices, int n_devices, const ai4e_model_desc* desc, const void* h_weights_blob,
+                     uint64_t blob_bytes, int max_batch, int max_wait_us, ai4e_pool** out) {
+  AI4E_REQUIRE(devices && n_devices >= 1 && n_devices <= 64 && out, "pool_create: bad arguments");
+  ai4e_pool* p = new ai4e_pool();
+  for (int i = 0; i < n_devices; ++i) {
+    ai4e_engine* e = nullptr;
+    int rc = ai4e_engine_create(devices[i], desc, h_weights_blob, blob_bytes, max_batch, max_wait_us, &e);
+    if (rc) { ai4e_pool_destroy(p); return rc; }
+    p->engines.push_back(e);
+  }
+  *out = p;
+  return AI4E_OK;
+}
+
+int ai4e_pool_destroy(ai4e_pool* p) {
+  if (!p) return AI4E_OK;
+  for (ai4e_engine* e : p->engines) ai4e_engine_destroy(e);
+  delete p;
+  return AI4E_OK;
+}
+
+// ticket = replica index in the top byte | replica-local ticket.  Routing: the healthy replica
+// with the shortest queue, round-robin among equals (the reference: Istio ROUND_ROBIN).
+int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
+                     uint64_t* out_ticket) {
+  AI4E_REQUIRE(p && out_ticket, "pool_submit: null pointer");
+  const size_t n = p->engines.size();
+  const uint64_t start = p->rr.fetch_add(1);
+  int best = -1;
+  uint64_t best_depth = ~0ull;
+  for (size_t k = 0; k < n; ++k) {
+    const size_t i = (start + k) % n;
+    ai4e_engine* e = p->engines[i];
+    if (!e->healthy.load()) continue;
+    uint64_t depth;
+    {
+      std::lock_guard<std::mutex> lk(e->mu);
+      depth = e->next_ticket - e->done_upto;
+    }
+    if (depth < best_depth) { best_depth = depth; best = (int)i; }
+  }
+  if (best < 0) { set_last_error("pool_submit: no healthy replica"); return AI4E_ERR_STATE; }
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit(p->engines[best], h_hwc, h, w, c, row_stride, tag, &t);
+  if (rc) return rc;
+  *out_ticket = ((uint64_t)best << 56) | (t & ((1ull << 56) - 1));
+  return AI4E_OK;
+}
+
+int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {
+  AI4E_REQUIRE(p, "pool_wait: null pool");
+  const size_t i = ticket >> 56;
+  AI4E_REQUIRE(i < p->engines.size(), "pool_wait: bad ticket");
+  return ai4e_engine_wait(p->engines[i], ticket & ((1ull << 56) - 1), top_idx5, top_prob5, logits_or_null);
+}
+
+int ai4e_pool_flush(ai4e_pool* p) {
+  AI4E_REQUIRE(p, "pool_flush: null pool");
+  for (ai4e_engine* e : p->engines) ai4e_engine_flush(e);
+  return AI4E_OK;
+}
+
+int ai4e_pool_size(ai4e_pool* p) { return p ? (int)p->engines.size() : 0; }
+
+int ai4e_pool_engine(ai4e_pool* p, int i, ai4e_engine** out) {
+  AI4E_REQUIRE(p && out && i >= 0 && i < (int)p->engines.size(), "pool_engine: bad index");
+  *out = p->engines[i];
+  return AI4E_OK;
+}
+
+}  // extern "C"

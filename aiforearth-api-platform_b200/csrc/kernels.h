@@ -35,18 +35,19 @@ struct IgemmParams {
 };
 
 struct IgemmPlan {
-  CUtensorMap tmap_a, tmap_b;
-  IgemmParams prm;
-  int block_n;
-  int grid;
+  CUtensorMap tmap_a;     // im2col-mode map over the input activations (N = max_batch)
+  CUtensorMap tmap_b[3];  // weight tiles for BLOCK_N = 64 / 128 / 256
+  bool has_bn[3];
+  IgemmParams prm;        // everything but the batch-dependent fields
+  int max_batch;
 };
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
 int igemm_pick_block_n(int Cout, long long M);
 int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
-                    int pad, const void* residual, int relu, void* out, int force_block_n);
-int igemm_launch(const IgemmPlan& plan, cudaStream_t stream);
+                    int pad, const void* residual, int relu, void* out);
+int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream_t stream);
 
 // ---- K3 / K5 (pool_head.cu)
 int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,

@@ -1,0 +1,170 @@
+"""GPU parity tests of the whole classify path (preprocess -> ResNet -> top-5) through the
+C ABI (`ai4e_engine_*`), against the CPU oracle and the committed goldens.
+
+Tolerances (north_star: identical top-5; logits within 1e-2 abs / 1e-3 rel):
+  * against `forward_bf16_emul` — the CPU restatement of what a bf16-storage engine
+    computes — every logit must satisfy |d| <= 1e-2 + 1e-3|ref|;
+  * against the fp32 torchvision forward, top-5 must be IDENTICAL on the golden images
+    (chosen with top-6 margins > 0.022), and logits may differ by the error of the bf16
+    storage format itself, which the goldens record (`fmt_err_max`, about 1.5e-2 on
+    ResNet-50): asserted as max |d| <= 2.5e-2 with at most 0.5% of logits outside the
+    north_star tolerance.  DESIGN.md "Parity" explains why the format error is what it is.
+"""
+import threading
+
+import numpy as np
+import pytest
+
+from oracle import preprocess_oracle as pp
+from oracle import resnet_oracle as ro
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _engine(arch, in_ch=3, hw=224, max_batch=32, keep_stages=False, max_wait_us=2000):
+    from ai4e_b200.engine import Engine
+    return Engine(util.program_for(arch, in_ch, hw, keep_stages), device=0, max_batch=max_batch,
+                  max_wait_us=max_wait_us)
+
+
+def _check_against_golden(g, idx, prob, logits):
+    ref = g["logits_fp32"]
+    emul = g["logits_bf16_emul"]
+    # (1) the restated bf16 algorithm: north_star tolerance, every logit
+    ok = util.within_north_star(logits, emul)
+    assert ok.all(), f"{(~ok).sum()} logits outside 1e-2/1e-3 of the bf16 oracle; max {np.abs(logits - emul).max():.4f}"
+    # (2) the fp32 reference: identical top-5, logits within the format error
+    assert np.array_equal(idx, g["top5_idx"]), "top-5 differs from the fp32 reference"
+    d = np.abs(logits - ref)
+    assert d.max() <= 2.5e-2, d.max()
+    assert (~util.within_north_star(logits, ref)).mean() <= 5e-3
+    assert np.allclose(prob, g["top5_prob"], atol=2e-4, rtol=3e-2)
+
+
+@pytest.mark.parametrize("name", ["resnet18", "resnet50"])
+def test_forward_host_matches_golden(name):
+    g, imgs = util.load_golden(name)
+    with _engine(str(g["arch"])) as e:
+        idx, prob, logits = e.forward(imgs, want_logits=True)
+        _check_against_golden(g, idx, prob, logits)
+        assert e.stats()["healthy"] and e.stats()["images"] == len(imgs)
+
+
+def test_landcover_4band_matches_golden():
+    g, imgs = util.load_golden("resnet50_landcover4")
+    with _engine("resnet50", in_ch=4, hw=256, max_batch=8) as e:
+        idx, prob, logits = e.forward(imgs, want_logits=True)
+        _check_against_golden(g, idx, prob, logits)
+
+
+def test_stages_match_bf16_oracle():
+    """every stage output against the bf16-emulated CPU forward (localises a wrong layer)."""
+    arch = "resnet50"
+    m = util.oracle_model(arch)
+    imgs = ro.synthetic_images(4, seed=77)
+    x = pp.preprocess_nchw(imgs, ro.IMAGENET_MEAN, ro.IMAGENET_STD)
+    _, stages = ro.forward_bf16_emul(m, x, return_stages=True)
+    with _engine(arch, keep_stages=True, max_batch=4) as e:
+        e.forward(imgs)
+        for name in ["stem", "pool", "layer1", "layer2", "layer3", "layer4"]:
+            got = pp.bf16_to_f32(e.read_stage(name, 4)).transpose(0, 3, 1, 2)
+            want = stages[name]
+            # Summation order differs from the CPU's, so a result that sits on a bf16 rounding
+            # boundary may round the other way (1 ulp = 2^-8 relative), and later layers see that
+            # flip.  Bound: relative L2 error of the stage <= 3e-3 (every element off by half an
+            # ulp would be 2e-3), no element off by more than 4 ulp of the stage's largest value.
+            err = np.abs(got - want)
+            rel_l2 = np.sqrt((err.astype(np.float64) ** 2).sum() / (want.astype(np.float64) ** 2).sum())
+            assert rel_l2 < 3e-3, f"{name}: relative L2 error {rel_l2:.5f}"
+            assert err.max() <= 2.0 ** -6 * np.abs(want).max(), f"{name}: max err {err.max():.4f}"
+
+
+def test_microbatch_threads_match_sync_forward():
+    g, imgs = util.load_golden("resnet18")
+    with _engine("resnet18", max_batch=8, max_wait_us=500) as e:
+        want_idx, want_prob, want_logits = e.forward(imgs[:8], want_logits=True)
+        n_threads, per = 6, 10
+        res = {}
+
+        def worker(t):
+            for j in range(per):
+                k = (t * per + j) % 8
+                res[(t, j)] = (k, e.classify(imgs[k], want_logits=True))
+
+        th = [threading.Thread(target=worker, args=(t,)) for t in range(n_threads)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        assert len(res) == n_threads * per
+        for k, (idx, prob, logits) in res.values():
+            assert np.array_equal(idx, want_idx[k])
+            # the same image in a batch of a different size may run with a different tile shape
+            assert np.abs(logits - want_logits[k]).max() <= 2e-3
+        st = e.stats()
+        assert st["images"] == 8 + n_threads * per and st["queue_depth"] == 0
+        assert st["lat_ms_p99"] >= st["lat_ms_p50"] > 0
+
+
+def test_submit_order_and_flush():
+    g, imgs = util.load_golden("resnet18")
+    with _engine("resnet18", max_batch=16, max_wait_us=200000) as e:  # long wait: flush must close the batch
+        tickets = [e.submit(imgs[i]) for i in range(5)]
+        e.flush()
+        assert e.stats()["queue_depth"] == 0
+        for i, t in enumerate(tickets):
+            idx, _ = e.wait(t)
+            assert np.array_equal(idx, g["top5_idx"][i])
+
+
+def test_resize_path_matches_oracle():
+    """256x256 payloads are bilinearly resized + centre-cropped to 224 inside K1."""
+    arch = "resnet18"
+    m = util.oracle_model(arch)
+    imgs = ro.synthetic_images(6, 256, 256, 3, seed=31)
+    x = pp.preprocess_resize_crop_nchw(imgs, 224, 224, 224, 224, ro.IMAGENET_MEAN, ro.IMAGENET_STD)
+    emul = ro.forward_bf16_emul(m, x)
+    with _engine(arch, max_batch=8) as e:
+        idx, prob, logits = e.forward(imgs, want_logits=True)
+        assert util.within_north_star(logits, emul).all(), np.abs(logits - emul).max()
+        t = [e.submit(im) for im in imgs]
+        for i, tk in enumerate(t):
+            i2, _, l2 = e.wait(tk, want_logits=True)
+            assert np.abs(l2 - logits[i]).max() <= 2e-3
+
+
+def test_strided_chip_submit():
+    """land-cover style: chips are views into a big tile (row stride > w*c)."""
+    g, imgs = util.load_golden("resnet50_landcover4")
+    tile = np.zeros((512, 512, 4), np.uint8)
+    tile[:256, 256:] = imgs[0]
+    tile[256:, :256] = imgs[1]
+    with _engine("resnet50", in_ch=4, hw=256, max_batch=4) as e:
+        t0 = e.submit(tile[:256, 256:])
+        t1 = e.submit(tile[256:, :256])
+        assert np.array_equal(e.wait(t0)[0], g["top5_idx"][0])
+        assert np.array_equal(e.wait(t1)[0], g["top5_idx"][1])
+
+
+def test_engine_rejects_bad_input():
+    from ai4e_b200 import Ai4eError
+    with _engine("resnet18", max_batch=4) as e:
+        with pytest.raises(ValueError):
+            e.forward(np.zeros((1, 224, 224, 4), np.uint8))
+        with pytest.raises(Ai4eError):
+            e.forward(np.zeros((5, 224, 224, 3), np.uint8))  # > max_batch
+        with pytest.raises(Ai4eError):
+            e.submit(np.zeros((1024, 1024, 3), np.uint8))  # larger than the staging slot
+        with pytest.raises(Ai4eError):
+            e.wait(12345)  # unknown ticket
+
+
+def test_pool_two_replicas_one_gpu():
+    """the dispatcher over two replicas (both on GPU 0 here; one per GPU in production)."""
+    from ai4e_b200.engine import Pool
+    g, imgs = util.load_golden("resnet18")
+    with Pool(util.program_for("resnet18"), devices=[0, 0], max_batch=4, max_wait_us=300) as p:
+        tickets = [p.submit(imgs[i % 8]) for i in range(24)]
+        for i, t in enumerate(tickets):
+            assert np.array_equal(p.wait(t)[0], g["top5_idx"][i % 8])
+        per = [s["images"] for s in p.stats()]
+        assert sum(per) == 24 and all(v > 0 for v in per), per
