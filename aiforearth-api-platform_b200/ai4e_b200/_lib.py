@@ -68,6 +68,8 @@ SIGNATURES = {
     "ai4e_engine_forward_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "ai4e_engine_forward_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "ai4e_engine_submit": (_i, [_vp, _vp, _i, _i, _i, _i, _u64, _u64p]),
+    "ai4e_engine_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
+    "ai4e_engine_profile": (_i, [_vp, _vp, _i, _i, _i, _i, _fp, _i]),
     "ai4e_engine_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),
     "ai4e_engine_flush": (_i, [_vp]),
     "ai4e_engine_stats_get": (_i, [_vp, C.POINTER(EngineStats)]),

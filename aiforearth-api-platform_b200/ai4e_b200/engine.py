@@ -91,6 +91,25 @@ class Engine(_Base):
                                              a.strides[0], tag, C.byref(t)))
         return t.value
 
+    def submit_batch(self, images_u8: np.ndarray) -> range:
+        """dense [B,H,W,C] uint8 host array -> tickets (a range).  Page-locked arrays are read in
+        place by the H2D copy: keep them unchanged until the last ticket has been waited for."""
+        a = images_u8
+        if a.dtype != np.uint8 or a.ndim != 4 or not a.flags.c_contiguous:
+            raise ValueError("expected a C-contiguous uint8 [B,H,W,C] array")
+        t = C.c_uint64()
+        L.check(self._lib.ai4e_engine_submit_batch(self._h, a.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1],
+                                                   a.shape[2], a.shape[3], C.byref(t)))
+        return range(t.value, t.value + a.shape[0])
+
+    def profile_layers(self, d_images, batch: int, h: int, w: int, reps: int = 5) -> np.ndarray:
+        """mean device ms of [preprocess, layer 0, layer 1, ...] on a device-resident batch."""
+        n = len(self.program.layers) + 1
+        out = np.zeros(n, np.float32)
+        L.check(self._lib.ai4e_engine_profile(self._h, C.c_void_p(d_images.data_ptr()), batch, h, w, reps,
+                                              out.ctypes.data_as(C.POINTER(C.c_float)), n))
+        return out
+
     def wait(self, ticket: int, want_logits: bool = False):
         idx, prob = self._results(1)
         logits = np.empty((self.num_classes,), np.float32) if want_logits else None

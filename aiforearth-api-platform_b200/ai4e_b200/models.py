@@ -228,3 +228,48 @@ def build_resnet_program(arch: str, state_dict: dict, in_h: int = 224, in_w: int
                              blob.add(fc_b.numpy().astype(np.float32)), "fc"))
     prog.blob = blob.bytes()
     return prog
+
+
+def synthetic_state_dict(arch: str, seed: int = 0, in_c: int = 3, num_classes: int = 1000,
+                         residual_gain: float = 0.1) -> dict:
+    """Seeded random weights with torchvision's parameter names and shapes (no checkpoints can be
+    downloaded offline).  Enough for throughput runs and smoke tests: kernel time does not depend
+    on the values.  Kaiming-normal convolutions, BN weight ~ U(0.5,1.5) (x residual_gain on the
+    last BN of a block), bias ~ N(0,0.1), running_mean ~ N(0,0.1), running_var ~ U(0.5,1.5)."""
+    kind, counts = ARCH_BLOCKS[arch]
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+
+    def conv(name, cout, cin, k):
+        std = (2.0 / (cout * k * k)) ** 0.5
+        sd[name + ".weight"] = torch.randn((cout, cin, k, k), generator=g) * std
+
+    def bn(name, c, gain=1.0):
+        sd[name + ".weight"] = (torch.rand(c, generator=g) + 0.5) * gain
+        sd[name + ".bias"] = torch.randn(c, generator=g) * 0.1
+        sd[name + ".running_mean"] = torch.randn(c, generator=g) * 0.1
+        sd[name + ".running_var"] = torch.rand(c, generator=g) + 0.5
+
+    conv("conv1", 64, in_c, 7)
+    bn("bn1", 64)
+    exp = 4 if kind == "bottleneck" else 1
+    cin = 64
+    for li, n_blocks in enumerate(counts):
+        width = 64 * 2 ** li
+        for bi in range(n_blocks):
+            pre = f"layer{li + 1}.{bi}"
+            stride = 2 if (li > 0 and bi == 0) else 1
+            if kind == "bottleneck":
+                conv(pre + ".conv1", width, cin, 1); bn(pre + ".bn1", width)
+                conv(pre + ".conv2", width, width, 3); bn(pre + ".bn2", width)
+                conv(pre + ".conv3", width * 4, width, 1); bn(pre + ".bn3", width * 4, residual_gain)
+            else:
+                conv(pre + ".conv1", width, cin, 3); bn(pre + ".bn1", width)
+                conv(pre + ".conv2", width, width, 3); bn(pre + ".bn2", width, residual_gain)
+            if stride != 1 or cin != width * exp:
+                conv(pre + ".downsample.0", width * exp, cin, 1); bn(pre + ".downsample.1", width * exp)
+            cin = width * exp
+    bound = 1.0 / cin ** 0.5
+    sd["fc.weight"] = (torch.rand((num_classes, cin), generator=g) * 2 - 1) * bound
+    sd["fc.bias"] = (torch.rand(num_classes, generator=g) * 2 - 1) * bound
+    return sd

@@ -56,6 +56,7 @@ struct BatchCtx {
   std::atomic<int> copied{0};
   Clock::time_point t_first;
   int launch_rc = 0;
+  const uint8_t* ext_src = nullptr;  // zero-copy source (page-locked caller memory), else h_in
 };
 
 }  // namespace
@@ -143,13 +144,17 @@ void free_ctx(BatchCtx& c) {
 
 // preprocess + every layer, enqueued on `stream`.  Caller holds e->launch_mu.
 int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
-                    int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream) {
+                    int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream,
+                    cudaEvent_t* marks = nullptr) {
   const ai4e_model_desc& m = e->desc;
+  int mark = 0;
+  if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   const bool resize = src_h != m.in_h || src_w != m.in_w;
   int rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, 0, resize ? m.in_h : 0,
                              resize ? m.in_w : 0, m.in_h, m.in_w, m.mean, m.std, AI4E_LAYOUT_NHWC,
                              m.in_c_pad, e->bufs[0], stream);
   if (rc < 0) return rc;
+  if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   for (LayerRt& L : e->layers) {
     const ai4e_layer_desc& d = L.d;
     if (d.op == AI4E_OP_CONV) {
@@ -170,6 +175,7 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
                        AI4E_TOPK, stream);
     }
     if (rc) return rc;
+    if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   }
   return AI4E_OK;
 }
@@ -178,7 +184,8 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
 int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
   const int K = e->desc.num_classes;
   const size_t img_bytes = (size_t)c.src_h * c.src_w * e->desc.in_c;
-  AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, c.h_in, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+  const uint8_t* h_src = c.ext_src ? c.ext_src : c.h_in;  // ext_src: caller's page-locked buffer
+  AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
   {
     std::lock_guard<std::mutex> lk(e->launch_mu);
     if (e->chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(c.stream, e->ev_chain, 0));
@@ -198,6 +205,15 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
                                   cudaMemcpyDeviceToHost, c.stream));
   AI4E_CUDA_TRY(cudaEventRecord(c.ev_done, c.stream));
   return AI4E_OK;
+}
+
+bool is_page_locked(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
 }
 
 void account_batch(ai4e_engine* e, BatchCtx& c) {  // caller holds e->mu
@@ -290,6 +306,7 @@ void completer_main(ai4e_engine* e) {
     if (rc == AI4E_OK) account_batch(e, *c);
     e->done_upto = c->first_ticket + c->count;
     c->count = 0;
+    c->ext_src = nullptr;
     c->copied.store(0);
     e->free_q.push_back(c);
     e->cv_free.notify_all();
@@ -501,7 +518,8 @@ int ai4e_engine_forward_host(ai4e_engine* e, const uint8_t* h_images, int batch,
   std::lock_guard<std::mutex> lk(e->sync_mu);
   BatchCtx& c = e->sync_ctx;
   c.count = batch; c.src_h = src_h; c.src_w = src_w;
-  memcpy(c.h_in, h_images, img_bytes * batch);
+  c.ext_src = is_page_locked(h_images) ? h_images : nullptr;  // page-locked input: H2D straight from it
+  if (!c.ext_src) memcpy(c.h_in, h_images, img_bytes * batch);
   int rc = launch_batch(e, c, h_logits_or_null != nullptr);
   if (rc) return rc;
   cudaError_t ce = cudaEventSynchronize(c.ev_done);
@@ -593,6 +611,94 @@ int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c
     for (int y = 0; y < h; ++y) memcpy(dst + (size_t)y * w * c, h_hwc + (size_t)y * row_stride, (size_t)w * c);
   }
   ctx->copied.fetch_add(1, std::memory_order_release);
+  return AI4E_OK;
+}
+
+int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count, int h, int w, int c,
+                             uint64_t* out_first_ticket) {
+  AI4E_REQUIRE(e && h_images && out_first_ticket, "submit_batch: null pointer");
+  AI4E_REQUIRE(c == e->desc.in_c, "submit_batch: images have %d channels, model takes %d", c, e->desc.in_c);
+  AI4E_REQUIRE(count >= 1 && count <= e->max_batch, "submit_batch: count %d outside [1, %d]", count, e->max_batch);
+  AI4E_REQUIRE(h > 0 && w > 0, "submit_batch: empty image");
+  const size_t img_bytes = (size_t)h * w * c;
+  AI4E_REQUIRE(img_bytes <= e->slot_bytes, "submit_batch: image of %zu bytes exceeds the staging slot (%zu)",
+               img_bytes, e->slot_bytes);
+  const bool pinned = is_page_locked(h_images);
+  BatchCtx* ctx = nullptr;
+  {
+    std::unique_lock<std::mutex> lk(e->mu);
+    for (;;) {
+      if (e->stopping) { set_last_error("submit_batch: engine is shutting down"); return AI4E_ERR_STATE; }
+      if (!e->healthy.load()) { set_last_error("submit_batch: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
+      if (e->open_ctx && e->open_ctx->count > 0) {  // a caller-made batch is never mixed with singles
+        e->closed_q.push_back(e->open_ctx);
+        e->open_ctx = nullptr;
+        e->cv_work.notify_one();
+      }
+      if (!e->open_ctx) {
+        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
+        e->open_ctx = e->free_q.front();
+        e->free_q.pop_front();
+      }
+      break;
+    }
+    ctx = e->open_ctx;
+    e->open_ctx = nullptr;
+    ctx->count = count; ctx->src_h = h; ctx->src_w = w;
+    ctx->t_first = Clock::now();
+    ctx->first_ticket = e->next_ticket;
+    ctx->ext_src = pinned ? h_images : nullptr;
+    ctx->copied.store(pinned ? count : 0);
+    *out_first_ticket = e->next_ticket;
+    for (int i = 0; i < count; ++i) {
+      const uint64_t r = (e->next_ticket + i) % kResultRing;
+      e->r_submit[r] = ctx->t_first;
+      e->r_status[r] = 1;
+    }
+    e->next_ticket += count;
+    e->closed_q.push_back(ctx);
+    e->cv_work.notify_one();
+  }
+  if (!pinned) {
+    memcpy(ctx->h_in, h_images, img_bytes * count);
+    ctx->copied.store(count, std::memory_order_release);
+  }
+  return AI4E_OK;
+}
+
+int ai4e_engine_profile(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w, int reps,
+                        float* h_ms_out, int n_out) {
+  AI4E_REQUIRE(e && d_images && h_ms_out, "profile: null pointer");
+  AI4E_REQUIRE(batch >= 1 && batch <= e->max_batch && reps >= 1, "profile: bad batch/reps");
+  const int n = (int)e->layers.size() + 1;  // preprocess + every layer
+  AI4E_REQUIRE(n_out >= n, "profile: need room for %d timings", n);
+  AI4E_CUDA_TRY(cudaSetDevice(e->device));
+  std::vector<cudaEvent_t> ev(n + 1);
+  for (auto& x : ev) AI4E_CUDA_TRY(cudaEventCreate(&x));
+  std::vector<double> acc(n, 0.0);
+  std::lock_guard<std::mutex> lk0(e->sync_mu);
+  BatchCtx& c = e->sync_ctx;
+  int rc = AI4E_OK;
+  for (int r = 0; r < reps && rc == AI4E_OK; ++r) {
+    {
+      std::lock_guard<std::mutex> lk(e->launch_mu);
+      if (e->chain_valid) cudaStreamWaitEvent(c.stream, e->ev_chain, 0);
+      rc = forward_enqueue(e, d_images, batch, src_h, src_w, c.d_idx, c.d_prob, c.d_logits, c.stream, ev.data());
+      cudaEventRecord(e->ev_chain, c.stream);
+      e->chain_valid = true;
+    }
+    if (rc) break;
+    cudaError_t ce = cudaStreamSynchronize(c.stream);
+    if (ce != cudaSuccess) { set_last_error("profile: %s", cudaGetErrorString(ce)); rc = AI4E_ERR_CUDA; break; }
+    for (int i = 0; i < n; ++i) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, ev[i], ev[i + 1]);
+      acc[i] += ms;
+    }
+  }
+  for (auto& x : ev) cudaEventDestroy(x);
+  if (rc) return rc;
+  for (int i = 0; i < n; ++i) h_ms_out[i] = (float)(acc[i] / reps);
   return AI4E_OK;
 }
 

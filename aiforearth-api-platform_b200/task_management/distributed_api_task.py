@@ -1,0 +1,120 @@
+"""Client of the platform's two cache-connector functions - same class, methods, payloads and
+sentinel results as the reference's `DistributedApiTaskManager`
+(/root/reference/APIs/1.0/Common/task_management/distributed_api_task.py:12-116).
+
+Differences, all on the transport and none on the contract:
+  * the reference opens a new aiohttp session and a new event loop for every call (:18,37,
+    79-80,103-104); this client keeps one pooled `requests.Session` per thread;
+  * when no CACHE_CONNECTOR_*_URI is configured, or AI4E_TASK_STORE=local, calls go to the
+    in-process `LocalTaskStore` (the control plane is out of scope and is exercised in-process);
+  * the error branches that raise NameError/AttributeError upstream (:50,94) return the
+    documented sentinel dicts instead.
+"""
+from __future__ import annotations
+
+import datetime
+import json
+import threading
+from os import getenv
+from urllib.parse import urlparse
+
+from task_management.local_task_store import LocalTaskStore, default_store
+
+_NOT_FOUND = '{{"TaskId": "{0}", "Status": "not found"}}'
+_ERROR = '{"TaskId": "-1", "Status": "error"}'
+
+
+class DistributedApiTaskManager:
+    def __init__(self, store: LocalTaskStore | None = None):
+        self.cache_connector_upsert_url = getenv('CACHE_CONNECTOR_UPSERT_URI')
+        self.cache_connector_get_url = getenv('CACHE_CONNECTOR_GET_URI')
+        use_local = store is not None or getenv('AI4E_TASK_STORE', '').lower() == 'local' or not (
+            self.cache_connector_upsert_url and self.cache_connector_get_url)
+        self.store = (store or default_store()) if use_local else None
+        self._tls = threading.local()
+
+    # ---- transport
+    def _session(self):
+        s = getattr(self._tls, "session", None)
+        if s is None:
+            import requests
+            s = requests.Session()
+            self._tls.session = s
+        return s
+
+    def _post(self, payload):
+        body = json.dumps(payload) if payload is not None else None
+        if self.store is not None:
+            return self.store.upsert(body)
+        try:
+            r = self._session().post(self.cache_connector_upsert_url, data=body,
+                                     headers={"Content-Type": "application/json"}, timeout=30)
+            return r.status_code, r.text
+        except Exception as e:  # noqa: BLE001
+            print("task store POST failed: " + str(e))
+            return 599, ""
+
+    def _get(self, task_id):
+        if self.store is not None:
+            return self.store.get(task_id)
+        try:
+            r = self._session().get(self.cache_connector_get_url, params={'taskId': task_id}, timeout=30)
+            return r.status_code, r.text
+        except Exception as e:  # noqa: BLE001
+            print("task store GET failed: " + str(e))
+            return 599, ""
+
+    @staticmethod
+    def _now():
+        return datetime.datetime.strftime(datetime.datetime.now(), "%Y-%m-%d %H:%M:%S")
+
+    # ---- the reference's public methods
+    def AddTask(self):
+        code, text = self._post(None)  # an empty body: the platform answers 400 -> the error sentinel
+        return json.loads(text if code == 200 else _ERROR)
+
+    def _UpdateTaskStatus(self, taskId, status, backendStatus):
+        old_stat = self.GetTaskStatus(taskId)
+        endpoint = 'http://localhost'
+        if not old_stat.get('Endpoint'):
+            print("Cannot find task status. Creating")
+        else:
+            endpoint = old_stat['Endpoint']
+        code, text = self._post({'TaskId': taskId, 'Timestamp': self._now(), 'Status': status,
+                                 'BackendStatus': backendStatus, 'Endpoint': endpoint, 'PublishToGrid': False})
+        if code != 200:
+            print("status code: " + str(code))
+            return json.loads(_NOT_FOUND.format(taskId))
+        return json.loads(text)
+
+    def CompleteTask(self, taskId, status):
+        return self._UpdateTaskStatus(taskId, status, 'completed')
+
+    def UpdateTaskStatus(self, taskId, status):
+        return self._UpdateTaskStatus(taskId, status, 'running')
+
+    def FailTask(self, taskId, status):
+        return self._UpdateTaskStatus(taskId, status, 'failed')
+
+    def AddPipelineTask(self, taskId, organization_moniker, version, api_name, body):
+        old_stat = self.GetTaskStatus(taskId)
+        if old_stat['Status'] == "not found":
+            print("Cannot find task status.")
+            return json.loads(_ERROR)
+        parsed_endpoint = urlparse(old_stat['Endpoint'])
+        path = '{}/{}/{}'.format(version, organization_moniker, api_name)
+        next_endpoint = '{}://{}/{}'.format(parsed_endpoint.scheme, parsed_endpoint.netloc, path)
+        print("Sending to next endpoint: " + next_endpoint)
+        code, text = self._post({'TaskId': taskId, 'Timestamp': self._now(), 'Status': 'created',
+                                 'BackendStatus': 'created', 'Endpoint': next_endpoint, 'Body': body,
+                                 'PublishToGrid': True})
+        if code != 200:
+            print("status code: " + str(code))
+            return json.loads(_NOT_FOUND.format(taskId))
+        return json.loads(text)
+
+    def GetTaskStatus(self, taskId):
+        code, text = self._get(taskId)
+        if code != 200:
+            return json.loads(_NOT_FOUND.format(taskId))
+        return json.loads(text)

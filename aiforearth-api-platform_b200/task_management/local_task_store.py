@@ -1,0 +1,118 @@
+"""In-process task store that honours the contract of the platform's cache-connector
+functions, so the hot path can be driven and benchmarked "in-process without network"
+(BASELINE.json north_star).  The Azure control plane itself is out of scope.
+
+Contract restated from the reference (citations relative to /root/reference):
+  * task JSON fields TaskId, Timestamp, Status, BackendStatus, Endpoint, Body, PublishToGrid
+    (ProcessManager/Classes/APITask.cs:12-18);
+  * upsert: an empty body is a 400 (CacheManager/CacheConnectorUpsert.cs:57-74); an empty
+    TaskId gets a new GUID (:92-100); Timestamp is overwritten with UTC now (:102); the stored
+    JSON has Body stripped (:119-127); the task id is added to the sorted set
+    "{EndpointPath}_{BackendStatus}" scored by epoch seconds (:130-133) and removed from the
+    previous state's set - running removes it from created, completed/failed from running
+    (:135-142); with PublishToGrid the original body is kept under "{TaskId}_ORIG" (:158) and a
+    later publish without body re-reads it (:175); the response is the stored JSON;
+  * get: 200 + JSON, or 204 when the id is unknown (CacheManager/CacheConnectorGet.cs:56-66).
+"""
+from __future__ import annotations
+
+import datetime
+import json
+import threading
+import time
+import uuid
+from urllib.parse import urlparse
+
+BACKEND_STATUSES = ("created", "running", "completed", "failed")
+ORIG_SUFFIX = "_ORIG"
+
+
+class LocalTaskStore:
+    def __init__(self, publisher=None):
+        self._lock = threading.Lock()
+        self.strings: dict[str, str] = {}
+        self.sorted_sets: dict[str, dict[str, int]] = {}
+        self.publisher = publisher  # callable(task_dict, body) -> bool, the "Event Grid / Service Bus" stand-in
+        self.upserts = 0
+        self.gets = 0
+
+    # ---- the two HTTP functions, as (status_code, text)
+    def upsert(self, body_text: str | None):
+        self.upserts += 1
+        if not body_text or not body_text.strip():
+            return 400, ""
+        try:
+            task = json.loads(body_text)
+        except ValueError:
+            return 400, ""
+        if not isinstance(task, dict) or not task.get("Endpoint") or not task.get("BackendStatus"):
+            return 400, ""
+        task_body = task.get("Body")
+        if not task.get("TaskId"):
+            task["TaskId"] = str(uuid.uuid4())
+        task["Timestamp"] = datetime.datetime.now(datetime.timezone.utc).strftime("%m/%d/%Y %H:%M:%S")
+        task["Body"] = None
+        task.setdefault("Status", None)
+        task.setdefault("PublishToGrid", False)
+        serialized = json.dumps(task)
+        path = urlparse(task["Endpoint"]).path
+        status = task["BackendStatus"]
+        tid = task["TaskId"]
+        now = int(time.time())
+        publish = bool(task.get("PublishToGrid"))
+        with self._lock:
+            self.strings[tid] = serialized
+            self.sorted_sets.setdefault(f"{path}_{status}", {})[tid] = now
+            if status == "running":
+                self.sorted_sets.get(f"{path}_created", {}).pop(tid, None)
+            elif status in ("completed", "failed"):
+                self.sorted_sets.get(f"{path}_running", {}).pop(tid, None)
+            if publish:
+                if task_body:
+                    self.strings[tid + ORIG_SUFFIX] = task_body if isinstance(task_body, str) else json.dumps(task_body)
+                else:
+                    task_body = self.strings.get(tid + ORIG_SUFFIX)
+        if publish and self.publisher is not None:
+            ok = False
+            try:
+                ok = bool(self.publisher(dict(task), task_body))
+            except Exception:  # noqa: BLE001 - a failed publish moves the task to failed, as upstream
+                ok = False
+            if not ok:
+                task["Status"] = "Failed - unable to send to backend service."
+                task["BackendStatus"] = "failed"
+                with self._lock:
+                    self.strings[tid] = json.dumps(task)
+                    self.sorted_sets.setdefault(f"{path}_failed", {})[tid] = now
+                    self.sorted_sets.get(f"{path}_created", {}).pop(tid, None)
+        return 200, serialized
+
+    def get(self, task_id: str):
+        self.gets += 1
+        with self._lock:
+            v = self.strings.get(task_id)
+        return (200, v) if v is not None else (204, "")
+
+    # ---- helpers for tests / the in-process platform
+    def create_task(self, endpoint: str, body: str = "", publish: bool = False) -> dict:
+        """what APIM's request policy does (APIManagement/request_policy.xml:5-21)."""
+        code, text = self.upsert(json.dumps({"TaskId": "", "Status": "created", "BackendStatus": "created",
+                                             "Endpoint": endpoint, "Body": body, "PublishToGrid": publish}))
+        assert code == 200
+        return json.loads(text)
+
+    def set_members(self, key: str):
+        with self._lock:
+            return dict(self.sorted_sets.get(key, {}))
+
+
+_default_store = None
+_default_lock = threading.Lock()
+
+
+def default_store() -> LocalTaskStore:
+    global _default_store
+    with _default_lock:
+        if _default_store is None:
+            _default_store = LocalTaskStore()
+        return _default_store

@@ -178,10 +178,24 @@ AI4E_API int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images,
  * per-task thread + per-image forward of ai4e_service.py:180-183,203. */
 AI4E_API int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride,
                        uint64_t tag, uint64_t* out_ticket);
+/* A caller-made batch (e.g. the 256 chips of a land-cover tile, or a dispatcher that already
+ * holds a full micro-batch): `count` dense images become one batch of their own, tickets
+ * first..first+count-1.  If h_images is page-locked (cudaHostAlloc / cudaHostRegister /
+ * torch pin_memory) the H2D copy reads it in place - keep it unchanged until the last ticket
+ * has been waited for; pageable memory is copied to the staging slot before returning. */
+AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count, int h, int w,
+                                      int c, uint64_t* out_first_ticket);
 AI4E_API int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                      float* logits_or_null);
 AI4E_API int ai4e_engine_flush(ai4e_engine* e);
 AI4E_API int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out);
+
+/* Measurement: runs `reps` forwards on a device-resident batch with a CUDA event between
+ * kernels and returns the mean device time (ms) of the preprocess kernel (entry 0) and of
+ * every layer of the program (entries 1..n_layers).  bench.py derives the per-kernel roofline
+ * from it.  No reference counterpart (the reference has no profile). */
+AI4E_API int ai4e_engine_profile(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
+                                 int reps, float* h_ms_out, int n_out);
 
 /* Debug/parity: copy activation slot `buf` of the last forward to the host (bf16 NHWC). */
 AI4E_API int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t bytes);
