@@ -1,13 +1,29 @@
-"""`TaskManager` - the facade user code and `APIService` call; same methods and delegation as
-the reference (/root/reference/APIs/1.0/base-py/task_management/api_task.py:8-38)."""
+"""`TaskManager`: the facade that `APIService` and user task functions call.
+
+Mirrors the public methods of the reference class
+(/root/reference/APIs/1.0/base-py/task_management/api_task.py:8-38): AddTask, CompleteTask,
+FailTask, UpdateTaskStatus, AddPipelineTask, GetTaskStatus, each answered by the
+distributed task client.  Tasks are created by the platform; a container only adopts the task
+whose id arrives in the `taskId` request header (reference :12-20).
+"""
+import logging
+
 from task_management.distributed_api_task import DistributedApiTaskManager
 
 try:
     from flask_restful import Resource
-except ImportError:  # build image has no flask_restful
+except ImportError:  # the build image has no flask_restful
     from ai4e_b200.compat.minirestful import Resource
 
-print("Creating API task manager.")
+_log = logging.getLogger("ai4e.task_manager")
+
+
+def _header_task_id(request):
+    """the platform-assigned task id carried by the request, or None."""
+    headers = getattr(request, "headers", None) if request else None
+    if headers is None or "taskId" not in headers:
+        return None
+    return headers.get("taskId")
 
 
 class TaskManager:
@@ -15,33 +31,35 @@ class TaskManager:
         self.distributed_api_task = DistributedApiTaskManager(store)
 
     def AddTask(self, request):
-        # the platform creates tasks; a request that carries a `taskId` header reuses that task
-        if not request or 'taskId' not in request.headers:
-            return self.distributed_api_task.AddTask()
-        return self.distributed_api_task.GetTaskStatus(request.headers.get('taskId'))
-
-    def CompleteTask(self, taskId, status):
-        print("Completing task: " + str(taskId) + " to:" + str(status))
-        return self.distributed_api_task.CompleteTask(taskId, status)
-
-    def FailTask(self, taskId, status):
-        self.distributed_api_task.FailTask(taskId, status)
-
-    def UpdateTaskStatus(self, taskId, status):
-        print("Updating task: " + str(taskId) + " to:" + str(status))
-        return self.distributed_api_task.UpdateTaskStatus(taskId, status)
-
-    def AddPipelineTask(self, taskId, organization_moniker, version, api_name, body):
-        print("Adding pipeline task: " + str(taskId))
-        return self.distributed_api_task.AddPipelineTask(taskId, organization_moniker, version, api_name, body)
+        task_id = _header_task_id(request)
+        backend = self.distributed_api_task
+        return backend.AddTask() if task_id is None else backend.GetTaskStatus(task_id)
 
     def GetTaskStatus(self, taskId):
         return self.distributed_api_task.GetTaskStatus(taskId)
 
+    def UpdateTaskStatus(self, taskId, status):
+        _log.debug("task %s -> running: %s", taskId, status)
+        return self.distributed_api_task.UpdateTaskStatus(taskId, status)
+
+    def CompleteTask(self, taskId, status):
+        _log.debug("task %s -> completed: %s", taskId, status)
+        return self.distributed_api_task.CompleteTask(taskId, status)
+
+    def FailTask(self, taskId, status):
+        _log.debug("task %s -> failed: %s", taskId, status)
+        self.distributed_api_task.FailTask(taskId, status)  # like upstream, returns nothing
+
+    def AddPipelineTask(self, taskId, organization_moniker, version, api_name, body):
+        _log.debug("task %s -> pipeline stage %s/%s/%s", taskId, version, organization_moniker, api_name)
+        return self.distributed_api_task.AddPipelineTask(taskId, organization_moniker, version, api_name, body)
+
 
 class Task(Resource):
+    """REST resource over the task client (the reference ships one here too, :40-46)."""
+
     def __init__(self, **kwargs):
-        self.distributed_api_task = kwargs['distributed_api_task']
+        self.distributed_api_task = kwargs["distributed_api_task"]
 
     def get(self, id):
         return self.distributed_api_task.GetTaskStatus(id)
