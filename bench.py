@@ -6,8 +6,8 @@
 
 Workload (BASELINE.json configs[1]): ResNet-50 bf16 classification, micro-batch 64, synthetic
 224x224 RGB, one replica per B200.  A "step" is one micro-batch of 64 images through
-preprocess -> 53 convolutions -> head.  Weights are the seeded synthetic ResNet-50 of the
-oracle; images are SURVEY 8(d)'s uniform-noise generator (content does not change the work).
+preprocess -> 53 convolutions -> head.  Weights are seeded random values
+(ai4e_b200.models.synthetic_state_dict); images are SURVEY 8(d)'s uniform-noise generator (content does not change the work).
 
 Printed keys (one JSON line, rank 0):
   value         images/s with the uint8 batch already resident in HBM (ai4e_engine_forward_device),
@@ -158,6 +158,7 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-layers", default=None, help="write per-layer device times (JSON) to this path")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -266,6 +267,22 @@ def main():
             conv_flops += 2 * B * p_ * q_ * l.cout * l.cin * l.kh * l.kw
             igemm_ms += float(ms[li + 1])
             igemm_launches += 1
+    if args.dump_layers and rank == 0:
+        rows, shp = [], {0: (HW, HW)}
+        for li, l in enumerate(prog.layers):
+            h, w = shp[l.in_buf]
+            if l.op == L.OP_HEAD:
+                rows.append({"name": l.name, "ms": float(ms[li + 1])})
+                continue
+            p_, q_ = (h + 2 * l.pad - l.kh) // l.stride + 1, (w + 2 * l.pad - l.kw) // l.stride + 1
+            shp[l.out_buf] = (p_, q_)
+            fl = 2 * B * p_ * q_ * l.cout * l.cin * l.kh * l.kw if l.op == L.OP_CONV else 0
+            byt = 2 * B * (h * w * l.cin + p_ * q_ * l.cout * (2 if l.res_buf >= 0 else 1)) + 2 * l.cout * l.cin * l.kh * l.kw
+            t = float(ms[li + 1])
+            rows.append({"name": l.name, "in": [h, w, l.cin], "out": [p_, q_, l.cout], "k": l.kh, "s": l.stride,
+                         "ms": t, "tflops": fl / t / 1e9 if t > 0 else 0, "gbs": byt / t / 1e6 if t > 0 else 0,
+                         "M": B * p_ * q_})
+        json.dump({"batch": B, "preprocess_ms": float(ms[0]), "layers": rows}, open(args.dump_layers, "w"), indent=1)
     achieved = conv_flops / (igemm_ms / 1e3) / 1e12
     peak_t = peaks["bf16_tflops_sustained"]
     pre_bytes = B * (HW * HW * IN_C + HW * HW * 4 * 2)  # u8 in + bf16 NHWC4 out (the engine's layout)
