@@ -4,6 +4,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <vector>
+
 using namespace ai4e;
 
 extern "C" {
@@ -46,6 +48,25 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   AI4E_REQUIRE(algo == AI4E_CONV_AUTO || algo == AI4E_CONV_IGEMM || algo == AI4E_CONV_DIRECT,
                "conv: unknown algo %d", algo);
   const bool can = igemm_supported(cin, cout, kh, kw, stride, pad) != 0;
+  if (algo != AI4E_CONV_DIRECT && !can && stem_supported(h, w, cin, cout, kh, kw, stride, pad)) {
+    // tensor-core stem.  This stateless entry repacks the weights on every call (a test
+    // convenience); the engine repacks once at creation.
+    AI4E_REQUIRE(d_residual_or_null == nullptr, "conv(stem): no residual input");
+    cudaStream_t s = (cudaStream_t)stream;
+    std::vector<uint16_t> w_in(64 * 7 * 7 * 4), w_sp(64 * 7 * 4 * 8);
+    AI4E_CUDA_TRY(cudaMemcpyAsync(w_in.data(), d_weight_krsc, w_in.size() * 2, cudaMemcpyDeviceToHost, s));
+    AI4E_CUDA_TRY(cudaStreamSynchronize(s));
+    stem_repack_weights(w_in.data(), w_sp.data());
+    void* d_sp = nullptr;
+    AI4E_CUDA_TRY(cudaMallocAsync(&d_sp, w_sp.size() * 2, s));
+    AI4E_CUDA_TRY(cudaMemcpyAsync(d_sp, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice, s));
+    AI4E_CUDA_TRY(cudaStreamSynchronize(s));  // w_sp is a stack-lifetime host buffer
+    IgemmPlan plan;
+    int rc = igemm_make_plan_stem(&plan, d_in_nhwc, batch, h, w, d_sp, d_bias, relu, d_out_nhwc);
+    if (rc == AI4E_OK) rc = igemm_launch(plan, batch, 0, s);
+    cudaFreeAsync(d_sp, s);
+    return rc;
+  }
   if (algo == AI4E_CONV_DIRECT || (algo == AI4E_CONV_AUTO && !can))
     return launch_conv_direct(d_in_nhwc, batch, h, w, cin, d_weight_krsc, d_bias, cout, kh, kw, stride,
                               pad, d_residual_or_null, relu, d_out_nhwc, (cudaStream_t)stream);

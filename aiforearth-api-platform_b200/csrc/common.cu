@@ -72,6 +72,36 @@ int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint6
   return AI4E_OK;
 }
 
+// general im2col-mode map (explicit bounding-box corners, traversal strides and swizzle)
+int tmap_encode_im2col(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c, const int lower[2],
+                       const int upper[2], const int stride_wh[2], int channels_per_pixel,
+                       int pixels_per_column, CUtensorMapSwizzle swizzle) {
+  std::call_once(g_once, resolve_driver_entry_points);
+  if (!g_encode_im2col) {
+    set_last_error("cuTensorMapEncodeIm2col is not available from this driver");
+    return AI4E_ERR_UNSUPPORTED;
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
+  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
+  int lo[2] = {lower[0], lower[1]}, up[2] = {upper[0], upper[1]};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride_wh[0], (cuuint32_t)stride_wh[1], 1};
+  CUresult r = g_encode_im2col(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(gaddr), dims, strides,
+                               lo, up, (cuuint32_t)channels_per_pixel, (cuuint32_t)pixels_per_column, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeIm2col failed with CUresult %d (N%d H%d W%d C%d, corners [%d,%d]/[%d,%d], "
+                   "stride %dx%d)", (int)r, n, h, w, c, lo[0], lo[1], up[0], up[1], stride_wh[0], stride_wh[1]);
+    return AI4E_ERR_CUDA;
+  }
+  // Drivers up to CUDA 13.1 set a descriptor bit that breaks im2col loads from tensors
+  // smaller than 128 KiB; CUTLASS (cute/atom/copy_traits_sm90_im2col.hpp) clears bit 21 of
+  // the second 64-bit word in that case, and so do we.
+  if (g_driver_version <= 13010 && (uint64_t)n * h * w * c * 2 < 131072ull)
+    reinterpret_cast<uint64_t*>(out)[1] &= ~(1ull << 21);
+  return AI4E_OK;
+}
+
 // im2col-mode map over an NHWC bf16 activation tensor for a forward convolution.
 //   dims (innermost first) {C, W, H, N}; bounding box of base pixels: lower corner = -pad,
 //   upper corner = pad - (filter - 1); traversal stride = convolution stride.  A load at base
@@ -82,32 +112,11 @@ int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint6
 int tmap_encode_im2col_nhwc(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c,
                             int filt_r, int filt_s, int stride, int pad, int channels_per_pixel,
                             int pixels_per_column) {
-  std::call_once(g_once, resolve_driver_entry_points);
-  if (!g_encode_im2col) {
-    set_last_error("cuTensorMapEncodeIm2col is not available from this driver");
-    return AI4E_ERR_UNSUPPORTED;
-  }
-  cuuint64_t dims[4] = {(cuuint64_t)c, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)n};
-  cuuint64_t strides[3] = {(cuuint64_t)c * 2, (cuuint64_t)w * c * 2, (cuuint64_t)h * w * c * 2};
-  int lower[2] = {-pad, -pad};
-  int upper[2] = {pad - (filt_s - 1), pad - (filt_r - 1)};
-  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
-  CUresult r = g_encode_im2col(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(gaddr),
-                               dims, strides, lower, upper, (cuuint32_t)channels_per_pixel,
-                               (cuuint32_t)pixels_per_column, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_last_error("cuTensorMapEncodeIm2col failed with CUresult %d (N%d H%d W%d C%d, %dx%d s%d p%d)",
-                   (int)r, n, h, w, c, filt_r, filt_s, stride, pad);
-    return AI4E_ERR_CUDA;
-  }
-  // Drivers up to CUDA 13.1 set a descriptor bit that breaks im2col loads from tensors
-  // smaller than 128 KiB; CUTLASS (cute/atom/copy_traits_sm90_im2col.hpp) clears bit 21 of
-  // the second 64-bit word in that case, and so do we.
-  if (g_driver_version <= 13010 && (uint64_t)n * h * w * c * 2 < 131072ull)
-    reinterpret_cast<uint64_t*>(out)[1] &= ~(1ull << 21);
-  return AI4E_OK;
+  const int lower[2] = {-pad, -pad};
+  const int upper[2] = {pad - (filt_s - 1), pad - (filt_r - 1)};
+  const int st[2] = {stride, stride};
+  return tmap_encode_im2col(out, gaddr, n, h, w, c, lower, upper, st, channels_per_pixel, pixels_per_column,
+                            CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
 }  // namespace ai4e

@@ -141,6 +141,27 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* tma
       "h"(off_w), "h"(off_h)
       : "memory");
 }
+// 2-D tile shared -> global (bulk async group); rows/columns outside the tensor are clipped
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(x), "r"(y)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// waits until at most N of this thread's bulk groups still READ their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 // 1-D bulk copy global -> shared (no tensor map)
 __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes,
                                              uint32_t bar) {
@@ -216,6 +237,19 @@ __device__ __forceinline__ uint64_t umma_smem_desc_kmajor(uint32_t saddr, uint32
   d |= static_cast<uint64_t>(layout_type) << 61;                  // layout type     [61,64)
   return d;
 }
+// General form: explicit leading-dimension (K direction between 16-byte core-matrix columns)
+// and stride-dimension (M/N direction between 8-row groups) byte offsets.  With layout_type 0
+// (no swizzle) the operand is a grid of 8-row x 16-byte core matrices, each 128 contiguous bytes.
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout_type) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr & 0x3FFFF) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(layout_type) << 61;
+  return d;
+}
 // Instruction descriptor for kind::f16 with bf16 A/B (both K-major) and fp32 accumulate.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_f32(int m, int n) {
   return (1u << 4)                       // D format  = F32
@@ -242,5 +276,9 @@ int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint6
 int tmap_encode_im2col_nhwc(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c,
                             int filt_r, int filt_s, int stride, int pad, int channels_per_pixel,
                             int pixels_per_column);
+// general im2col-mode map: explicit bounding-box corners {w, h}, traversal strides {w, h}, swizzle
+int tmap_encode_im2col(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c, const int lower[2],
+                       const int upper[2], const int stride_wh[2], int channels_per_pixel,
+                       int pixels_per_column, CUtensorMapSwizzle swizzle);
 
 }  // namespace ai4e

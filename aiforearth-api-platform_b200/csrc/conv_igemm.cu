@@ -10,7 +10,7 @@
 // inside the callback the reference invokes at APIs/1.0/base-py/ai4e_service.py:203;
 // oracle: torch.nn.functional.conv2d in oracle/resnet_oracle.py (_conv_bf16).
 //
-// Structure (one persistent CTA per SM, 192 threads, warp-specialised):
+// Structure (one persistent CTA per SM, 320 threads, warp-specialised):
 //   warp 0   TMA producer.  A tiles come straight from the NHWC activation tensor through an
 //            IM2COL-mode tensor map: one `cp.async.bulk.tensor.4d...im2col` per K block
 //            fetches 128 consecutive output pixels x 64 channels for filter tap (r, s), with
@@ -22,9 +22,14 @@
 //            stages and signals the epilogue.  Two accumulator stages in TMEM
 //            (2 x BLOCK_N fp32 columns) let the epilogue of tile i overlap the MMAs of
 //            tile i+1.
-//   warps 2-5  epilogue: `tcgen05.ld` 32 lanes x 32 columns at a time, + bias, + residual,
-//            ReLU, pack to bf16, 16-byte stores.  A warp may only touch the TMEM lane
-//            quadrant `warp_id % 4`, hence four consecutive warps.
+//   warps 2-9  epilogue, 64 output channels at a time: `tcgen05.ld` (each thread owns one pixel
+//            row), + bias, + residual, ReLU, pack to bf16 into a 128-byte-swizzled staging
+//            tile in shared memory, which one thread hands to the TMA unit
+//            (`cp.async.bulk.tensor.2d.global.shared::cta`): stores to HBM are full 128-byte
+//            lines, asynchronous, and rows past the tensor end are clipped by hardware.  The
+//            residual tile arrives the same way (TMA load, two chunks ahead).  Staging and
+//            residual tiles are double-buffered.  A warp may only touch the TMEM lane quadrant
+//            `warp_id % 4`; warps w and w+4 split the 64 channels of a chunk between them.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -35,34 +40,55 @@ namespace ai4e {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kUmmaK = 16;
-constexpr int kIgemmThreads = 192;
+constexpr int kEpiWarps = 8;                              // two warps per TMEM lane quadrant
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kIgemmThreads = 64 + kEpiThreads;           // + TMA producer warp + MMA warp
 constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
+constexpr int kChunkN = 64;                               // epilogue works on 64 channels at a time
+constexpr int kChunkBytes = kBlockM * kChunkN * 2;        // 16 KiB: 128 rows x 128 bytes, swizzled
 
-template <int BLOCK_N>
+// Stem (7x7 stride 2, 3/4 input channels -> 64): the NHWC4 image is read as an [H][W/2][8] grid
+// of "super-pixels" (two adjacent pixels = 8 channels = 16 bytes, the smallest unit im2col-mode
+// TMA can fetch).  Output pixel q needs pixels 2q-3 .. 2q+3 = super-pixels q-2 .. q+1, so the
+// 7-tap row becomes 4 super-pixel taps (the first carries one zero-weight pixel).  Each K block
+// is one filter row r: 4 taps x 8 channels = 32 K values, held as four un-swizzled
+// [128 rows][16 bytes] slabs (the canonical no-swizzle K-major layout: 8x16-byte core
+// matrices, LBO = slab size, SBO = 128 bytes).  K = 7 x 32 = 224 for 147 useful taps.
+constexpr int kStemTaps = 4;
+constexpr int kStemSlabA = kBlockM * 16;  // 2 KiB
+constexpr int kStemKBlocks = 7;
+
+template <int BLOCK_N, bool kStem = false>
 struct IgemmCfg {
-  static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
-  static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+  static constexpr int kAStage = kStem ? kStemTaps * kStemSlabA : kABytes;
+  static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : BLOCK_N * kBlockK * 2;
+  static constexpr int kStageBytes = kAStage + kBBytes;
+  static constexpr int kStages = kStem ? 8 : (BLOCK_N == 256) ? 3 : (BLOCK_N == 128 ? 5 : 6);
   static constexpr int kTmemCols = 2 * BLOCK_N;  // 128 / 256 / 512: power of two >= 32
-  // 1024-byte alignment slack + stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + (2 * kStages + 4) * 8 + 16;
+  static constexpr int kEpiBytes = 4 * kChunkBytes;  // 2 output staging tiles + 2 residual tiles
+  // 1024-byte alignment slack + stages + epilogue tiles + barriers (full, empty, tmem_full[2],
+  // tmem_empty[2], res_full[2]) + tmem ptr
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + (2 * kStages + 6) * 8 + 16;
 };
 
-template <int BLOCK_N>
+template <int BLOCK_N, bool kStem>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
-conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                  const __grid_constant__ CUtensorMap tmap_b, const IgemmParams p) {
-  using Cfg = IgemmCfg<BLOCK_N>;
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
+                  const IgemmParams p) {
+  using Cfg = IgemmCfg<BLOCK_N, kStem>;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + kStages * Cfg::kStageBytes;
+  const uint32_t epi_base = smem_base + kStages * Cfg::kStageBytes;  // [out0][out1][res0][res1]
+  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
   auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
-  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 4);
+  auto res_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 4 + s); };
+  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 6);
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_addr - smem_u32(smem_raw)));
 
@@ -78,8 +104,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);
-      mbar_init(tmem_empty_bar(s), 128);
+      mbar_init(tmem_empty_bar(s), kEpiThreads);
+      mbar_init(res_full_bar(s), 1);
     }
+    tma_prefetch_desc(&tmap_out);
+    if (p.residual) tma_prefetch_desc(&tmap_res);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -104,18 +133,29 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const int rem = m0 - n_img * p.PQ;
         const int p0 = rem / p.Q;
         const int q0 = rem - p0 * p.Q;
-        const int w_base = q0 * p.stride - p.pad;
+        // base pixel of the tile in input coordinates (stem: W in super-pixels, stride 1, pad 2)
+        const int w_base = kStem ? q0 - 2 : q0 * p.stride - p.pad;
         const int h_base = p0 * p.stride - p.pad;
-        int r = 0, s = 0, cb = 0;
+        [[maybe_unused]] int r = 0, s = 0, cb = 0;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
-          const uint32_t b_dst = a_dst + kABytes;
+          const uint32_t b_dst = a_dst + Cfg::kAStage;
           mbar_expect_tx(full_bar(stage), Cfg::kStageBytes);
-          tma_load_im2col_4d(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
-                             (uint16_t)s, (uint16_t)r);
-          tma_load_2d(b_dst, &tmap_b, full_bar(stage), kb * kBlockK, tile_n * BLOCK_N);
-          if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
+          if constexpr (kStem) {
+            // K block kb = filter row; one im2col load per super-pixel tap, one weight slab each
+#pragma unroll
+            for (int t = 0; t < kStemTaps; ++t) {
+              tma_load_im2col_4d(a_dst + t * kStemSlabA, &tmap_a, full_bar(stage), 0, w_base, h_base, n_img,
+                                 (uint16_t)t, (uint16_t)kb);
+              tma_load_2d(b_dst + t * BLOCK_N * 16, &tmap_b, full_bar(stage), kb * 32 + t * 8, tile_n * BLOCK_N);
+            }
+          } else {
+            tma_load_im2col_4d(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
+                               (uint16_t)s, (uint16_t)r);
+            tma_load_2d(b_dst, &tmap_b, full_bar(stage), kb * kBlockK, tile_n * BLOCK_N);
+            if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
+          }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -137,13 +177,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
-          const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
-          const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
+          if constexpr (kStem) {
+            // un-swizzled slabs: one MMA (K = 16) spans two slabs; LBO = slab size, SBO = 128 bytes
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
-            // +2 in the (addr >> 4) start-address field
-            umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < kStemTaps / 2; ++k) {
+              const uint64_t adesc = umma_smem_desc(a_addr + 2 * k * kStemSlabA, kStemSlabA, 128, 0);
+              const uint64_t bdesc =
+                  umma_smem_desc(a_addr + Cfg::kAStage + 2 * k * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
+              umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+          } else {
+            const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
+            const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
+              // +2 in the (addr >> 4) start-address field
+              umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
           }
           umma_commit(empty_bar(stage));  // smem stage reusable once these MMAs retire
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -153,53 +204,98 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   } else {
     // ------------------------------- epilogue -----------------------------------
-    const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+    // Eight warps: warp pair (w, w+4) shares TMEM lane quadrant w % 4 (= rows 32*quad..+31 of the
+    // tile); within every 64-channel chunk the first warp of the pair takes channels 0-31, the
+    // second 32-63.  Two warps per scheduler hide the TMEM / shared-memory latencies.
+    const int quad = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = quad * 32 + lane;
+    const bool leader = (warp == 2 && lane == 0);
+    const bool has_res = p.residual != nullptr;
+    const bool relu = p.relu != 0;
+    constexpr int kChunks = BLOCK_N / kChunkN;
+    uint8_t* const smem_gen = smem_raw + (epi_base - smem_u32(smem_raw));  // generic view of the epilogue tiles
+    const uint32_t sw = (uint32_t)(row & 7);
+    uint32_t unit_off[4];  // this thread's four 16-byte units inside a swizzled 128-byte row
+#pragma unroll
+    for (int j = 0; j < 4; ++j) unit_off[j] = (uint32_t)row * 128u + ((((uint32_t)(half * 4 + j)) ^ sw) << 4);
     uint32_t it = 0;
+    uint32_t chunk_seq = 0;  // chunks processed so far: selects staging / residual buffer and phase
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const uint32_t acc = it & 1u;
       const uint32_t acc_phase = (it >> 1) & 1u;
       const int tile_n = tile % p.tiles_n;
       const int tile_m = tile / p.tiles_n;
-      const long long m = (long long)tile_m * kBlockM + row;
-      const bool valid = m < p.M;
+      const int m0 = tile_m * kBlockM;
       const int n0 = tile_n * BLOCK_N;
+      if (has_res && leader) {  // residual tiles for the first two chunks travel while the MMAs run
+#pragma unroll
+        for (int c = 0; c < 2 && c < kChunks; ++c) {
+          const uint32_t b = (chunk_seq + c) & 1u;
+          mbar_expect_tx(res_full_bar(b), kChunkBytes);
+          tma_load_2d(epi_base + (2 + b) * kChunkBytes, &tmap_res, res_full_bar(b), n0 + c * kChunkN, m0);
+        }
+      }
       mbar_wait(tmem_full_bar(acc), acc_phase);
       tc_fence_after();
-      const uint32_t t_addr = tmem_base + acc * BLOCK_N + ((uint32_t)(quad * 32) << 16);
-      bf16* out_row = p.out + m * p.Cout + n0;
-      const bf16* res_row = p.residual ? p.residual + m * p.Cout + n0 : nullptr;
+      const uint32_t t_addr = tmem_base + acc * BLOCK_N + half * 32 + ((uint32_t)(quad * 32) << 16);
 #pragma unroll 1
-      for (int ch = 0; ch < BLOCK_N / 32; ++ch) {
+      for (int c = 0; c < kChunks; ++c, ++chunk_seq) {
+        const uint32_t b = chunk_seq & 1u;
+        uint8_t* const out_gen = smem_gen + b * kChunkBytes;
+        const uint8_t* const res_gen = smem_gen + (2 + b) * kChunkBytes;
         uint32_t v[32];
-        tmem_ld_32x32b_x32(t_addr + ch * 32, v);
+        tmem_ld_32x32b_x32(t_addr + c * kChunkN, v);
+        float4 bias[8];
+        {
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0 + c * kChunkN + half * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bias[j] = __ldg(b4 + j);
+        }
+        // the TMA store that last read this staging tile (two chunks ago) must be done with it
+        if (leader) bulk_wait_group_read<1>();
+        named_bar_sync(1, kEpiThreads);
+        uint4 r[4];
+        if (has_res) {
+          mbar_wait(res_full_bar(b), (chunk_seq >> 1) & 1u);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) r[j] = *reinterpret_cast<const uint4*>(res_gen + unit_off[j]);
+        }
         tmem_wait_ld();
-        if (valid) {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0 + ch * 32);
-          uint32_t o[16];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(b4 + j);
-            float x0 = __uint_as_float(v[4 * j + 0]) + b.x;
-            float x1 = __uint_as_float(v[4 * j + 1]) + b.y;
-            float x2 = __uint_as_float(v[4 * j + 2]) + b.z;
-            float x3 = __uint_as_float(v[4 * j + 3]) + b.w;
-            if (res_row) {
-              const uint2 rr = __ldg(reinterpret_cast<const uint2*>(res_row + ch * 32 + 4 * j));
-              x0 += bf16_lo(rr.x); x1 += bf16_hi(rr.x); x2 += bf16_lo(rr.y); x3 += bf16_hi(rr.y);
-            }
-            if (p.relu) { x0 = fmaxf(x0, 0.f); x1 = fmaxf(x1, 0.f); x2 = fmaxf(x2, 0.f); x3 = fmaxf(x3, 0.f); }
-            o[2 * j] = pack_bf16x2(x0, x1);
-            o[2 * j + 1] = pack_bf16x2(x2, x3);
+        for (int j = 0; j < 4; ++j) {  // 8 channels = one 16-byte unit of the swizzled row
+          float x[8];
+          x[0] = __uint_as_float(v[8 * j + 0]) + bias[2 * j].x; x[1] = __uint_as_float(v[8 * j + 1]) + bias[2 * j].y;
+          x[2] = __uint_as_float(v[8 * j + 2]) + bias[2 * j].z; x[3] = __uint_as_float(v[8 * j + 3]) + bias[2 * j].w;
+          x[4] = __uint_as_float(v[8 * j + 4]) + bias[2 * j + 1].x; x[5] = __uint_as_float(v[8 * j + 5]) + bias[2 * j + 1].y;
+          x[6] = __uint_as_float(v[8 * j + 6]) + bias[2 * j + 1].z; x[7] = __uint_as_float(v[8 * j + 7]) + bias[2 * j + 1].w;
+          if (has_res) {
+            x[0] += bf16_lo(r[j].x); x[1] += bf16_hi(r[j].x); x[2] += bf16_lo(r[j].y); x[3] += bf16_hi(r[j].y);
+            x[4] += bf16_lo(r[j].z); x[5] += bf16_hi(r[j].z); x[6] += bf16_lo(r[j].w); x[7] += bf16_hi(r[j].w);
           }
-          uint4* dst = reinterpret_cast<uint4*>(out_row + ch * 32);
+          if (relu) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) dst[j] = make_uint4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+            for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], 0.f);
+          }
+          *reinterpret_cast<uint4*>(out_gen + unit_off[j]) =
+              make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
+                         pack_bf16x2(x[6], x[7]));
+        }
+        fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
+        named_bar_sync(2, kEpiThreads);
+        if (leader) {
+          tma_store_2d(&tmap_out, epi_base + b * kChunkBytes, n0 + c * kChunkN, m0);
+          bulk_commit_group();
+          if (has_res && c + 2 < kChunks) {  // everyone is done reading res_buf[b]: refill it
+            mbar_expect_tx(res_full_bar(b), kChunkBytes);
+            tma_load_2d(epi_base + (2 + b) * kChunkBytes, &tmap_res, res_full_bar(b), n0 + (c + 2) * kChunkN, m0);
+          }
         }
       }
       tc_fence_before();
-      mbar_arrive(tmem_empty_bar(acc));  // 128 arrivals free this accumulator stage
+      mbar_arrive(tmem_empty_bar(acc));  // kEpiThreads arrivals free this accumulator stage
     }
+    if (leader) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
   }
 
   tc_fence_before();
@@ -256,12 +352,24 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias;
   q.residual = (const bf16*)residual; q.out = (bf16*)out;
   plan->max_batch = N;
+  plan->is_stem = false;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint64_t ktot = (uint64_t)R * S * Cin;
   const uint64_t dims[2] = {ktot, (uint64_t)Cout};
   const uint64_t strides[1] = {ktot * 2};
   const uint32_t es[2] = {1, 1};
+  // output / residual tiles: [M rows][Cout] bf16, 128 rows x 64 channels per TMA, 128B swizzle
+  {
+    const uint64_t odims[2] = {(uint64_t)Cout, (uint64_t)N * P * Q};
+    const uint64_t ostr[1] = {(uint64_t)Cout * 2};
+    const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
+    rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    rc = tmap_encode_tiled(&plan->tmap_res, residual ? residual : out, 2, odims, ostr, obox, es,
+                           CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
   const int bns[3] = {64, 128, 256};
   for (int i = 0; i < 3; ++i) {
     plan->has_bn[i] = Cout % bns[i] == 0;
@@ -273,18 +381,74 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   return AI4E_OK;
 }
 
-template <int BN>
-static int igemm_launch_bn(const CUtensorMap& ta, const CUtensorMap& tb, const IgemmParams& prm, int grid,
+int stem_supported(int H, int W, int Cin, int Cout, int R, int S, int stride, int pad) {
+  return Cin == 4 && Cout == 64 && R == 7 && S == 7 && stride == 2 && pad == 3 && W % 2 == 0 && H >= 7 && W >= 8;
+}
+
+// [64][7][7][4] KRSC bf16 weights -> [64][7][4 taps][8] "super-pixel" weights (see kStemTaps):
+// tap t, channel c < 4  <- filter column 2t-1 (zero for t = 0); channel 4+c <- filter column 2t.
+void stem_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp) {
+  for (int co = 0; co < 64; ++co)
+    for (int r = 0; r < 7; ++r)
+      for (int t = 0; t < kStemTaps; ++t)
+        for (int c = 0; c < 8; ++c) {
+          const int s = (c < 4) ? 2 * t - 1 : 2 * t;
+          const int ch = c & 3;
+          w_sp[((co * 7 + r) * kStemTaps + t) * 8 + c] = (s < 0) ? (uint16_t)0 : w_krsc[((co * 7 + r) * 7 + s) * 4 + ch];
+        }
+}
+
+// `weight_sp` is the repacked [64][224] device tensor.  Output geometry as for any 7x7/2 pad 3.
+int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
+                         const float* bias, int relu, void* out) {
+  AI4E_REQUIRE(stem_supported(H, W, 4, 64, 7, 7, 2, 3), "conv(stem): unsupported input %dx%d", H, W);
+  AI4E_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(weight_sp) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(out) & 15) == 0 && (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
+               "conv(stem): pointers must be 16-byte aligned");
+  const int P = (H + 6 - 7) / 2 + 1, Q = (W + 6 - 7) / 2 + 1;
+  AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "conv(stem): M too large");
+  IgemmParams& q = plan->prm;
+  q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = 64; q.S = kStemTaps; q.stride = 2; q.pad = 3;
+  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks;
+  q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias; q.residual = nullptr; q.out = (bf16*)out;
+  plan->max_batch = N;
+  plan->is_stem = true;
+  // input as [N][H][W/2][8]: 4 taps from super-pixel q-2, traversal stride 1 in W and 2 in H.
+  // lower corner {-2, -3}; upper corner = right/bottom padding - (taps - 1) = {1 - 3, 3 - 6}.
+  const int lower[2] = {-2, -3}, upper[2] = {-2, -3}, st[2] = {1, 2};
+  int rc = tmap_encode_im2col(&plan->tmap_a, in, N, H, W / 2, 8, lower, upper, st, 8, kBlockM,
+                              CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  const uint32_t es[2] = {1, 1};
+  const uint64_t wdims[2] = {(uint64_t)kStemKBlocks * 32, 64};
+  const uint64_t wstr[1] = {(uint64_t)kStemKBlocks * 32 * 2};
+  const uint32_t wbox[2] = {8, 64};
+  for (int i = 0; i < 3; ++i) plan->has_bn[i] = false;
+  plan->has_bn[0] = true;
+  rc = tmap_encode_tiled(&plan->tmap_b[0], weight_sp, 2, wdims, wstr, wbox, es, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  const uint64_t odims[2] = {64, (uint64_t)N * P * Q};
+  const uint64_t ostr[1] = {64 * 2};
+  const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
+  rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rc) return rc;
+  plan->tmap_res = plan->tmap_out;
+  return AI4E_OK;
+}
+
+template <int BN, bool kStem>
+static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const IgemmParams& prm, int grid,
                            cudaStream_t stream) {
   static unsigned long long attr_done = 0;  // bit per device
   int dev = 0;
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
   if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN>::kSmemBytes));
+    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kStem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       IgemmCfg<BN, kStem>::kSmemBytes));
     attr_done |= 1ull << dev;
   }
-  conv_igemm_kernel<BN><<<grid, kIgemmThreads, IgemmCfg<BN>::kSmemBytes, stream>>>(ta, tb, prm);
+  conv_igemm_kernel<BN, kStem><<<grid, kIgemmThreads, IgemmCfg<BN, kStem>::kSmemBytes, stream>>>(
+      plan.tmap_a, tb, plan.tmap_out, plan.tmap_res, prm);
   AI4E_CUDA_TRY(cudaGetLastError());
   return AI4E_OK;
 }
@@ -294,6 +458,13 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
                plan.max_batch);
   IgemmParams prm = plan.prm;
   const long long M = (long long)batch * prm.PQ;
+  if (plan.is_stem) {
+    prm.M = (int)M;
+    prm.tiles_m = (int)((M + kBlockM - 1) / kBlockM);
+    prm.tiles_n = 1;
+    prm.num_tiles = prm.tiles_m;
+    return igemm_launch_bn<64, true>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()), stream);
+  }
   const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M);
   const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
   AI4E_REQUIRE(bi >= 0 && plan.has_bn[bi], "conv(igemm): BLOCK_N %d not available for Cout %d", bn, prm.Cout);
@@ -303,9 +474,9 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
   prm.num_tiles = prm.tiles_m * prm.tiles_n;
   const int grid = std::min(prm.num_tiles, sm_count());
   switch (bn) {
-    case 64: return igemm_launch_bn<64>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
-    case 128: return igemm_launch_bn<128>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
-    default: return igemm_launch_bn<256>(plan.tmap_a, plan.tmap_b[bi], prm, grid, stream);
+    case 64: return igemm_launch_bn<64, false>(plan, plan.tmap_b[bi], prm, grid, stream);
+    case 128: return igemm_launch_bn<128, false>(plan, plan.tmap_b[bi], prm, grid, stream);
+    default: return igemm_launch_bn<256, false>(plan, plan.tmap_b[bi], prm, grid, stream);
   }
 }
 

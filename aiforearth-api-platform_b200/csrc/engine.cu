@@ -68,6 +68,7 @@ struct ai4e_engine {
   std::vector<void*> bufs;
   std::vector<size_t> buf_elems_per_image;
   uint8_t* d_blob = nullptr;
+  uint16_t* d_stem_w = nullptr;  // stem weights repacked for the tensor-core stem
   float* d_pooled = nullptr;
   size_t slot_bytes = 0;  // staging bytes per image
   int launches = 0;
@@ -432,7 +433,20 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   for (LayerRt& L : e->layers) {
     const ai4e_layer_desc& d = L.d;
     e->launches += d.op == AI4E_OP_HEAD ? 3 : 1;
-    if (d.op != AI4E_OP_CONV || !L.igemm) continue;
+    if (d.op != AI4E_OP_CONV) continue;
+    if (!L.igemm && d.res_buf < 0 && stem_supported(L.in_h, L.in_w, d.cin, d.cout, d.kh, d.kw, d.stride, d.pad) &&
+        !getenv("AI4E_B200_DIRECT_STEM")) {
+      std::vector<uint16_t> w_sp(64 * 7 * 4 * 8);
+      stem_repack_weights(reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(blob) + d.w_off), w_sp.data());
+      if (!e->d_stem_w) TRY_OR_FAIL(cudaMalloc((void**)&e->d_stem_w, w_sp.size() * 2));
+      TRY_OR_FAIL(cudaMemcpy(e->d_stem_w, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice));
+      int rc = igemm_make_plan_stem(&L.plan, e->bufs[d.in_buf], max_batch, L.in_h, L.in_w, e->d_stem_w,
+                                    (const float*)(e->d_blob + d.b_off), d.relu, e->bufs[d.out_buf]);
+      if (rc) return fail(rc);
+      L.igemm = true;
+      continue;
+    }
+    if (!L.igemm) continue;
     int rc = igemm_make_plan(&L.plan, e->bufs[d.in_buf], max_batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
                              (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
                              d.res_buf >= 0 ? e->bufs[d.res_buf] : nullptr, d.relu, e->bufs[d.out_buf]);
@@ -500,6 +514,7 @@ int ai4e_engine_destroy(ai4e_engine* e) {
     if (b) cudaFree(b);
   if (e->d_pooled) cudaFree(e->d_pooled);
   if (e->d_blob) cudaFree(e->d_blob);
+  if (e->d_stem_w) cudaFree(e->d_stem_w);
   if (e->ev_chain) cudaEventDestroy(e->ev_chain);
   delete e;
   return AI4E_OK;

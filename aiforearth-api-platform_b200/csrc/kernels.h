@@ -37,9 +37,12 @@ struct IgemmParams {
 struct IgemmPlan {
   CUtensorMap tmap_a;     // im2col-mode map over the input activations (N = max_batch)
   CUtensorMap tmap_b[3];  // weight tiles for BLOCK_N = 64 / 128 / 256
+  CUtensorMap tmap_out;   // output tiles (TMA store), 128 rows x 64 channels
+  CUtensorMap tmap_res;   // residual tiles (TMA load), same geometry
   bool has_bn[3];
   IgemmParams prm;        // everything but the batch-dependent fields
   int max_batch;
+  bool is_stem;           // 7x7/2 stem on super-pixels (see conv_igemm.cu)
 };
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
@@ -48,6 +51,11 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
                     int pad, const void* residual, int relu, void* out);
 int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream_t stream);
+// tensor-core stem: 7x7 stride 2 pad 3, NHWC4 input, 64 outputs
+int stem_supported(int H, int W, int Cin, int Cout, int R, int S, int stride, int pad);
+void stem_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][7][7][4] -> [64][7][4][8]
+int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
+                         const float* bias, int relu, void* out);
 
 // ---- K3 / K5 (pool_head.cu)
 int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,

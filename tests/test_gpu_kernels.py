@@ -140,6 +140,28 @@ def test_conv_direct_vs_oracle(case):
     _check_conv(out, want)
 
 
+STEM_CASES = [
+    (2, 224, 224, 4, 64, 7, 2, 3, True, False),   # the stem at full size (M = 25088, 196 tiles)
+    (3, 32, 32, 4, 64, 7, 2, 3, True, False),     # small: most taps touch the zero padding
+    (1, 256, 256, 4, 64, 7, 2, 3, False, False),  # land-cover chip size, no ReLU
+    (2, 30, 50, 4, 64, 7, 2, 3, True, False),     # ragged: M = 2*15*25 = 750, rows wrap mid-tile
+    (1, 8, 8, 4, 64, 7, 2, 3, True, False),       # tiny: M = 16
+]
+
+
+@pytest.mark.parametrize("case", STEM_CASES, ids=lambda c: "x".join(str(v) for v in c[:3]))
+def test_conv_stem_tensor_core_vs_oracle(case):
+    """7x7/2 stem on tcgen05 through super-pixel im2col loads (AUTO picks it for Cin = 4)."""
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, cin, cout, k, stride, pad, relu, residual = case
+    x, wt, bias, res, want = _conv_case(*case, seed=9)
+    out = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), stride, pad, None, relu, algo=L.CONV_AUTO)
+    torch.cuda.synchronize()
+    _check_conv(out, want)
+    direct = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), stride, pad, None, relu, algo=L.CONV_DIRECT)
+    assert (out.float() - direct.float()).abs().max() <= 2.0 ** -6 * want.abs().max()
+
+
 # (b, h, w, cin, cout, k, stride, pad, relu, residual): every conv geometry of ResNet-18/50
 # after the stem, at small batch, plus ragged tails (M not a multiple of 128)
 IGEMM_CASES = [
