@@ -17,6 +17,7 @@ LAYOUT_NCHW, LAYOUT_NHWC = 0, 1
 CONV_AUTO, CONV_IGEMM, CONV_DIRECT = 0, 1, 2
 OP_CONV, OP_MAXPOOL, OP_HEAD = 0, 1, 2
 TOPK = 5
+HEAD_NOALLOC_MAX_FLOATS = 64 * 2048
 
 
 class Ai4eLibraryError(RuntimeError):
@@ -63,6 +64,7 @@ SIGNATURES = {
     "ai4e_conv_layer": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp]),
     "ai4e_maxpool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ai4e_head": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),
+    "ai4e_head_noalloc": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),
     "ai4e_engine_create": (_i, [_i, C.POINTER(ModelDesc), _vp, _u64, _i, _i, C.POINTER(_vp)]),
     "ai4e_engine_destroy": (_i, [_vp]),
     "ai4e_engine_forward_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),

@@ -89,3 +89,19 @@ def head(x_nhwc: torch.Tensor, fc_w: torch.Tensor, fc_b: torch.Tensor, topk: int
     L.check(lib.ai4e_head(_ptr(x_nhwc), b, h * w, c, _ptr(fc_w), _ptr(fc_b), classes, _ptr(logits), _ptr(idx),
                           _ptr(prob), topk, _stream_ptr(stream)))
     return logits, idx[:, :topk], prob[:, :topk]
+
+
+def head_noalloc(x_nhwc: torch.Tensor, fc_w: torch.Tensor, fc_b: torch.Tensor, topk: int = L.TOPK, stream=None):
+    """`head` for callers that must not allocate device memory: the pooled-feature scratch is a
+    fixed array inside the library (batch*C <= L.HEAD_NOALLOC_MAX_FLOATS), shared by every call on
+    the device - do not overlap calls.  The output tensors here are made by the caller (torch)."""
+    lib = L.load()
+    assert x_nhwc.is_contiguous() and fc_w.is_contiguous() and fc_b.is_contiguous()
+    b, h, w, c = x_nhwc.shape
+    classes = fc_w.shape[0]
+    logits = torch.empty((b, classes), dtype=torch.float32, device=x_nhwc.device)
+    idx = torch.empty((b, max(topk, 1)), dtype=torch.int32, device=x_nhwc.device)
+    prob = torch.empty((b, max(topk, 1)), dtype=torch.float32, device=x_nhwc.device)
+    L.check(lib.ai4e_head_noalloc(_ptr(x_nhwc), b, h * w, c, _ptr(fc_w), _ptr(fc_b), classes, _ptr(logits),
+                                  _ptr(idx), _ptr(prob), topk, _stream_ptr(stream)))
+    return logits, idx[:, :topk], prob[:, :topk]

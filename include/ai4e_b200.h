@@ -111,6 +111,21 @@ AI4E_API int ai4e_head(const void* d_in_nhwc, int batch, int hw, int c, const vo
               const float* d_fc_b, int classes, float* d_logits, int32_t* d_top_idx,
               float* d_top_prob, int topk, void* stream);
 
+/* K5 for callers that must not allocate device memory: a request thread whose framework has
+ * already given the whole GPU to its own pool allocator, or a latency-critical path that cannot
+ * take the device-wide synchronisation of cudaMalloc / cudaFree.  Same arguments and results as
+ * ai4e_head, but the batch*c floats of pooled-feature scratch live in a fixed array inside the
+ * library (AI4E_HEAD_NOALLOC_MAX_FLOATS floats = 512 KiB, held by every GPU that loads the
+ * library until exit).  batch*c above the limit -> AI4E_ERR_INVALID.  All calls on a device
+ * share the array: calls that overlap on the GPU race, so keep them on one stream or order
+ * them with an event.  The first call on each device resolves the array's address; make it
+ * before any stream capture on that device.  This entry point has no counterpart in the
+ * reference. */
+#define AI4E_HEAD_NOALLOC_MAX_FLOATS (64 * 2048)
+AI4E_API int ai4e_head_noalloc(const void* d_in_nhwc, int batch, int hw, int c, const void* d_fc_w,
+                               const float* d_fc_b, int classes, float* d_logits, int32_t* d_top_idx,
+                               float* d_top_prob, int topk, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Engine: one model replica on one GPU (the reference runs one replica per pod).
  * ------------------------------------------------------------------------------------- */
