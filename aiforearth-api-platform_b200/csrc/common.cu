@@ -1,6 +1,7 @@
 // Error plumbing and tensor-map encoders shared by every kernel file.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -15,6 +16,14 @@ void set_last_error(const char* fmt, ...) {
   va_end(ap);
 }
 const char* get_last_error() { return g_err; }
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* v = getenv("AI4E_B200_NO_PDL");
+    return !(v && v[0] == '1');
+  }();
+  return on;
+}
 
 // ----------------------------------------------------------------------------------------
 // cuTensorMapEncode* resolved through the runtime so the library has no link-time

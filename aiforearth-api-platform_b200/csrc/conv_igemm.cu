@@ -119,6 +119,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
+  // everything above touched only this kernel's own shared memory / TMEM / parameters: it may
+  // overlap the previous layer's tail.  From here on we read its output and overwrite buffers
+  // it may still read.
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
@@ -447,9 +452,9 @@ static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const I
                                        IgemmCfg<BN, kStem>::kSmemBytes));
     attr_done |= 1ull << dev;
   }
-  conv_igemm_kernel<BN, kStem><<<grid, kIgemmThreads, IgemmCfg<BN, kStem>::kSmemBytes, stream>>>(
-      plan.tmap_a, tb, plan.tmap_out, plan.tmap_res, prm);
-  AI4E_CUDA_TRY(cudaGetLastError());
+  AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kStem>, dim3(grid), dim3(kIgemmThreads),
+                           (size_t)IgemmCfg<BN, kStem>::kSmemBytes, stream, plan.tmap_a, tb, plan.tmap_out,
+                           plan.tmap_res, prm));
   return AI4E_OK;
 }
 

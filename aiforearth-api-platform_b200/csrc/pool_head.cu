@@ -5,6 +5,12 @@
 // APIs/1.0/base-py/ai4e_service.py:203; oracle/resnet_oracle.py restates it).
 #include "common.cuh"
 
+// Loads of tensors written by the PREVIOUS kernel use __ldcg (L2 only).  These kernels start
+// early under programmatic dependent launch; the read-only (.nc) path that `const __restrict__`
+// / __ldg select may then serve lines cached before the producer wrote them (seen on B200 as
+// stale logits in the top-k kernel).  Weights and biases, constant for the engine's life, keep
+// __ldg.
+
 namespace ai4e {
 
 int sm_count();
@@ -16,6 +22,8 @@ int sm_count();
 __global__ void __launch_bounds__(256)
 maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int N, int H, int W, int C8,
                int k, int stride, int pad, int P, int Q) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long total = (long long)N * P * Q * C8;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -33,7 +41,7 @@ maxpool_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int N, int
       for (int s = 0; s < k; ++s) {
         const int w = q * stride - pad + s;
         if (w < 0 || w >= W) continue;
-        const uint4 v = __ldg(in + (((long long)n * H + h) * W + w) * C8 + c8);
+        const uint4 v = __ldcg(in + (((long long)n * H + h) * W + w) * C8 + c8);
         const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -56,118 +64,188 @@ int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride
   const int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   const long long total = (long long)N * P * Q * (C / 8);
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)sm_count() * 16);
-  maxpool_kernel<<<grid, 256, 0, stream>>>((const uint4*)in, (uint4*)out, N, H, W, C / 8, k, stride,
-                                           pad, P, Q);
-  AI4E_CUDA_TRY(cudaGetLastError());
+  AI4E_CUDA_TRY(launch_pdl(maxpool_kernel, dim3(grid), dim3(256), 0, stream, (const uint4*)in, (uint4*)out, N, H, W,
+                           C / 8, k, stride, pad, P, Q));
   return AI4E_OK;
 }
 
 // ---------------------------------------------------------------------------------------
-// global average pool: [N, HW, C] bf16 -> [N, C] fp32.  thread = (n, 8 channels)
+// global average pool: [N, HW, C] bf16 -> [N, C] fp32.
+// block = (image, 256 channels): 32 lanes x 8 channels (16-byte loads, 512 contiguous bytes per
+// pixel row) times kPoolParts pixel groups, reduced through shared memory.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-avgpool_kernel(const uint4* __restrict__ in, float* __restrict__ out, int N, int HW, int C8) {
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= N * C8) return;
-  const int n = idx / C8, c8 = idx % C8;
+constexpr int kPoolParts = 7;
+__global__ void __launch_bounds__(32 * kPoolParts)
+avgpool_kernel(const uint4* __restrict__ in, float* __restrict__ out, int HW, int C8) {
+  __shared__ float part[kPoolParts][32][9];
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31, prt = threadIdx.x >> 5;
+  const int n = blockIdx.y;
+  const int c8 = blockIdx.x * 32 + lane;
   float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  const uint4* p = in + (long long)n * HW * C8 + c8;
-  for (int i = 0; i < HW; ++i) {
-    const uint4 v = __ldg(p + (long long)i * C8);
-    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+  if (c8 < C8) {
+    const uint4* p = in + (long long)n * HW * C8 + c8;
+    for (int i = prt; i < HW; i += kPoolParts) {
+      const uint4 v = __ldcg(p + (long long)i * C8);
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { s[2 * j] += bf16_lo(u[j]); s[2 * j + 1] += bf16_hi(u[j]); }
+      for (int j = 0; j < 4; ++j) { s[2 * j] += bf16_lo(u[j]); s[2 * j + 1] += bf16_hi(u[j]); }
+    }
   }
-  const float inv = 1.0f / (float)HW;
-  float4* o = reinterpret_cast<float4*>(out + (long long)n * C8 * 8 + c8 * 8);
-  o[0] = make_float4(s[0] * inv, s[1] * inv, s[2] * inv, s[3] * inv);
-  o[1] = make_float4(s[4] * inv, s[5] * inv, s[6] * inv, s[7] * inv);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[prt][lane][j] = s[j];
+  __syncthreads();
+  // 256 sums to finish: thread t < 256 -> (lane t/8, channel t%8)
+  for (int t = threadIdx.x; t < 256; t += 32 * kPoolParts) {
+    const int l = t >> 3, j = t & 7;
+    float a = 0.f;
+#pragma unroll
+    for (int q = 0; q < kPoolParts; ++q) a += part[q][l][j];
+    const int cc = (blockIdx.x * 32 + l) * 8 + j;
+    if (cc < C8 * 8) out[(long long)n * C8 * 8 + cc] = a * (1.0f / (float)HW);
+  }
 }
 
 // ---------------------------------------------------------------------------------------
-// FC: logits[n][k] = bias[k] + sum_c pooled[n][c] * W[k][c]   (W bf16 [classes][C])
-// CTA = 8 warps = 8 classes x up to 8 images whose pooled vectors sit in shared memory.
+// FC: logits[n][k] = bias[k] + sum_c pooled[n][c] * W[k][c]   (W bf16 [classes][C], fp32 math)
+// CTA = 4 warps x 2 classes = 8 classes, all images.  A lane keeps its share of the two weight
+// rows in registers (k = i*128 + lane*4 .. +3), pooled vectors pass through shared memory
+// kFcImgs at a time as conflict-free 16-byte loads, warp-shuffle reduction per (class, image).
 // ---------------------------------------------------------------------------------------
 constexpr int kFcImgs = 8;
-__global__ void __launch_bounds__(256)
-fc_kernel(const float* __restrict__ pooled, const uint4* __restrict__ w, const float* __restrict__ bias,
+constexpr int kFcMaxC = 2048;
+__global__ void __launch_bounds__(128)
+fc_kernel(const float* __restrict__ pooled, const bf16* __restrict__ w, const float* __restrict__ bias,
           float* __restrict__ logits, int N, int C, int classes) {
-  extern __shared__ float x_s[];  // [kFcImgs][C]
-  const int n0 = blockIdx.y * kFcImgs;
-  const int nimg = min(kFcImgs, N - n0);
-  for (int i = threadIdx.x; i < nimg * C; i += blockDim.x) x_s[i] = pooled[(long long)n0 * C + i];
-  __syncthreads();
+  extern __shared__ float4 x_s4[];  // [kFcImgs][C/4]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cls = blockIdx.x * 8 + warp;
-  if (cls >= classes) return;
-  float acc[kFcImgs];
+  const int cls0 = blockIdx.x * 8 + warp * 2;
+  const int c4 = C / 4;
+  const int iters = (c4 + 31) / 32;  // 4 weights per lane per iteration; the last one may be partial
+  float wr[2][kFcMaxC / 32];
 #pragma unroll
-  for (int i = 0; i < kFcImgs; ++i) acc[i] = 0.f;
-  const uint4* wr = w + (long long)cls * (C / 8);
-  for (int c8 = lane; c8 < C / 8; c8 += 32) {
-    const uint4 v = __ldg(wr + c8);
-    const uint32_t u[4] = {v.x, v.y, v.z, v.w};
-    float wf[8];
+  for (int q = 0; q < 2; ++q) {
+    const int cls = min(cls0 + q, classes - 1);
+    const uint2* row = reinterpret_cast<const uint2*>(w + (long long)cls * C);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { wf[2 * j] = bf16_lo(u[j]); wf[2 * j + 1] = bf16_hi(u[j]); }
-#pragma unroll
-    for (int i = 0; i < kFcImgs; ++i) {
-      if (i < nimg) {
-        const float* xp = x_s + i * C + c8 * 8;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i] = fmaf(wf[j], xp[j], acc[i]);
+    for (int i = 0; i < kFcMaxC / 128; ++i) {
+      wr[q][4 * i + 0] = wr[q][4 * i + 1] = wr[q][4 * i + 2] = wr[q][4 * i + 3] = 0.f;
+      if (i < iters && i * 32 + lane < c4) {
+        const uint2 v = __ldg(row + i * 32 + lane);
+        wr[q][4 * i + 0] = bf16_lo(v.x); wr[q][4 * i + 1] = bf16_hi(v.x);
+        wr[q][4 * i + 2] = bf16_lo(v.y); wr[q][4 * i + 3] = bf16_hi(v.y);
       }
     }
   }
+  const float b0 = bias[min(cls0, classes - 1)], b1 = bias[min(cls0 + 1, classes - 1)];
+  pdl_launch_dependents();  // the weights above are constants: loading them overlaps the pooling kernel
+  pdl_wait();
+  for (int n0 = 0; n0 < N; n0 += kFcImgs) {
+    const int nimg = min(kFcImgs, N - n0);
+    __syncthreads();
+    const float4* src = reinterpret_cast<const float4*>(pooled + (long long)n0 * C);
+    for (int i = threadIdx.x; i < nimg * c4; i += blockDim.x) x_s4[i] = __ldcg(src + i);
+    __syncthreads();
+    for (int im = 0; im < nimg; ++im) {
+      const float4* xp = x_s4 + im * c4 + lane;
+      float a0 = 0.f, a1 = 0.f;
 #pragma unroll
-  for (int i = 0; i < kFcImgs; ++i) {
-    float v = acc[i];
+      for (int i = 0; i < kFcMaxC / 128; ++i) {
+        if (i < iters && i * 32 + lane < c4) {
+          const float4 x = xp[i * 32];
+          a0 = fmaf(wr[0][4 * i], x.x, a0); a0 = fmaf(wr[0][4 * i + 1], x.y, a0);
+          a0 = fmaf(wr[0][4 * i + 2], x.z, a0); a0 = fmaf(wr[0][4 * i + 3], x.w, a0);
+          a1 = fmaf(wr[1][4 * i], x.x, a1); a1 = fmaf(wr[1][4 * i + 1], x.y, a1);
+          a1 = fmaf(wr[1][4 * i + 2], x.z, a1); a1 = fmaf(wr[1][4 * i + 3], x.w, a1);
+        }
+      }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0 && i < nimg) logits[(long long)(n0 + i) * classes + cls] = v + bias[cls];
+      for (int o = 16; o > 0; o >>= 1) {
+        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+      }
+      if (lane == 0) {
+        float* lrow = logits + (long long)(n0 + im) * classes;
+        if (cls0 < classes) lrow[cls0] = a0 + b0;
+        if (cls0 + 1 < classes) lrow[cls0 + 1] = a1 + b1;
+      }
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------
-// softmax + top-k (k <= 8): one warp per image.  Ties resolve to the lower class index,
-// matching a stable descending sort.
+// softmax + top-k (k <= 8): one 256-thread block per image.  Ties resolve to the lower class
+// index, matching a stable descending sort.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
-softmax_topk_kernel(const float* __restrict__ logits, int N, int classes, int topk,
-                    int32_t* __restrict__ top_idx, float* __restrict__ top_prob) {
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= N) return;
-  const float* z = logits + (long long)warp * classes;
+constexpr int kSmThreads = 256;
+constexpr int kSmMaxPerThread = 16;  // classes <= 4096
+
+__device__ __forceinline__ void better(float& bv, int& bi, float ov, int oi) {
+  if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+}
+
+__global__ void __launch_bounds__(kSmThreads)
+softmax_topk_kernel(const float* __restrict__ logits, int classes, int topk, int32_t* __restrict__ top_idx,
+                    float* __restrict__ top_prob) {
+  __shared__ float red_v[kSmThreads / 32];
+  __shared__ int red_i[kSmThreads / 32];
+  __shared__ int bc_i;
+  const int n = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_launch_dependents();
+  pdl_wait();
+  const float* z = logits + (long long)n * classes;
+  float v[kSmMaxPerThread];
   float mx = -INFINITY;
-  for (int i = lane; i < classes; i += 32) mx = fmaxf(mx, z[i]);
+#pragma unroll
+  for (int j = 0; j < kSmMaxPerThread; ++j) {
+    const int i = tid + j * kSmThreads;
+    v[j] = i < classes ? __ldcg(z + i) : -INFINITY;
+    mx = fmaxf(mx, v[j]);
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if (lane == 0) red_v[warp] = mx;
+  __syncthreads();
+  mx = red_v[0];
+#pragma unroll
+  for (int w = 1; w < kSmThreads / 32; ++w) mx = fmaxf(mx, red_v[w]);
+  __syncthreads();
   float sum = 0.f;
-  for (int i = lane; i < classes; i += 32) sum += expf(z[i] - mx);
+#pragma unroll
+  for (int j = 0; j < kSmMaxPerThread; ++j) sum += (tid + j * kSmThreads < classes) ? expf(v[j] - mx) : 0.f;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-  float prev_v = INFINITY;
-  int prev_i = -1;
+  if (lane == 0) red_v[warp] = sum;
+  __syncthreads();
+  sum = 0.f;
+#pragma unroll
+  for (int w = 0; w < kSmThreads / 32; ++w) sum += red_v[w];
   for (int t = 0; t < topk; ++t) {
-    // best (value, index) strictly after (prev_v, prev_i) in (value desc, index asc) order
     float bv = -INFINITY;
     int bi = 0x7fffffff;
-    for (int i = lane; i < classes; i += 32) {
-      const float v = z[i];
-      const bool after = (v < prev_v) || (v == prev_v && i > prev_i);
-      if (after && (v > bv || (v == bv && i < bi))) { bv = v; bi = i; }
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    for (int j = 0; j < kSmMaxPerThread; ++j) better(bv, bi, v[j], tid + j * kSmThreads);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      better(bv, bi, __shfl_xor_sync(0xffffffffu, bv, o), __shfl_xor_sync(0xffffffffu, bi, o));
+    __syncthreads();
+    if (lane == 0) { red_v[warp] = bv; red_i[warp] = bi; }
+    __syncthreads();
+    if (tid == 0) {
+      float fv = red_v[0];
+      int fi = red_i[0];
+#pragma unroll
+      for (int w = 1; w < kSmThreads / 32; ++w) better(fv, fi, red_v[w], red_i[w]);
+      bc_i = fi;
+      top_idx[(long long)n * topk + t] = fi;
+      top_prob[(long long)n * topk + t] = expf(fv - mx) / sum;
     }
-    if (lane == 0) {
-      top_idx[(long long)warp * topk + t] = bi;
-      top_prob[(long long)warp * topk + t] = expf(bv - mx) / sum;
-    }
-    prev_v = bv; prev_i = bi;
+    __syncthreads();
+    const int win = bc_i;  // remove the winner from its owner's registers
+#pragma unroll
+    for (int j = 0; j < kSmMaxPerThread; ++j)
+      if (tid + j * kSmThreads == win) v[j] = -INFINITY;
   }
 }
 
@@ -175,21 +253,29 @@ int launch_head(const void* in, int N, int HW, int C, const void* fc_w, const fl
                 int classes, float* pooled_scratch, float* logits, int32_t* top_idx, float* top_prob,
                 int topk, cudaStream_t stream) {
   AI4E_REQUIRE(in && fc_w && fc_b && pooled_scratch && logits, "head: null pointer");
-  AI4E_REQUIRE(N > 0 && HW > 0 && C % 8 == 0 && classes > 0, "head: bad geometry");
+  AI4E_REQUIRE(N > 0 && HW > 0 && classes > 0, "head: bad geometry");
+  AI4E_REQUIRE(C % 8 == 0 && C <= kFcMaxC, "head: C %d must be a multiple of 8 and <= %d", C, kFcMaxC);
+  AI4E_REQUIRE(classes <= kSmThreads * kSmMaxPerThread, "head: %d classes (max %d)", classes,
+               kSmThreads * kSmMaxPerThread);
   AI4E_REQUIRE(topk >= 0 && topk <= 8 && topk <= classes, "head: topk %d unsupported", topk);
-  avgpool_kernel<<<(N * (C / 8) + 255) / 256, 256, 0, stream>>>((const uint4*)in, pooled_scratch, N,
-                                                                HW, C / 8);
-  AI4E_CUDA_TRY(cudaGetLastError());
+  const int C8 = C / 8;
+  AI4E_CUDA_TRY(launch_pdl(avgpool_kernel, dim3((C8 + 31) / 32, N), dim3(32 * kPoolParts), 0, stream,
+                           (const uint4*)in, pooled_scratch, HW, C8));
   const size_t smem = (size_t)kFcImgs * C * sizeof(float);
-  AI4E_REQUIRE(smem <= 96 * 1024, "head: C %d too large", C);
-  AI4E_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((classes + 7) / 8, (N + kFcImgs - 1) / kFcImgs);
-  fc_kernel<<<grid, 256, smem, stream>>>(pooled_scratch, (const uint4*)fc_w, fc_b, logits, N, C, classes);
-  AI4E_CUDA_TRY(cudaGetLastError());
+  static unsigned long long attr_done = 0;
+  int dev = 0;
+  AI4E_CUDA_TRY(cudaGetDevice(&dev));
+  if (!(attr_done >> dev & 1ull)) {
+    AI4E_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kFcImgs * kFcMaxC * (int)sizeof(float)));
+    attr_done |= 1ull << dev;
+  }
+  AI4E_CUDA_TRY(launch_pdl(fc_kernel, dim3((classes + 7) / 8), dim3(128), smem, stream, (const float*)pooled_scratch,
+                           (const bf16*)fc_w, fc_b, logits, N, C, classes));
   if (topk > 0) {
     AI4E_REQUIRE(top_idx && top_prob, "head: null top-k outputs");
-    softmax_topk_kernel<<<(N * 32 + 127) / 128, 128, 0, stream>>>(logits, N, classes, topk, top_idx, top_prob);
-    AI4E_CUDA_TRY(cudaGetLastError());
+    AI4E_CUDA_TRY(launch_pdl(softmax_topk_kernel, dim3(N), dim3(kSmThreads), 0, stream, (const float*)logits, classes,
+                             topk, top_idx, top_prob));
   }
   return AI4E_OK;
 }

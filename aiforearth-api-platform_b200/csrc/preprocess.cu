@@ -56,6 +56,7 @@ preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chu
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * kChunkPix * C + C * 256 * 2);
 
   const int tid = threadIdx.x;
+  pdl_launch_dependents();  // the stem may start its prologue while this kernel streams
 #pragma unroll
   for (int c = 0; c < C; ++c) lut[c * 256 + tid] = norm_to_bf16((float)tid, p.mean[c], p.stdv[c]);
   if (tid == 0) {
