@@ -34,6 +34,7 @@
 #include "kernels.h"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace ai4e {
 
@@ -58,37 +59,58 @@ constexpr int kStemTaps = 4;
 constexpr int kStemSlabA = kBlockM * 16;  // 2 KiB
 constexpr int kStemKBlocks = 7;
 
-template <int BLOCK_N, bool kStem = false>
+// Stem, row mode (W % 16 == 0, at most 128 output columns): one tile = one output row.  The seven
+// input rows a row of outputs needs are fetched whole, each by one tiled TMA load of full
+// 128-byte lines (zero fill outside the image gives the padding), into plain row buffers where
+// 16-byte unit u holds super-pixel u - 8.  Output pixel q, tap t reads unit q + t + 6, so the A
+// operand of filter row r is that row buffer itself seen through an un-swizzled K-major
+// descriptor whose core matrices OVERLAP: 16 bytes from one GEMM row to the next (rows of a core
+// matrix), 16 bytes from one tap to the next (LBO), 128 bytes between 8-row groups (SBO).  The
+// im2col expansion happens in the tensor core's address generator; shared memory and L2 see
+// every input byte once per output row.  All 28 KiB of weights stay resident in shared memory.
+constexpr int kRowsMaxGroups = 18;                       // 128-byte groups per row buffer (W <= 256)
+constexpr int kRowsStage = 7 * kRowsMaxGroups * 128 + 256;  // 16 KiB incl. over-read slack
+constexpr int kModeGeneric = 0, kModeStemIm2col = 1, kModeStemRows = 2;
+
+template <int BLOCK_N, int kMode = kModeGeneric>
 struct IgemmCfg {
-  static constexpr int kAStage = kStem ? kStemTaps * kStemSlabA : kABytes;
-  static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : BLOCK_N * kBlockK * 2;
+  static constexpr bool kStem = kMode == kModeStemIm2col;
+  static constexpr bool kRows = kMode == kModeStemRows;
+  static constexpr int kAStage = kStem ? kStemTaps * kStemSlabA : kRows ? kRowsStage : kABytes;
+  static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : kRows ? 0 : BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kAStage + kBBytes;
-  static constexpr int kStages = kStem ? 8 : (BLOCK_N == 256) ? 3 : (BLOCK_N == 128 ? 5 : 6);
+  static constexpr int kResidentB = kRows ? kStemKBlocks * kStemTaps * BLOCK_N * 16 : 0;  // 28 KiB
+  static constexpr int kStages = kStem ? 8 : kRows ? 6 : (BLOCK_N == 256) ? 3 : (BLOCK_N == 128 ? 5 : 6);
   static constexpr int kTmemCols = 2 * BLOCK_N;  // 128 / 256 / 512: power of two >= 32
   static constexpr int kEpiBytes = 4 * kChunkBytes;  // 2 output staging tiles + 2 residual tiles
-  // 1024-byte alignment slack + stages + epilogue tiles + barriers (full, empty, tmem_full[2],
-  // tmem_empty[2], res_full[2]) + tmem ptr
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + (2 * kStages + 6) * 8 + 16;
+  // 1024-byte alignment slack + stages + resident weights + epilogue tiles + barriers (full, empty,
+  // tmem_full[2], tmem_empty[2], res_full[2], b_full) + tmem ptr
+  static constexpr int kSmemBytes =
+      1024 + kStages * kStageBytes + kResidentB + kEpiBytes + (2 * kStages + 7) * 8 + 16;
 };
 
-template <int BLOCK_N, bool kStem>
+template <int BLOCK_N, int kMode>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const IgemmParams p) {
-  using Cfg = IgemmCfg<BLOCK_N, kStem>;
+  using Cfg = IgemmCfg<BLOCK_N, kMode>;
+  constexpr bool kStem = Cfg::kStem;
+  constexpr bool kRows = Cfg::kRows;
   constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t epi_base = smem_base + kStages * Cfg::kStageBytes;  // [out0][out1][res0][res1]
+  const uint32_t bres_base = smem_base + kStages * Cfg::kStageBytes;  // resident weights (row-mode stem)
+  const uint32_t epi_base = bres_base + Cfg::kResidentB;              // [out0][out1][res0][res1]
   const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
   auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
   auto res_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 4 + s); };
-  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 6);
+  const uint32_t b_full_bar = bar_base + 8u * (2 * kStages + 6);
+  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 7);
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_addr - smem_u32(smem_raw)));
 
@@ -107,6 +129,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_init(tmem_empty_bar(s), kEpiThreads);
       mbar_init(res_full_bar(s), 1);
     }
+    mbar_init(b_full_bar, 1);
     tma_prefetch_desc(&tmap_out);
     if (p.residual) tma_prefetch_desc(&tmap_res);
     fence_mbar_init();
@@ -130,7 +153,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      if constexpr (kRows) {
+        // weights: 7 rows x 4 taps of [BLOCK_N][16 B] slabs, once per CTA
+        mbar_expect_tx(b_full_bar, Cfg::kResidentB);
+        for (int i = 0; i < kStemKBlocks * kStemTaps; ++i)
+          tma_load_2d(bres_base + i * BLOCK_N * 16, &tmap_b, b_full_bar, i * 8, 0);
+        for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+          const int n_img = tile / p.P;
+          const int y0 = (tile - n_img * p.P) * 2 - 3;
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
+          mbar_expect_tx(full_bar(stage), 7u * p.stem_rb);
+#pragma unroll
+          for (int r = 0; r < 7; ++r)  // group -1 = super-pixels -8..-1: zero padding by OOB fill
+            tma_load_4d(a_dst + r * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, y0 + r, n_img);
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+      for (int tile = blockIdx.x; !kRows && tile < p.num_tiles; tile += gridDim.x) {
         const int tile_n = tile % p.tiles_n;
         const int tile_m = tile / p.tiles_n;
         const int m0 = tile_m * kBlockM;
@@ -172,13 +212,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
+      if constexpr (kRows) mbar_wait(b_full_bar, 0);
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it & 1u;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(tmem_empty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        if constexpr (kRows) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+#pragma unroll
+          for (int r = 0; r < 7; ++r) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {  // taps (2h, 2h+1) = one K = 16 step
+              const uint64_t adesc = umma_smem_desc(a_addr + r * p.stem_rb + (6 + 2 * h) * 16, 16, 128, 0);
+              const uint64_t bdesc =
+                  umma_smem_desc(bres_base + (r * kStemTaps + 2 * h) * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
+              umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (r | h) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(empty_bar(stage));
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        for (int kb = 0; !kRows && kb < p.num_k_blocks; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
@@ -289,7 +347,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
         named_bar_sync(2, kEpiThreads);
         if (leader) {
-          tma_store_2d(&tmap_out, epi_base + b * kChunkBytes, n0 + c * kChunkN, m0);
+          if constexpr (kRows) tma_store_3d(&tmap_out, epi_base + b * kChunkBytes, 0, 0, tile);  // row `tile` of [N*P][Q][64]
+          else tma_store_2d(&tmap_out, epi_base + b * kChunkBytes, n0 + c * kChunkN, m0);
           bulk_commit_group();
           if (has_res && c + 2 < kChunks) {  // everyone is done reading res_buf[b]: refill it
             mbar_expect_tx(res_full_bar(b), kChunkBytes);
@@ -357,7 +416,8 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias;
   q.residual = (const bf16*)residual; q.out = (bf16*)out;
   plan->max_batch = N;
-  plan->is_stem = false;
+  plan->stem_mode = kModeGeneric;
+  q.stem_rb = 0;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint64_t ktot = (uint64_t)R * S * Cin;
@@ -404,6 +464,7 @@ void stem_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp) {
 }
 
 // `weight_sp` is the repacked [64][224] device tensor.  Output geometry as for any 7x7/2 pad 3.
+// Row mode when W % 16 == 0 and the output row fits one tile (W <= 256), else im2col mode.
 int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
                          const float* bias, int relu, void* out) {
   AI4E_REQUIRE(stem_supported(H, W, 4, 64, 7, 7, 2, 3), "conv(stem): unsupported input %dx%d", H, W);
@@ -414,15 +475,30 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "conv(stem): M too large");
   IgemmParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = 64; q.S = kStemTaps; q.stride = 2; q.pad = 3;
-  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks;
+  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks; q.stem_rb = 0;
   q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias; q.residual = nullptr; q.out = (bf16*)out;
   plan->max_batch = N;
-  plan->is_stem = true;
-  // input as [N][H][W/2][8]: 4 taps from super-pixel q-2, traversal stride 1 in W and 2 in H.
-  // lower corner {-2, -3}; upper corner = right/bottom padding - (taps - 1) = {1 - 3, 3 - 6}.
-  const int lower[2] = {-2, -3}, upper[2] = {-2, -3}, st[2] = {1, 2};
-  int rc = tmap_encode_im2col(&plan->tmap_a, in, N, H, W / 2, 8, lower, upper, st, 8, kBlockM,
-                              CU_TENSOR_MAP_SWIZZLE_NONE);
+  const bool rows = (W % 16 == 0) && Q <= kBlockM && !getenv("AI4E_B200_STEM_IM2COL");
+  plan->stem_mode = rows ? kModeStemRows : kModeStemIm2col;
+  const uint32_t es4[4] = {1, 1, 1, 1};
+  int rc;
+  if (rows) {
+    // input rows as [N][H][W/16 groups][64 elements]; the box is one row, `groups` x 128 bytes,
+    // starting one group left of the image (zero fill) so that unit u holds super-pixel u - 8
+    const int groups = (Q + 10 + 7) / 8;  // units 0 .. Q-1 + 3 + 6 must exist
+    AI4E_REQUIRE(groups <= kRowsMaxGroups, "conv(stem): row too wide");
+    q.stem_rb = groups * 128;
+    const uint64_t adims[4] = {64, (uint64_t)W / 16, (uint64_t)H, (uint64_t)N};
+    const uint64_t astr[3] = {128, (uint64_t)W * 8, (uint64_t)H * W * 8};
+    const uint32_t abox[4] = {64, (uint32_t)groups, 1, 1};
+    rc = tmap_encode_tiled(&plan->tmap_a, in, 4, adims, astr, abox, es4, CU_TENSOR_MAP_SWIZZLE_NONE);
+  } else {
+    // input as [N][H][W/2][8]: 4 taps from super-pixel q-2, traversal stride 1 in W and 2 in H.
+    // lower corner {-2, -3}; upper corner = right/bottom padding - (taps - 1) = {1 - 3, 3 - 6}.
+    const int lower[2] = {-2, -3}, upper[2] = {-2, -3}, st[2] = {1, 2};
+    rc = tmap_encode_im2col(&plan->tmap_a, in, N, H, W / 2, 8, lower, upper, st, 8, kBlockM,
+                            CU_TENSOR_MAP_SWIZZLE_NONE);
+  }
   if (rc) return rc;
   const uint32_t es[2] = {1, 1};
   const uint64_t wdims[2] = {(uint64_t)kStemKBlocks * 32, 64};
@@ -432,28 +508,35 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   plan->has_bn[0] = true;
   rc = tmap_encode_tiled(&plan->tmap_b[0], weight_sp, 2, wdims, wstr, wbox, es, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc) return rc;
-  const uint64_t odims[2] = {64, (uint64_t)N * P * Q};
-  const uint64_t ostr[1] = {64 * 2};
-  const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
-  rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
+  if (rows) {
+    const uint64_t odims[3] = {64, (uint64_t)Q, (uint64_t)N * P};
+    const uint64_t ostr[2] = {64 * 2, (uint64_t)Q * 64 * 2};
+    const uint32_t obox[3] = {(uint32_t)kChunkN, (uint32_t)Q, 1};
+    rc = tmap_encode_tiled(&plan->tmap_out, out, 3, odims, ostr, obox, es4, CU_TENSOR_MAP_SWIZZLE_128B);
+  } else {
+    const uint64_t odims[2] = {64, (uint64_t)N * P * Q};
+    const uint64_t ostr[1] = {64 * 2};
+    const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
+    rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
+  }
   if (rc) return rc;
   plan->tmap_res = plan->tmap_out;
   return AI4E_OK;
 }
 
-template <int BN, bool kStem>
+template <int BN, int kMode>
 static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const IgemmParams& prm, int grid,
                            cudaStream_t stream) {
   static unsigned long long attr_done = 0;  // bit per device
   int dev = 0;
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
   if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kStem>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN, kStem>::kSmemBytes));
+    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       IgemmCfg<BN, kMode>::kSmemBytes));
     attr_done |= 1ull << dev;
   }
-  AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kStem>, dim3(grid), dim3(kIgemmThreads),
-                           (size_t)IgemmCfg<BN, kStem>::kSmemBytes, stream, plan.tmap_a, tb, plan.tmap_out,
+  AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kMode>, dim3(grid), dim3(kIgemmThreads),
+                           (size_t)IgemmCfg<BN, kMode>::kSmemBytes, stream, plan.tmap_a, tb, plan.tmap_out,
                            plan.tmap_res, prm));
   return AI4E_OK;
 }
@@ -463,12 +546,19 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
                plan.max_batch);
   IgemmParams prm = plan.prm;
   const long long M = (long long)batch * prm.PQ;
-  if (plan.is_stem) {
+  if (plan.stem_mode == kModeStemRows) {
+    prm.M = (int)M;
+    prm.tiles_m = prm.num_tiles = batch * prm.P;  // one tile per output row
+    prm.tiles_n = 1;
+    return igemm_launch_bn<64, kModeStemRows>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()), stream);
+  }
+  if (plan.stem_mode == kModeStemIm2col) {
     prm.M = (int)M;
     prm.tiles_m = (int)((M + kBlockM - 1) / kBlockM);
     prm.tiles_n = 1;
     prm.num_tiles = prm.tiles_m;
-    return igemm_launch_bn<64, true>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()), stream);
+    return igemm_launch_bn<64, kModeStemIm2col>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()),
+                                                stream);
   }
   const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M);
   const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
@@ -479,9 +569,9 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
   prm.num_tiles = prm.tiles_m * prm.tiles_n;
   const int grid = std::min(prm.num_tiles, sm_count());
   switch (bn) {
-    case 64: return igemm_launch_bn<64, false>(plan, plan.tmap_b[bi], prm, grid, stream);
-    case 128: return igemm_launch_bn<128, false>(plan, plan.tmap_b[bi], prm, grid, stream);
-    default: return igemm_launch_bn<256, false>(plan, plan.tmap_b[bi], prm, grid, stream);
+    case 64: return igemm_launch_bn<64, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
+    case 128: return igemm_launch_bn<128, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
+    default: return igemm_launch_bn<256, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
   }
 }
 

@@ -29,6 +29,7 @@ struct IgemmParams {
   int num_k_blocks;
   int tiles_m, tiles_n, num_tiles;
   int relu;
+  int stem_rb;     // row-mode stem: bytes per input-row buffer in shared memory
   const float* bias;
   const bf16* residual;
   bf16* out;
@@ -42,7 +43,7 @@ struct IgemmPlan {
   bool has_bn[3];
   IgemmParams prm;        // everything but the batch-dependent fields
   int max_batch;
-  bool is_stem;           // 7x7/2 stem on super-pixels (see conv_igemm.cu)
+  int stem_mode;          // 0 generic conv; 1 stem via im2col super-pixels; 2 stem via row buffers
 };
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);

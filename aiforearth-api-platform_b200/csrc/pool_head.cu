@@ -123,6 +123,9 @@ fc_kernel(const float* __restrict__ pooled, const bf16* __restrict__ w, const fl
   const int cls0 = blockIdx.x * 8 + warp * 2;
   const int c4 = C / 4;
   const int iters = (c4 + 31) / 32;  // 4 weights per lane per iteration; the last one may be partial
+  // blockIdx.y splits the images so that several CTAs share an SM and hide each other's latency
+  const int n_per = (N + gridDim.y - 1) / gridDim.y;
+  const int n_begin = blockIdx.y * n_per, n_end = min(N, n_begin + n_per);
   float wr[2][kFcMaxC / 32];
 #pragma unroll
   for (int q = 0; q < 2; ++q) {
@@ -141,25 +144,27 @@ fc_kernel(const float* __restrict__ pooled, const bf16* __restrict__ w, const fl
   const float b0 = bias[min(cls0, classes - 1)], b1 = bias[min(cls0 + 1, classes - 1)];
   pdl_launch_dependents();  // the weights above are constants: loading them overlaps the pooling kernel
   pdl_wait();
-  for (int n0 = 0; n0 < N; n0 += kFcImgs) {
-    const int nimg = min(kFcImgs, N - n0);
+  for (int n0 = n_begin; n0 < n_end; n0 += kFcImgs) {
+    const int nimg = min(kFcImgs, n_end - n0);
     __syncthreads();
     const float4* src = reinterpret_cast<const float4*>(pooled + (long long)n0 * C);
     for (int i = threadIdx.x; i < nimg * c4; i += blockDim.x) x_s4[i] = __ldcg(src + i);
     __syncthreads();
     for (int im = 0; im < nimg; ++im) {
       const float4* xp = x_s4 + im * c4 + lane;
-      float a0 = 0.f, a1 = 0.f;
+      float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;  // four independent chains per class
 #pragma unroll
       for (int i = 0; i < kFcMaxC / 128; ++i) {
-        if (i < iters && i * 32 + lane < c4) {
-          const float4 x = xp[i * 32];
-          a0 = fmaf(wr[0][4 * i], x.x, a0); a0 = fmaf(wr[0][4 * i + 1], x.y, a0);
-          a0 = fmaf(wr[0][4 * i + 2], x.z, a0); a0 = fmaf(wr[0][4 * i + 3], x.w, a0);
-          a1 = fmaf(wr[1][4 * i], x.x, a1); a1 = fmaf(wr[1][4 * i + 1], x.y, a1);
-          a1 = fmaf(wr[1][4 * i + 2], x.z, a1); a1 = fmaf(wr[1][4 * i + 3], x.w, a1);
+        if (i < iters) {
+          // lanes past the end of a partial last iteration hold zero weights; clamp their address
+          const float4 x = xp[min(i * 32, c4 - 1 - lane)];
+          s0.x = fmaf(wr[0][4 * i], x.x, s0.x); s0.y = fmaf(wr[0][4 * i + 1], x.y, s0.y);
+          s0.z = fmaf(wr[0][4 * i + 2], x.z, s0.z); s0.w = fmaf(wr[0][4 * i + 3], x.w, s0.w);
+          s1.x = fmaf(wr[1][4 * i], x.x, s1.x); s1.y = fmaf(wr[1][4 * i + 1], x.y, s1.y);
+          s1.z = fmaf(wr[1][4 * i + 2], x.z, s1.z); s1.w = fmaf(wr[1][4 * i + 3], x.w, s1.w);
         }
       }
+      float a0 = (s0.x + s0.y) + (s0.z + s0.w), a1 = (s1.x + s1.y) + (s1.z + s1.w);
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         a0 += __shfl_xor_sync(0xffffffffu, a0, o);
@@ -270,7 +275,8 @@ int launch_head(const void* in, int N, int HW, int C, const void* fc_w, const fl
                                        kFcImgs * kFcMaxC * (int)sizeof(float)));
     attr_done |= 1ull << dev;
   }
-  AI4E_CUDA_TRY(launch_pdl(fc_kernel, dim3((classes + 7) / 8), dim3(128), smem, stream, (const float*)pooled_scratch,
+  const int img_split = N >= 32 ? 4 : (N >= 16 ? 2 : 1);
+  AI4E_CUDA_TRY(launch_pdl(fc_kernel, dim3((classes + 7) / 8, img_split), dim3(128), smem, stream, (const float*)pooled_scratch,
                            (const bf16*)fc_w, fc_b, logits, N, C, classes));
   if (topk > 0) {
     AI4E_REQUIRE(top_idx && top_prob, "head: null top-k outputs");

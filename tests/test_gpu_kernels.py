@@ -146,6 +146,9 @@ STEM_CASES = [
     (1, 256, 256, 4, 64, 7, 2, 3, False, False),  # land-cover chip size, no ReLU
     (2, 30, 50, 4, 64, 7, 2, 3, True, False),     # ragged: M = 2*15*25 = 750, rows wrap mid-tile
     (1, 8, 8, 4, 64, 7, 2, 3, True, False),       # tiny: M = 16
+    (2, 40, 64, 4, 64, 7, 2, 3, True, False),     # W % 16 == 0: row-buffer mode, 32 outputs per row
+    (1, 18, 16, 4, 64, 7, 2, 3, False, False),    # row mode, 8 outputs per row, rows mostly padding
+    (1, 64, 240, 4, 64, 7, 2, 3, True, False),    # row mode, 120 outputs per row
 ]
 
 
