@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libai4e_b200.so")
+LIB_PATH = os.environ.get("AI4E_B200_LIB") or os.path.join(_HERE, "libai4e_b200.so")  # env: A/B builds
 
 OK = 0
 ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM, ERR_STATE, ERR_TIMEOUT = -1, -2, -3, -4, -5, -6

@@ -24,7 +24,7 @@ NVCC_FLAGS = [
     "-std=c++17", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden", "-Xcompiler", "-Wall",
     "--expt-relaxed-constexpr",
-]
+] + os.environ.get("AI4E_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

@@ -43,7 +43,7 @@ constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kEpiWarps = 8;                              // two warps per TMEM lane quadrant
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kIgemmThreads = 64 + kEpiThreads;           // + TMA producer warp + MMA warp
+constexpr int kIgemmThreads = 64 + kEpiThreads + 32;      // + A-producer warp, MMA warp, B-producer warp
 constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kChunkN = 64;                               // epilogue works on 64 channels at a time
 constexpr int kChunkBytes = kBlockM * kChunkN * 2;        // 16 KiB: 128 rows x 128 bytes, swizzled
@@ -80,13 +80,23 @@ struct IgemmCfg {
   static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : kRows ? 0 : BLOCK_N * kBlockK * 2;
   static constexpr int kStageBytes = kAStage + kBBytes;
   static constexpr int kResidentB = kRows ? kStemKBlocks * kStemTaps * BLOCK_N * 16 : 0;  // 28 KiB
-  static constexpr int kStages = kStem ? 8 : kRows ? 6 : (BLOCK_N == 256) ? 3 : (BLOCK_N == 128 ? 5 : 6);
+  // The K loop is latency-bound (measured on B200: a pipeline slot takes ~3100 cycles to go round -
+  // TMA latency ~2150, MMAs + barrier wake-ups ~570, issue ~370 - against 128-512 cycles of MMA work),
+  // so throughput is proportional to the number of stages in flight: take every stage that fits.
+  static constexpr int kMaxStages = 12;
   static constexpr int kTmemCols = 2 * BLOCK_N;  // 128 / 256 / 512: power of two >= 32
-  static constexpr int kEpiBytes = 4 * kChunkBytes;  // 2 output staging tiles + 2 residual tiles
-  // 1024-byte alignment slack + stages + resident weights + epilogue tiles + barriers (full, empty,
-  // tmem_full[2], tmem_empty[2], res_full[2], b_full) + tmem ptr
-  static constexpr int kSmemBytes =
-      1024 + kStages * kStageBytes + kResidentB + kEpiBytes + (2 * kStages + 7) * 8 + 16;
+  // epilogue tiles: 2 output staging tiles, + 2 residual tiles only when the layer has a residual
+  __host__ __device__ static constexpr int epi_bytes(bool has_res) { return (has_res ? 4 : 2) * kChunkBytes; }
+  static constexpr int kBarBytes = (2 * kMaxStages + 7) * 8 + 16;  // full, empty, tmem_full/empty[2], res_full[2], b_full, tmem ptr
+  static constexpr int kSmemLimit = 227 * 1024;
+  __host__ __device__ static constexpr int stages(bool has_res) {
+    const int room = kSmemLimit - 1024 - kResidentB - epi_bytes(has_res) - kBarBytes;
+    const int n = room / kStageBytes;
+    return n > kMaxStages ? kMaxStages : n;
+  }
+  __host__ __device__ static constexpr int smem_bytes(bool has_res) {
+    return 1024 + stages(has_res) * kStageBytes + kResidentB + epi_bytes(has_res) + kBarBytes;
+  }
 };
 
 template <int BLOCK_N, int kMode>
@@ -97,20 +107,21 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   using Cfg = IgemmCfg<BLOCK_N, kMode>;
   constexpr bool kStem = Cfg::kStem;
   constexpr bool kRows = Cfg::kRows;
-  constexpr int kStages = Cfg::kStages;
+  const int kStages = Cfg::stages(p.residual != nullptr);  // runtime: depends on the epilogue's needs
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bres_base = smem_base + kStages * Cfg::kStageBytes;  // resident weights (row-mode stem)
   const uint32_t epi_base = bres_base + Cfg::kResidentB;              // [out0][out1][res0][res1]
-  const uint32_t bar_base = epi_base + Cfg::kEpiBytes;
+  const uint32_t bar_base = epi_base + Cfg::epi_bytes(p.residual != nullptr);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-  auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
-  auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
-  auto res_full_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 4 + s); };
-  const uint32_t b_full_bar = bar_base + 8u * (2 * kStages + 6);
-  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kStages + 7);
+  constexpr int kMS = Cfg::kMaxStages;
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kMS + s); };
+  auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kMS + s); };
+  auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kMS + 2 + s); };
+  auto res_full_bar = [&](int s) { return bar_base + 8u * (2 * kMS + 4 + s); };
+  const uint32_t b_full_bar = bar_base + 8u * (2 * kMS + 6);
+  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kMS + 7);
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_addr - smem_u32(smem_raw)));
 
@@ -121,7 +132,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(full_bar(s), 1);
+      mbar_init(full_bar(s), kMode == kModeGeneric ? 2 : 1);  // generic: A and B come from two producers
       mbar_init(empty_bar(s), 1);
     }
     for (int s = 0; s < 2; ++s) {
@@ -150,23 +161,30 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
-    if (lane == 0) {
+    // (whole warp convergent, one elected lane issues - see the MMA warp)
+    {
       int stage = 0;
       uint32_t phase = 0;
       if constexpr (kRows) {
         // weights: 7 rows x 4 taps of [BLOCK_N][16 B] slabs, once per CTA
-        mbar_expect_tx(b_full_bar, Cfg::kResidentB);
-        for (int i = 0; i < kStemKBlocks * kStemTaps; ++i)
-          tma_load_2d(bres_base + i * BLOCK_N * 16, &tmap_b, b_full_bar, i * 8, 0);
+        if (elect_one()) {
+          mbar_expect_tx(b_full_bar, Cfg::kResidentB);
+          for (int i = 0; i < kStemKBlocks * kStemTaps; ++i)
+            tma_load_2d(bres_base + i * BLOCK_N * 16, &tmap_b, b_full_bar, i * 8, 0);
+        }
+        __syncwarp();
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
           const int n_img = tile / p.P;
           const int y0 = (tile - n_img * p.P) * 2 - 3;
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
-          mbar_expect_tx(full_bar(stage), 7u * p.stem_rb);
+          if (elect_one()) {
+            mbar_expect_tx(full_bar(stage), 7u * p.stem_rb);
 #pragma unroll
-          for (int r = 0; r < 7; ++r)  // group -1 = super-pixels -8..-1: zero padding by OOB fill
-            tma_load_4d(a_dst + r * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, y0 + r, n_img);
+            for (int r = 0; r < 7; ++r)  // group -1 = super-pixels -8..-1: zero padding by OOB fill
+              tma_load_4d(a_dst + r * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, y0 + r, n_img);
+          }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -185,29 +203,57 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
-          const uint32_t b_dst = a_dst + Cfg::kAStage;
-          mbar_expect_tx(full_bar(stage), Cfg::kStageBytes);
-          if constexpr (kStem) {
-            // K block kb = filter row; one im2col load per super-pixel tap, one weight slab each
+          [[maybe_unused]] const uint32_t b_dst = a_dst + Cfg::kAStage;
+          // generic mode: this warp brings A only; the B tile comes from the B-producer warp
+          if (elect_one()) {
+            mbar_expect_tx(full_bar(stage), kMode == kModeGeneric ? Cfg::kAStage : Cfg::kStageBytes);
+            if constexpr (kStem) {
+              // K block kb = filter row; one im2col load per super-pixel tap, one weight slab each
 #pragma unroll
-            for (int t = 0; t < kStemTaps; ++t) {
-              tma_load_im2col_4d(a_dst + t * kStemSlabA, &tmap_a, full_bar(stage), 0, w_base, h_base, n_img,
-                                 (uint16_t)t, (uint16_t)kb);
-              tma_load_2d(b_dst + t * BLOCK_N * 16, &tmap_b, full_bar(stage), kb * 32 + t * 8, tile_n * BLOCK_N);
+              for (int t = 0; t < kStemTaps; ++t) {
+                tma_load_im2col_4d(a_dst + t * kStemSlabA, &tmap_a, full_bar(stage), 0, w_base, h_base, n_img,
+                                   (uint16_t)t, (uint16_t)kb);
+                tma_load_2d(b_dst + t * BLOCK_N * 16, &tmap_b, full_bar(stage), kb * 32 + t * 8, tile_n * BLOCK_N);
+              }
+            } else {
+              tma_load_im2col_4d(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
+                                 (uint16_t)s, (uint16_t)r);
             }
-          } else {
-            tma_load_im2col_4d(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
-                               (uint16_t)s, (uint16_t)r);
-            tma_load_2d(b_dst, &tmap_b, full_bar(stage), kb * kBlockK, tile_n * BLOCK_N);
+          }
+          __syncwarp();
+          if constexpr (!kStem) {
             if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
     }
+  } else if (warp == 2 + kEpiWarps) {
+    // ------------------------------- B (weights) producer, generic mode ----------
+    // One thread needs ~190 cycles per TMA instruction and ~615 per stage for wait + expect_tx +
+    // two loads (clock64 trace, B200): longer than a stage's MMAs.  Two threads halve that.
+    if (kMode == kModeGeneric) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int n0 = (tile % p.tiles_n) * BLOCK_N;
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
+            tma_load_2d(smem_base + stage * Cfg::kStageBytes + Cfg::kAStage, &tmap_b, full_bar(stage), kb * kBlockK, n0);
+          }
+          __syncwarp();
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
   } else if (warp == 1) {
     // ------------------------------- MMA issuer ---------------------------------
-    if (lane == 0) {
+    // The whole warp runs this loop convergently and one elected lane issues: every operand is then
+    // provably warp-uniform and the compiler feeds tcgen05.mma straight from uniform registers.
+    // (Under `if (lane == 0)` it wraps each MMA in a per-lane "waterfall" loop of ~12 instructions.)
+    {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM, BLOCK_N);
       int stage = 0;
       uint32_t phase = 0;
@@ -223,49 +269,56 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+          if (elect_one()) {
 #pragma unroll
-          for (int r = 0; r < 7; ++r) {
+            for (int r = 0; r < 7; ++r) {
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {  // taps (2h, 2h+1) = one K = 16 step
-              const uint64_t adesc = umma_smem_desc(a_addr + r * p.stem_rb + (6 + 2 * h) * 16, 16, 128, 0);
-              const uint64_t bdesc =
-                  umma_smem_desc(bres_base + (r * kStemTaps + 2 * h) * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
-              umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (r | h) != 0 ? 1u : 0u);
+              for (int h = 0; h < 2; ++h) {  // taps (2h, 2h+1) = one K = 16 step
+                const uint64_t adesc = umma_smem_desc(a_addr + r * p.stem_rb + (6 + 2 * h) * 16, 16, 128, 0);
+                const uint64_t bdesc =
+                    umma_smem_desc(bres_base + (r * kStemTaps + 2 * h) * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
+                umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (r | h) != 0 ? 1u : 0u);
+              }
             }
+            umma_commit(empty_bar(stage));
           }
-          umma_commit(empty_bar(stage));
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
         for (int kb = 0; !kRows && kb < p.num_k_blocks; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
-          if constexpr (kStem) {
-            // un-swizzled slabs: one MMA (K = 16) spans two slabs; LBO = slab size, SBO = 128 bytes
+          if (elect_one()) {
+            if constexpr (kStem) {
+              // un-swizzled slabs: one MMA (K = 16) spans two slabs; LBO = slab size, SBO = 128 bytes
 #pragma unroll
-            for (int k = 0; k < kStemTaps / 2; ++k) {
-              const uint64_t adesc = umma_smem_desc(a_addr + 2 * k * kStemSlabA, kStemSlabA, 128, 0);
-              const uint64_t bdesc =
-                  umma_smem_desc(a_addr + Cfg::kAStage + 2 * k * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
-              umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
-          } else {
-            const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
-            const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
+              for (int k = 0; k < kStemTaps / 2; ++k) {
+                const uint64_t adesc = umma_smem_desc(a_addr + 2 * k * kStemSlabA, kStemSlabA, 128, 0);
+                const uint64_t bdesc =
+                    umma_smem_desc(a_addr + Cfg::kAStage + 2 * k * BLOCK_N * 16, BLOCK_N * 16, 128, 0);
+                umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              }
+            } else {
+              const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
+              const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-              // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
-              // +2 in the (addr >> 4) start-address field
-              umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) {
+                // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
+                // +2 in the (addr >> 4) start-address field
+                umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              }
             }
+            umma_commit(empty_bar(stage));  // smem stage reusable once these MMAs retire
           }
-          umma_commit(empty_bar(stage));  // smem stage reusable once these MMAs retire
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tmem_full_bar(acc));  // accumulator complete -> epilogue
+        if (elect_one()) umma_commit(tmem_full_bar(acc));  // accumulator complete -> epilogue
+        __syncwarp();
       }
     }
-  } else {
+  } else if (warp < 2 + kEpiWarps) {
     // ------------------------------- epilogue -----------------------------------
     // Eight warps: warp pair (w, w+4) shares TMEM lane quadrant w % 4 (= rows 32*quad..+31 of the
     // tile); within every 64-channel chunk the first warp of the pair takes channels 0-31, the
@@ -532,11 +585,12 @@ static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const I
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
   if (!(attr_done >> dev & 1ull)) {
     AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN, kMode>::kSmemBytes));
+                                       IgemmCfg<BN, kMode>::smem_bytes(false)));
     attr_done |= 1ull << dev;
   }
   AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kMode>, dim3(grid), dim3(kIgemmThreads),
-                           (size_t)IgemmCfg<BN, kMode>::kSmemBytes, stream, plan.tmap_a, tb, plan.tmap_out,
+                           (size_t)IgemmCfg<BN, kMode>::smem_bytes(prm.residual != nullptr), stream, plan.tmap_a, tb,
+                           plan.tmap_out,
                            plan.tmap_res, prm));
   return AI4E_OK;
 }

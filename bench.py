@@ -102,6 +102,14 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def workload_config(batch: int, replicas: int) -> dict:
+    """the `config` object both arms print (the reference arm runs the same workload on the CPU)."""
+    return {"workload": f"ResNet-50 bf16 classification, micro-batch {batch}, synthetic 224x224 RGB, one replica per GPU",
+            "batch": batch, "replicas": replicas, "parallelism": f"{replicas} independent replica(s), no collective",
+            "l2": f"{POOL_BATCHES} distinct input batches rotated ({POOL_BATCHES * batch * HW * HW * IN_C / 1e6:.0f} MB > 126 MB L2); "
+                  f"activations of one step ({batch * 43.6:.0f} MB) exceed L2 as well"}
+
+
 def noise_batches(n_batches: int, batch: int, seed: int = 1234) -> np.ndarray:
     rng = np.random.default_rng(seed)
     return rng.integers(0, 256, (n_batches, batch, HW, HW, IN_C), dtype=np.uint8)
@@ -144,7 +152,7 @@ def run_reference(args, rank: int):
         "impl": "reference", "metric": "images/sec end-to-end (preprocess+classify)", "value": v, "unit": "images/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"ResNet-50 224x224 classification, micro-batch {args.batch}, CPU oracle", "batch": args.batch},
+        "config": workload_config(args.batch, max(args.gpus, 1)),
         "cpu_baseline": {"value": v, "unit": "images/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
@@ -292,10 +300,7 @@ def main():
         "metric": "images/sec end-to-end (preprocess+classify)", "value": value, "unit": "images/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_dev / K, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"ResNet-50 bf16 classification, micro-batch {B}, synthetic 224x224 RGB, one replica per GPU",
-                   "batch": B, "replicas": world, "parallelism": f"{world} independent replica(s), no collective",
-                   "l2": f"{POOL_BATCHES} distinct input batches rotated ({POOL_BATCHES * B * HW * HW * IN_C / 1e6:.0f} MB > 126 MB L2); "
-                         f"activations of one step ({B * 43.6:.0f} MB) exceed L2 as well"},
+        "config": workload_config(B, world),
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": B * HW * HW * IN_C,
                 "d2h_bytes_per_step": B * (5 * 4 + 5 * 4 + prog.num_classes * 4),
                 "api": "Engine.submit_batch/wait, page-locked host batches, 3 batches in flight"},

@@ -193,6 +193,12 @@ IGEMM_CASES = [
     (5, 13, 17, 128, 192, 3, 2, 1, True, True),   # odd sizes, Cout = 3 x 64
     (1, 64, 64, 64, 128, 3, 1, 1, True, False),   # M = 4096: exact multiple of 128
     (2, 8, 8, 64, 64, 1, 1, 0, False, False),     # M = 128: exactly one tile
+    # big enough that the wide tiles are chosen (>= 148 tiles at BLOCK_N = 256 / 128) and every
+    # pipeline stage and mbarrier phase wraps several times per CTA
+    (8, 56, 56, 64, 256, 1, 1, 0, True, True),    # BLOCK_N = 256, 3 stages, K = 64
+    (7, 56, 56, 64, 256, 3, 1, 1, True, False),   # BLOCK_N = 256, 9 K blocks over 3 stages
+    (8, 56, 56, 256, 128, 1, 1, 0, True, False),  # BLOCK_N = 128, 5 stages, 4 K blocks
+    (6, 56, 56, 128, 256, 3, 1, 1, True, True),   # BLOCK_N = 128, 18 K blocks
 ]
 
 
