@@ -4,6 +4,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <cstdio>
+#include <cstdlib>
 #include <vector>
 
 using namespace ai4e;
@@ -74,6 +76,25 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   int rc = igemm_make_plan(&plan, d_in_nhwc, batch, h, w, cin, d_weight_krsc, d_bias, cout, kh, kw,
                            stride, pad, d_residual_or_null, relu, d_out_nhwc);
   if (rc) return rc;
+  if (const char* trace = getenv("AI4E_B200_PIPE_TRACE")) {  // developer aid: dump CTA 0's pipeline timestamps
+    long long* d = nullptr;
+    AI4E_CUDA_TRY(cudaMalloc((void**)&d, 1024 * sizeof(long long)));
+    AI4E_CUDA_TRY(cudaMemset(d, 0, 1024 * sizeof(long long)));
+    plan.prm.dbg = d;
+    rc = igemm_launch(plan, batch, 0, (cudaStream_t)stream);
+    AI4E_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    std::vector<long long> h(1024);
+    AI4E_CUDA_TRY(cudaMemcpy(h.data(), d, 1024 * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    if (FILE* f = fopen(trace, "w")) {  // columns: slot free, A issued (producer) | data seen, MMAs issued (MMA warp)
+      for (int i = 0; i < 192; ++i) fprintf(f, "%d %lld %lld %lld %lld\n", i, h[i], h[192 + i], h[384 + i], h[576 + i]);
+      for (int i = 0; i < 40; ++i)  // epilogue leader, per 64-channel chunk
+        fprintf(f, "E %d %lld %lld %lld %lld %lld %lld\n", i, h[768 + 6 * i], h[769 + 6 * i], h[770 + 6 * i], h[771 + 6 * i],
+                h[772 + 6 * i], h[773 + 6 * i]);
+      fclose(f);
+    }
+    return rc;
+  }
   return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 

@@ -182,6 +182,12 @@ __device__ __forceinline__ void tma_load_im2col_4d_mc(uint32_t dst, const void* 
       "h"(off_w), "h"(off_h), "h"(mask)
       : "memory");
 }
+// L2 prefetch of a 2-D tile (no shared-memory destination, no completion signal)
+__device__ __forceinline__ void tma_prefetch_l2_2d(const void* tmap, int x, int y) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(x), "r"(y)
+               : "memory");
+}
 // 2-D tile shared -> global (bulk async group); rows/columns outside the tensor are clipped
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int x, int y) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"

@@ -33,6 +33,15 @@
 #include "common.cuh"
 #include "kernels.h"
 
+// Developer aid: -DAI4E_PIPE_TRACE makes CTA 0 record clock64 stamps of its pipeline into
+// IgemmParams::dbg (dumped by ai4e_conv_layer when AI4E_B200_PIPE_TRACE=<file> is set).  Compiled out
+// by default: even the dormant `if (p.dbg ...)` checks cost 5 % of the convolution time.
+#ifdef AI4E_PIPE_TRACE
+#define AI4E_TRACE(cond, slot) do { if (p.dbg && blockIdx.x == 0 && (cond)) p.dbg[(slot)] = clock64(); } while (0)
+#else
+#define AI4E_TRACE(cond, slot) do { } while (0)
+#endif
+
 #include <algorithm>
 #include <cstdlib>
 
@@ -165,6 +174,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     {
       int stage = 0;
       uint32_t phase = 0;
+      [[maybe_unused]] int ptrace = 0;
       if constexpr (kRows) {
         // weights: 7 rows x 4 taps of [BLOCK_N][16 B] slabs, once per CTA
         if (elect_one()) {
@@ -202,6 +212,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         [[maybe_unused]] int r = 0, s = 0, cb = 0;
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
+          AI4E_TRACE(lane == 0 && ptrace < 192, ptrace);  // slot free
           const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
           [[maybe_unused]] const uint32_t b_dst = a_dst + Cfg::kAStage;
           // generic mode: this warp brings A only; the B tile comes from the B-producer warp
@@ -221,6 +232,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
           }
           __syncwarp();
+          AI4E_TRACE(lane == 0 && ptrace < 192, 192 + ptrace); ++ptrace;  // A issued
           if constexpr (!kStem) {
             if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
           }
@@ -258,6 +270,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
+      [[maybe_unused]] int mtrace = 0;
       if constexpr (kRows) mbar_wait(b_full_bar, 0);
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
         const uint32_t acc = it & 1u;
@@ -287,6 +300,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         for (int kb = 0; !kRows && kb < p.num_k_blocks; ++kb) {
           mbar_wait(full_bar(stage), phase);
+          // (the two trace stores cost ~140 cycles per K block: traced periods overstate the loop)
+          AI4E_TRACE(lane == 0 && mtrace < 192, 384 + mtrace);  // data seen
           tc_fence_after();
           const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
           if (elect_one()) {
@@ -312,6 +327,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             umma_commit(empty_bar(stage));  // smem stage reusable once these MMAs retire
           }
           __syncwarp();
+          AI4E_TRACE(lane == 0 && mtrace < 192, 576 + mtrace); ++mtrace;  // MMAs issued
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
         if (elect_one()) umma_commit(tmem_full_bar(acc));  // accumulator complete -> epilogue
@@ -351,6 +367,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_expect_tx(res_full_bar(b), kChunkBytes);
           tma_load_2d(epi_base + (2 + b) * kChunkBytes, &tmap_res, res_full_bar(b), n0 + c * kChunkN, m0);
         }
+        // The residual was written three layers ago and has usually left L2; a chunk's load is
+        // only issued two chunks (~2000 cycles) ahead, less than a loaded DRAM round trip (the
+        // epilogue trace showed stalls of 1000-3000 cycles on res_full).  Pull the NEXT tile's
+        // residual into L2 now, a whole tile ahead.
+        const int ntile = tile + gridDim.x;
+#ifndef AI4E_NO_RES_PREFETCH
+        if (ntile < p.num_tiles) {
+          const int nm0 = (ntile / p.tiles_n) * kBlockM, nn0 = (ntile % p.tiles_n) * BLOCK_N;
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c) tma_prefetch_l2_2d(&tmap_res, nn0 + c * kChunkN, nm0);
+        }
+#else
+        (void)ntile;
+#endif
       }
       mbar_wait(tmem_full_bar(acc), acc_phase);
       tc_fence_after();
@@ -360,6 +390,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const uint32_t b = chunk_seq & 1u;
         uint8_t* const out_gen = smem_gen + b * kChunkBytes;
         const uint8_t* const res_gen = smem_gen + (2 + b) * kChunkBytes;
+        [[maybe_unused]] const bool etr = leader && chunk_seq < 40;
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 0);  // chunk start (tile's accumulator ready)
         uint32_t v[32];
         tmem_ld_32x32b_x32(t_addr + c * kChunkN, v);
         float4 bias[8];
@@ -370,7 +402,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         // the TMA store that last read this staging tile (two chunks ago) must be done with it
         if (leader) bulk_wait_group_read<1>();
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 1);  // staging tile free
         named_bar_sync(1, kEpiThreads);
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 2);  // barrier 1 passed
         uint4 r[4];
         if (has_res) {
           mbar_wait(res_full_bar(b), (chunk_seq >> 1) & 1u);
@@ -378,6 +412,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           for (int j = 0; j < 4; ++j) r[j] = *reinterpret_cast<const uint4*>(res_gen + unit_off[j]);
         }
         tmem_wait_ld();
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 3);  // accumulators (and residual) in registers
 #pragma unroll
         for (int j = 0; j < 4; ++j) {  // 8 channels = one 16-byte unit of the swizzled row
           float x[8];
@@ -398,7 +433,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                          pack_bf16x2(x[6], x[7]));
         }
         fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 4);  // staged
         named_bar_sync(2, kEpiThreads);
+        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 5);  // barrier 2 passed
         if (leader) {
           if constexpr (kRows) tma_store_3d(&tmap_out, epi_base + b * kChunkBytes, 0, 0, tile);  // row `tile` of [N*P][Q][64]
           else tma_store_2d(&tmap_out, epi_base + b * kChunkBytes, n0 + c * kChunkN, m0);
@@ -470,7 +507,7 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   q.residual = (const bf16*)residual; q.out = (bf16*)out;
   plan->max_batch = N;
   plan->stem_mode = kModeGeneric;
-  q.stem_rb = 0;
+  q.stem_rb = 0; q.dbg = nullptr;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint64_t ktot = (uint64_t)R * S * Cin;
@@ -528,7 +565,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "conv(stem): M too large");
   IgemmParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = 64; q.S = kStemTaps; q.stride = 2; q.pad = 3;
-  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks; q.stem_rb = 0;
+  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks; q.stem_rb = 0; q.dbg = nullptr;
   q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias; q.residual = nullptr; q.out = (bf16*)out;
   plan->max_batch = N;
   const bool rows = (W % 16 == 0) && Q <= kBlockM && !getenv("AI4E_B200_STEM_IM2COL");

@@ -30,6 +30,7 @@ struct IgemmParams {
   int tiles_m, tiles_n, num_tiles;
   int relu;
   int stem_rb;     // row-mode stem: bytes per input-row buffer in shared memory
+  long long* dbg;  // developer aid: clock64 stamps of CTA 0's pipeline (768 slots), null in production
   const float* bias;
   const bf16* residual;
   bf16* out;

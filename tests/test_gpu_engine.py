@@ -170,3 +170,70 @@ def test_pool_two_replicas_one_gpu():
             assert np.array_equal(p.wait(t)[0], g["top5_idx"][i % 8])
         per = [s["images"] for s in p.stats()]
         assert sum(per) == 24 and all(v > 0 for v in per), per
+
+
+def test_landcover_tile_pipeline():
+    """configs[3] in small: a 512x768x4 tile -> 6 chips of 256x256x4 -> per-chip top-5, equal to the
+    engine's own batch forward on the copied chips and (for the golden chips) to the oracle."""
+    from ai4e_b200.landcover import classify_tile
+    g, imgs = util.load_golden("resnet50_landcover4")
+    tile = np.zeros((512, 768, 4), np.uint8)
+    k = 0
+    for r in range(2):
+        for c in range(3):
+            tile[r * 256:(r + 1) * 256, c * 256:(c + 1) * 256] = imgs[k]
+            k += 1
+    with _engine("resnet50", in_ch=4, hw=256, max_batch=4, max_wait_us=500) as e:
+        cls, idx, prob = classify_tile(e, tile)
+        assert cls.shape == (2, 3) and idx.shape == (2, 3, 5)
+        assert np.array_equal(idx.reshape(6, 5), g["top5_idx"][:6])
+        assert np.allclose(prob.reshape(6, 5), g["top5_prob"][:6], atol=2e-4, rtol=3e-2)
+
+
+def test_async_endpoint_drives_the_engine():
+    """configs[2] in small: the drop-in `APIService` async endpoint + in-process task store + engine.
+    32 tasks are posted with a taskId header; worker threads block in engine.classify, the
+    micro-batcher groups them, every task ends 'completed' with the golden top-5."""
+    import json
+    import time
+    from ai4e_service import APIService
+    from task_management.api_task import TaskManager
+    from task_management.local_task_store import LocalTaskStore
+    try:
+        from flask import Flask
+    except ImportError:
+        from ai4e_b200.compat.miniflask import Flask
+    g, imgs = util.load_golden("resnet18")
+    app = Flask("svc")
+    store = LocalTaskStore()
+    svc = APIService(app, type("L", (), {"tracer": None, "log_exception": lambda *a, **k: None})())
+    svc.api_task_manager = TaskManager(store=store)
+    with _engine("resnet18", max_batch=16, max_wait_us=3000) as e:
+        @svc.api_async_func(api_path="/classify", methods=["POST"], maximum_concurrent_requests=64,
+                            content_types=["application/octet-stream"],
+                            request_processing_function=lambda request: {
+                                "image": np.frombuffer(request.get_data(), np.uint8).reshape(224, 224, 3)})
+        def classify(*args, **kwargs):
+            tid = kwargs["taskId"]
+            svc.api_task_manager.UpdateTaskStatus(tid, "running")
+            idx, prob = e.classify(kwargs["image"])
+            svc.api_task_manager.CompleteTask(tid, "completed - " + json.dumps({"top5": idx.tolist()}))
+
+        client = app.test_client()
+        tasks = []
+        for i in range(32):
+            t = store.create_task("http://container/classify")
+            r = client.post("/classify", data=imgs[i % len(imgs)].tobytes(),
+                            headers={"taskId": t["TaskId"], "Content-Type": "application/octet-stream"})
+            assert r.get_data(as_text=True) == "TaskId: " + t["TaskId"]
+            tasks.append((t["TaskId"], i % len(imgs)))
+        deadline = time.time() + 30
+        while time.time() < deadline and len(store.set_members("/classify_completed")) < 32:
+            time.sleep(0.01)
+        assert len(store.set_members("/classify_completed")) == 32
+        for tid, k in tasks:
+            st = json.loads(store.get(tid)[1])
+            assert st["BackendStatus"] == "completed"
+            assert json.loads(st["Status"][len("completed - "):])["top5"] == g["top5_idx"][k].tolist()
+        hist = e.stats()["batch_hist"]
+        assert sum(hist[1:]) > 0, f"no batch larger than one image was formed: {hist}"
