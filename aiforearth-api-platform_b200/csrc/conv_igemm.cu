@@ -52,10 +52,11 @@ constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kUmmaK = 16;
 constexpr int kEpiWarps = 8;                              // two warps per TMEM lane quadrant
 constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kIgemmThreads = 64 + kEpiThreads + 32;      // + A-producer warp, MMA warp, B-producer warp
+constexpr int kIgemmThreads = 64 + kEpiThreads + 64;      // + A-producer warp, MMA warp, B-producer warp, residual warp
 constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
 constexpr int kChunkN = 64;                               // epilogue works on 64 channels at a time
 constexpr int kChunkBytes = kBlockM * kChunkN * 2;        // 16 KiB: 128 rows x 128 bytes, swizzled
+constexpr int kSliceBytes = 32 * kChunkN * 2;             // 4 KiB: one epilogue warp's 32 rows of a chunk
 
 // Stem (7x7 stride 2, 3/4 input channels -> 64): the NHWC4 image is read as an [H][W/2][8] grid
 // of "super-pixels" (two adjacent pixels = 8 channels = 16 bytes, the smallest unit im2col-mode
@@ -94,17 +95,19 @@ struct IgemmCfg {
   // so throughput is proportional to the number of stages in flight: take every stage that fits.
   static constexpr int kMaxStages = 12;
   static constexpr int kTmemCols = 2 * BLOCK_N;  // 128 / 256 / 512: power of two >= 32
-  // epilogue tiles: 2 output staging tiles, + 2 residual tiles only when the layer has a residual
-  __host__ __device__ static constexpr int epi_bytes(bool has_res) { return (has_res ? 4 : 2) * kChunkBytes; }
-  static constexpr int kBarBytes = (2 * kMaxStages + 7) * 8 + 16;  // full, empty, tmem_full/empty[2], res_full[2], b_full, tmem ptr
+  // epilogue: a 4 KB output staging slice and 256 bytes of bias per epilogue warp, + two 16 KB residual
+  // buffers per side when the layer has a residual
+  static constexpr int kEpiFixed = kEpiWarps * (kSliceBytes + kChunkN * 4);
+  __host__ __device__ static constexpr int epi_bytes(bool has_res) { return kEpiFixed + (has_res ? 4 * kChunkBytes : 0); }
+  static constexpr int kBarBytes = (2 * kMaxStages + 4 + 8 + 2) * 8 + 16;  // full, empty, tmem_full/empty[2], res_full/empty[4], b_full, tmem ptr
   static constexpr int kSmemLimit = 227 * 1024;
   __host__ __device__ static constexpr int stages(bool has_res) {
-    const int room = kSmemLimit - 1024 - kResidentB - epi_bytes(has_res) - kBarBytes;
+    const int room = kSmemLimit - kResidentB - epi_bytes(has_res) - kBarBytes;
     const int n = room / kStageBytes;
     return n > kMaxStages ? kMaxStages : n;
   }
   __host__ __device__ static constexpr int smem_bytes(bool has_res) {
-    return 1024 + stages(has_res) * kStageBytes + kResidentB + epi_bytes(has_res) + kBarBytes;
+    return stages(has_res) * kStageBytes + kResidentB + epi_bytes(has_res) + kBarBytes;
   }
 };
 
@@ -117,9 +120,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   constexpr bool kStem = Cfg::kStem;
   constexpr bool kRows = Cfg::kRows;
   const int kStages = Cfg::stages(p.residual != nullptr);  // runtime: depends on the epilogue's needs
-  extern __shared__ uint8_t smem_raw[];
-  // SWIZZLE_128B operand tiles need 1024-byte alignment
-  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  // SWIZZLE_128B operand tiles need 1024-byte alignment.  The kernel has no static shared memory, so
+  // the dynamic window starts at the CTA's shared base; the budget above has no slack for rounding up.
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = smem_u32(smem_raw);
+  if (smem_base & 1023u) __trap();
   const uint32_t bres_base = smem_base + kStages * Cfg::kStageBytes;  // resident weights (row-mode stem)
   const uint32_t epi_base = bres_base + Cfg::kResidentB;              // [out0][out1][res0][res1]
   const uint32_t bar_base = epi_base + Cfg::epi_bytes(p.residual != nullptr);
@@ -129,8 +134,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kMS + s); };
   auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kMS + 2 + s); };
   auto res_full_bar = [&](int s) { return bar_base + 8u * (2 * kMS + 4 + s); };
-  const uint32_t b_full_bar = bar_base + 8u * (2 * kMS + 6);
-  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kMS + 7);
+  auto res_empty_bar = [&](int s) { return bar_base + 8u * (2 * kMS + 8 + s); };  // res_full/empty: two per epilogue side
+  const uint32_t b_full_bar = bar_base + 8u * (2 * kMS + 12);
+  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kMS + 13);
   volatile uint32_t* tmem_ptr_gen =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_addr - smem_u32(smem_raw)));
 
@@ -146,8 +152,12 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);
-      mbar_init(tmem_empty_bar(s), kEpiThreads);
+      // one arrival per epilogue warp that reads the tile: a 64-wide tile is drained by one side
+      mbar_init(tmem_empty_bar(s), BLOCK_N == kChunkN ? 4 : kEpiWarps);
+    }
+    for (int s = 0; s < 4; ++s) {
       mbar_init(res_full_bar(s), 1);
+      mbar_init(res_empty_bar(s), 4);
     }
     mbar_init(b_full_bar, 1);
     tma_prefetch_desc(&tmap_out);
@@ -336,120 +346,149 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     }
   } else if (warp < 2 + kEpiWarps) {
     // ------------------------------- epilogue -----------------------------------
-    // Eight warps: warp pair (w, w+4) shares TMEM lane quadrant w % 4 (= rows 32*quad..+31 of the
-    // tile); within every 64-channel chunk the first warp of the pair takes channels 0-31, the
-    // second 32-63.  Two warps per scheduler hide the TMEM / shared-memory latencies.
+    // Eight independent warps, no block-level barriers.  A warp can read only its own TMEM lane
+    // quadrant (warp id % 4), so quadrant and "side" (warp - 2) / 4 identify it; the 64-channel
+    // chunks of the CTA's tiles, numbered q = tile_iteration * kChunks + c, alternate between the two
+    // sides.  Each warp owns a 32-row x 64-channel output staging slice which it stores with its own
+    // 4 KB TMA box; residual chunks (128 rows) arrive through the residual warp below.  Per chunk:
+    // accumulator load, arithmetic into packed registers, wait until the previous store has read
+    // the staging slice, STS, store.  Thread = one pixel row, 64 channels = one 128-byte swizzled row.
+    // The bias of the chunk is staged in a warp-private 256 bytes of shared memory: with 227 KB of
+    // the SM carved out as shared memory L1 is tiny, and sixteen serialised LDG.128 of the bias
+    // were most of the ~850-cycle arithmetic phase (pipeline trace, B200).
+    const int ew = warp - 2;
+    const int side = ew >> 2;
     const int quad = warp & 3;
-    const int half = (warp - 2) >> 2;
-    const int row = quad * 32 + lane;
-    const bool leader = (warp == 2 && lane == 0);
     const bool has_res = p.residual != nullptr;
     const bool relu = p.relu != 0;
     constexpr int kChunks = BLOCK_N / kChunkN;
-    uint8_t* const smem_gen = smem_raw + (epi_base - smem_u32(smem_raw));  // generic view of the epilogue tiles
-    const uint32_t sw = (uint32_t)(row & 7);
-    uint32_t unit_off[4];  // this thread's four 16-byte units inside a swizzled 128-byte row
-#pragma unroll
-    for (int j = 0; j < 4; ++j) unit_off[j] = (uint32_t)row * 128u + ((((uint32_t)(half * 4 + j)) ^ sw) << 4);
-    uint32_t it = 0;
-    uint32_t chunk_seq = 0;  // chunks processed so far: selects staging / residual buffer and phase
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+    const uint32_t out_buf = epi_base + ew * kSliceBytes;                                   // [out x8]
+    uint8_t* const out_gen = smem_raw + (out_buf - smem_u32(smem_raw));
+    float* const bias_gen = reinterpret_cast<float*>(smem_raw + (epi_base + kEpiWarps * kSliceBytes - smem_u32(smem_raw))) + ew * kChunkN;
+    const uint8_t* const res_gen0 =                                                         // [res x2] per side
+        smem_raw + (epi_base + Cfg::kEpiFixed + (2 * side) * kChunkBytes - smem_u32(smem_raw)) + quad * kSliceBytes;
+    const uint32_t sw = (uint32_t)(lane & 7);
+    const uint32_t row_off = (uint32_t)lane * 128u;
+    uint32_t gs = 0;  // chunks this warp has processed: selects the residual buffer and phase
+    for (uint32_t q = side;; q += 2, ++gs) {
+      const uint32_t it = q / kChunks;
+      const int tile = blockIdx.x + (int)it * gridDim.x;
+      if (tile >= p.num_tiles) break;
+      const int c = (int)(q % kChunks);
+      const int m0 = (kRows ? 0 : (tile / p.tiles_n) * kBlockM) + quad * 32;
+      const int n0c = (kRows ? 0 : (tile % p.tiles_n) * BLOCK_N) + c * kChunkN;
       const uint32_t acc = it & 1u;
-      const uint32_t acc_phase = (it >> 1) & 1u;
-      const int tile_n = tile % p.tiles_n;
-      const int tile_m = tile / p.tiles_n;
-      const int m0 = tile_m * kBlockM;
-      const int n0 = tile_n * BLOCK_N;
-      if (has_res && leader) {  // residual tiles for the first two chunks travel while the MMAs run
-#pragma unroll
-        for (int c = 0; c < 2 && c < kChunks; ++c) {
-          const uint32_t b = (chunk_seq + c) & 1u;
-          mbar_expect_tx(res_full_bar(b), kChunkBytes);
-          tma_load_2d(epi_base + (2 + b) * kChunkBytes, &tmap_res, res_full_bar(b), n0 + c * kChunkN, m0);
-        }
-        // The residual was written three layers ago and has usually left L2; a chunk's load is
-        // only issued two chunks (~2000 cycles) ahead, less than a loaded DRAM round trip (the
-        // epilogue trace showed stalls of 1000-3000 cycles on res_full).  Pull the NEXT tile's
-        // residual into L2 now, a whole tile ahead.
-        const int ntile = tile + gridDim.x;
-#ifndef AI4E_NO_RES_PREFETCH
-        if (ntile < p.num_tiles) {
-          const int nm0 = (ntile / p.tiles_n) * kBlockM, nn0 = (ntile % p.tiles_n) * BLOCK_N;
-#pragma unroll
-          for (int c = 0; c < kChunks; ++c) tma_prefetch_l2_2d(&tmap_res, nn0 + c * kChunkN, nm0);
-        }
-#else
-        (void)ntile;
-#endif
+      const float2 bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + n0c) + lane);  // lands during the waits
+      // first chunk of this tile for this warp: the tile's accumulator must be complete
+      if (c < 2) {
+        mbar_wait(tmem_full_bar(acc), (it >> 1) & 1u);
+        tc_fence_after();
       }
-      mbar_wait(tmem_full_bar(acc), acc_phase);
-      tc_fence_after();
-      const uint32_t t_addr = tmem_base + acc * BLOCK_N + half * 32 + ((uint32_t)(quad * 32) << 16);
-#pragma unroll 1
-      for (int c = 0; c < kChunks; ++c, ++chunk_seq) {
-        const uint32_t b = chunk_seq & 1u;
-        uint8_t* const out_gen = smem_gen + b * kChunkBytes;
-        const uint8_t* const res_gen = smem_gen + (2 + b) * kChunkBytes;
-        [[maybe_unused]] const bool etr = leader && chunk_seq < 40;
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 0);  // chunk start (tile's accumulator ready)
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(t_addr + c * kChunkN, v);
-        float4 bias[8];
-        {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0 + c * kChunkN + half * 32);
+      const uint32_t t_addr = tmem_base + acc * BLOCK_N + c * kChunkN + ((uint32_t)(quad * 32) << 16);
+      [[maybe_unused]] const bool etr = ew == 0 && lane == 0 && gs < 40;
+      AI4E_TRACE(etr, 768 + 6 * gs + 0);  // chunk start (tile's accumulator ready)
+      uint32_t v[64];
+      {
+        uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+        uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[32]);
+        tmem_ld_32x32b_x32(t_addr, lo);
+        tmem_ld_32x32b_x32(t_addr + 32, hi);
+      }
+      reinterpret_cast<float2*>(bias_gen)[lane] = bias2;  // (the previous chunk's readers passed a __syncwarp)
+      const uint8_t* const res_row = res_gen0 + (gs & 1u) * kChunkBytes + row_off;
+      if (has_res) mbar_wait(res_full_bar(2 * side + (gs & 1u)), (gs >> 1) & 1u);
+      __syncwarp();
+      const float4* const b4 = reinterpret_cast<const float4*>(bias_gen);
+      // operands of unit j + 1 are fetched before the arithmetic of unit j
+      float4 ba = b4[0], bb = b4[1];
+      uint4 r = make_uint4(0, 0, 0, 0);
+      if (has_res) r = *reinterpret_cast<const uint4*>(res_row + (sw << 4));
+      tmem_wait_ld();
+      AI4E_TRACE(etr, 768 + 6 * gs + 1);  // accumulators in registers, residual landed
+      // last chunk of this tile for this warp: its TMEM reads are done, free the accumulator stage
+      if (c + 2 >= kChunks) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
+      }
+      uint4 o[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) bias[j] = __ldg(b4 + j);
+      for (int j = 0; j < 8; ++j) {  // 8 channels = one 16-byte unit of the swizzled row
+        float4 nba = ba, nbb = bb;
+        uint4 nr = r;
+        if (j < 7) {
+          nba = b4[2 * j + 2];
+          nbb = b4[2 * j + 3];
+          if (has_res) nr = *reinterpret_cast<const uint4*>(res_row + ((((uint32_t)(j + 1)) ^ sw) << 4));
         }
-        // the TMA store that last read this staging tile (two chunks ago) must be done with it
-        if (leader) bulk_wait_group_read<1>();
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 1);  // staging tile free
-        named_bar_sync(1, kEpiThreads);
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 2);  // barrier 1 passed
-        uint4 r[4];
+        float x[8];
+        x[0] = __uint_as_float(v[8 * j + 0]) + ba.x; x[1] = __uint_as_float(v[8 * j + 1]) + ba.y;
+        x[2] = __uint_as_float(v[8 * j + 2]) + ba.z; x[3] = __uint_as_float(v[8 * j + 3]) + ba.w;
+        x[4] = __uint_as_float(v[8 * j + 4]) + bb.x; x[5] = __uint_as_float(v[8 * j + 5]) + bb.y;
+        x[6] = __uint_as_float(v[8 * j + 6]) + bb.z; x[7] = __uint_as_float(v[8 * j + 7]) + bb.w;
         if (has_res) {
-          mbar_wait(res_full_bar(b), (chunk_seq >> 1) & 1u);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) r[j] = *reinterpret_cast<const uint4*>(res_gen + unit_off[j]);
+          x[0] += bf16_lo(r.x); x[1] += bf16_hi(r.x); x[2] += bf16_lo(r.y); x[3] += bf16_hi(r.y);
+          x[4] += bf16_lo(r.z); x[5] += bf16_hi(r.z); x[6] += bf16_lo(r.w); x[7] += bf16_hi(r.w);
         }
-        tmem_wait_ld();
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 3);  // accumulators (and residual) in registers
+        if (relu) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {  // 8 channels = one 16-byte unit of the swizzled row
-          float x[8];
-          x[0] = __uint_as_float(v[8 * j + 0]) + bias[2 * j].x; x[1] = __uint_as_float(v[8 * j + 1]) + bias[2 * j].y;
-          x[2] = __uint_as_float(v[8 * j + 2]) + bias[2 * j].z; x[3] = __uint_as_float(v[8 * j + 3]) + bias[2 * j].w;
-          x[4] = __uint_as_float(v[8 * j + 4]) + bias[2 * j + 1].x; x[5] = __uint_as_float(v[8 * j + 5]) + bias[2 * j + 1].y;
-          x[6] = __uint_as_float(v[8 * j + 6]) + bias[2 * j + 1].z; x[7] = __uint_as_float(v[8 * j + 7]) + bias[2 * j + 1].w;
-          if (has_res) {
-            x[0] += bf16_lo(r[j].x); x[1] += bf16_hi(r[j].x); x[2] += bf16_lo(r[j].y); x[3] += bf16_hi(r[j].y);
-            x[4] += bf16_lo(r[j].z); x[5] += bf16_hi(r[j].z); x[6] += bf16_lo(r[j].w); x[7] += bf16_hi(r[j].w);
-          }
-          if (relu) {
-#pragma unroll
-            for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], 0.f);
-          }
-          *reinterpret_cast<uint4*>(out_gen + unit_off[j]) =
-              make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
-                         pack_bf16x2(x[6], x[7]));
+          for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], 0.f);
         }
-        fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 4);  // staged
-        named_bar_sync(2, kEpiThreads);
-        AI4E_TRACE(etr, 768 + 6 * chunk_seq + 5);  // barrier 2 passed
-        if (leader) {
-          if constexpr (kRows) tma_store_3d(&tmap_out, epi_base + b * kChunkBytes, 0, 0, tile);  // row `tile` of [N*P][Q][64]
-          else tma_store_2d(&tmap_out, epi_base + b * kChunkBytes, n0 + c * kChunkN, m0);
-          bulk_commit_group();
-          if (has_res && c + 2 < kChunks) {  // everyone is done reading res_buf[b]: refill it
-            mbar_expect_tx(res_full_bar(b), kChunkBytes);
-            tma_load_2d(epi_base + (2 + b) * kChunkBytes, &tmap_res, res_full_bar(b), n0 + (c + 2) * kChunkN, m0);
-          }
-        }
+        o[j] = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
+                          pack_bf16x2(x[6], x[7]));
+        ba = nba; bb = nbb; r = nr;
       }
-      tc_fence_before();
-      mbar_arrive(tmem_empty_bar(acc));  // kEpiThreads arrivals free this accumulator stage
+      AI4E_TRACE(etr, 768 + 6 * gs + 2);  // arithmetic done
+      // the TMA store of this warp's previous chunk must have read the staging slice by now
+      if (lane == 0) bulk_wait_group_read<0>();
+      __syncwarp();
+      if (has_res && lane == 0) mbar_arrive(res_empty_bar(2 * side + (gs & 1u)));  // this warp is done with it
+      AI4E_TRACE(etr, 768 + 6 * gs + 3);  // staging slice free
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<uint4*>(out_gen + row_off + ((((uint32_t)j) ^ sw) << 4)) = o[j];
+      fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
+      __syncwarp();
+      AI4E_TRACE(etr, 768 + 6 * gs + 4);  // staged
+      if (lane == 0) {
+        if constexpr (kRows) {
+          if (quad * 32 < p.Q) tma_store_3d(&tmap_out, out_buf, 0, quad * 32, tile);  // row `tile` of [N*P][Q][64]
+        } else {
+          if (m0 < p.M) tma_store_2d(&tmap_out, out_buf, n0c, m0);
+        }
+        bulk_commit_group();
+      }
+      AI4E_TRACE(etr, 768 + 6 * gs + 5);  // store issued
     }
-    if (leader) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
+    if (lane == 0) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
+  } else if (warp == 3 + kEpiWarps) {
+    // ------------------------------- residual warp -------------------------------
+    // One thread walks the CTA's chunks in order and keeps two 128-row x 64-channel residual
+    // buffers per epilogue side filled; the four warps of a side release a buffer through
+    // res_empty (count 4).  The residual was written three layers ago and has usually left L2,
+    // so the chunk four ahead is also pulled into L2.  (Issued from the epilogue warps these
+    // TMA instructions cost each of them ~600 cycles per chunk.)
+    if (p.residual != nullptr && lane == 0) {
+      constexpr int kChunks = BLOCK_N / kChunkN;
+      auto coords = [&](uint32_t q, int& m0, int& n0c) -> bool {
+        const int tile = blockIdx.x + (int)(q / kChunks) * gridDim.x;
+        if (tile >= p.num_tiles) return false;
+        m0 = (tile / p.tiles_n) * kBlockM;
+        n0c = (tile % p.tiles_n) * BLOCK_N + (int)(q % kChunks) * kChunkN;
+        return true;
+      };
+      int m0, n0c;
+      for (uint32_t q = 0; q < 4; ++q)
+        if (coords(q, m0, n0c)) tma_prefetch_l2_2d(&tmap_res, n0c, m0);
+      for (uint32_t q = 0;; ++q) {
+        if (!coords(q, m0, n0c)) break;
+        const uint32_t sd = q & 1u, n = q >> 1, b = n & 1u;  // side, side-chunk index, buffer
+        if (n >= 2) mbar_wait(res_empty_bar(2 * sd + b), ((n >> 1) - 1u) & 1u);
+        mbar_expect_tx(res_full_bar(2 * sd + b), kChunkBytes);
+        tma_load_2d(epi_base + Cfg::kEpiFixed + (2 * sd + b) * kChunkBytes, &tmap_res, res_full_bar(2 * sd + b), n0c, m0);
+        if (coords(q + 4, m0, n0c)) tma_prefetch_l2_2d(&tmap_res, n0c, m0);
+      }
+    }
   }
 
   tc_fence_before();
@@ -464,12 +503,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 // ----------------------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------------------
-int igemm_pick_block_n(int Cout, long long M) {
+int igemm_pick_block_n(int Cout, long long M, bool has_res) {
   const int sms = sm_count();
   const long long tiles_m = (M + kBlockM - 1) / kBlockM;
-  // the widest tile that still leaves at least one tile per SM; wider tiles re-read A less
+  // the widest tile that still leaves at least one tile per SM; wider tiles re-read A less.
+  // With a residual the epilogue needs 96 KB of shared memory, which would leave a 256-wide tile
+  // only two pipeline stages: those layers stop at 128 (measured: capping every layer at 128
+  // costs 0.4%).  AI4E_B200_MAX_BN lowers the cap for experiments.
+  static const int env_max_bn = [] { const char* v = getenv("AI4E_B200_MAX_BN"); return v ? atoi(v) : 256; }();
+  const int max_bn = std::min(env_max_bn, has_res ? 128 : 256);
   for (int bn : {256, 128, 64}) {
-    if (Cout % bn) continue;
+    if (Cout % bn || bn > max_bn) continue;
     if (tiles_m * (Cout / bn) >= sms || bn == 64) return bn;
   }
   for (int bn : {64, 128, 256})
@@ -514,14 +558,15 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   const uint64_t dims[2] = {ktot, (uint64_t)Cout};
   const uint64_t strides[1] = {ktot * 2};
   const uint32_t es[2] = {1, 1};
-  // output / residual tiles: [M rows][Cout] bf16, 128 rows x 64 channels per TMA, 128B swizzle
+  // output / residual: [M rows][Cout] bf16, 32 rows x 64 channels per TMA (one epilogue warp), 128B swizzle
   {
     const uint64_t odims[2] = {(uint64_t)Cout, (uint64_t)N * P * Q};
     const uint64_t ostr[1] = {(uint64_t)Cout * 2};
-    const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
+    const uint32_t obox[2] = {(uint32_t)kChunkN, 32};
     rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    rc = tmap_encode_tiled(&plan->tmap_res, residual ? residual : out, 2, odims, ostr, obox, es,
+    const uint32_t rbox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};  // residual: a whole 128-row chunk per TMA
+    rc = tmap_encode_tiled(&plan->tmap_res, residual ? residual : out, 2, odims, ostr, rbox, es,
                            CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   }
@@ -601,12 +646,12 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   if (rows) {
     const uint64_t odims[3] = {64, (uint64_t)Q, (uint64_t)N * P};
     const uint64_t ostr[2] = {64 * 2, (uint64_t)Q * 64 * 2};
-    const uint32_t obox[3] = {(uint32_t)kChunkN, (uint32_t)Q, 1};
+    const uint32_t obox[3] = {(uint32_t)kChunkN, 32, 1};
     rc = tmap_encode_tiled(&plan->tmap_out, out, 3, odims, ostr, obox, es4, CU_TENSOR_MAP_SWIZZLE_128B);
   } else {
     const uint64_t odims[2] = {64, (uint64_t)N * P * Q};
     const uint64_t ostr[1] = {64 * 2};
-    const uint32_t obox[2] = {(uint32_t)kChunkN, (uint32_t)kBlockM};
+    const uint32_t obox[2] = {(uint32_t)kChunkN, 32};
     rc = tmap_encode_tiled(&plan->tmap_out, out, 2, odims, ostr, obox, es, CU_TENSOR_MAP_SWIZZLE_128B);
   }
   if (rc) return rc;
@@ -622,7 +667,7 @@ static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const I
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
   if (!(attr_done >> dev & 1ull)) {
     AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN, kMode>::smem_bytes(false)));
+                                       IgemmCfg<BN, kMode>::kSmemLimit));
     attr_done |= 1ull << dev;
   }
   AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kMode>, dim3(grid), dim3(kIgemmThreads),
@@ -651,7 +696,7 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
     return igemm_launch_bn<64, kModeStemIm2col>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()),
                                                 stream);
   }
-  const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M);
+  const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M, prm.residual != nullptr);
   const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
   AI4E_REQUIRE(bi >= 0 && plan.has_bn[bi], "conv(igemm): BLOCK_N %d not available for Cout %d", bn, prm.Cout);
   prm.M = (int)M;

@@ -48,7 +48,7 @@ struct IgemmPlan {
 };
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
-int igemm_pick_block_n(int Cout, long long M);
+int igemm_pick_block_n(int Cout, long long M, bool has_res);
 int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
                     int pad, const void* residual, int relu, void* out);
