@@ -70,13 +70,15 @@ int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride
 }
 
 // ---------------------------------------------------------------------------------------
-// global average pool: [N, HW, C] bf16 -> [N, C] fp32.
+// global average pool: [N, HW, C] bf16 -> pooled features [N, C] as two bf16 planes, hi and lo
+// (hi = bf16(mean), lo = bf16(mean - hi): 16 mantissa bits, what the FC below feeds the tensor
+// cores; the scratch is N*C*4 bytes either way).
 // block = (image, 256 channels): 32 lanes x 8 channels (16-byte loads, 512 contiguous bytes per
 // pixel row) times kPoolParts pixel groups, reduced through shared memory.
 // ---------------------------------------------------------------------------------------
 constexpr int kPoolParts = 7;
 __global__ void __launch_bounds__(32 * kPoolParts)
-avgpool_kernel(const uint4* __restrict__ in, float* __restrict__ out, int HW, int C8) {
+avgpool_kernel(const uint4* __restrict__ in, bf16* __restrict__ out_hi, bf16* __restrict__ out_lo, int HW, int C8) {
   __shared__ float part[kPoolParts][32][9];
   pdl_launch_dependents();
   pdl_wait();
@@ -103,77 +105,104 @@ avgpool_kernel(const uint4* __restrict__ in, float* __restrict__ out, int HW, in
 #pragma unroll
     for (int q = 0; q < kPoolParts; ++q) a += part[q][l][j];
     const int cc = (blockIdx.x * 32 + l) * 8 + j;
-    if (cc < C8 * 8) out[(long long)n * C8 * 8 + cc] = a * (1.0f / (float)HW);
+    if (cc < C8 * 8) {
+      a *= 1.0f / (float)HW;
+      const bf16 hi = __float2bfloat16_rn(a);
+      out_hi[(long long)n * C8 * 8 + cc] = hi;
+      out_lo[(long long)n * C8 * 8 + cc] = __float2bfloat16_rn(a - __bfloat162float(hi));
+    }
   }
 }
 
 // ---------------------------------------------------------------------------------------
-// FC: logits[n][k] = bias[k] + sum_c pooled[n][c] * W[k][c]   (W bf16 [classes][C], fp32 math)
-// CTA = 4 warps x 2 classes = 8 classes, all images.  A lane keeps its share of the two weight
-// rows in registers (k = i*128 + lane*4 .. +3), pooled vectors pass through shared memory
-// kFcImgs at a time as conflict-free 16-byte loads, warp-shuffle reduction per (class, image).
+// FC: logits[n][k] = bias[k] + sum_c pooled[n][c] * W[k][c]   (W bf16 [classes][C])
+// Tensor cores through mma.sync m16n8k16 (bf16 x bf16 -> fp32): the matrix is 64 x 1000 x 2048, far
+// too small to amortise a tcgen05/TMEM pipeline, and the kernel is bound by pulling the pooled
+// features out of L2.  pooled = hi + lo, so each k step issues two MMAs and the result carries
+// 16 mantissa bits of the fp32 mean (the products are exact, accumulation is fp32).
+// CTA = 16 classes x 64 images: 16 warps = 4 image groups of 16 x 4 interleaved quarters of K,
+// each warp a 16 x 16 tile (two n8 tiles); the four K partials meet in shared memory.
+// K is consumed 32 at a time with a permuted order so that a thread's fragment words are
+// contiguous in memory: thread (g = lane / 4, t = lane % 4) loads elements 8t .. 8t+7 of the block
+// (16 bytes) from rows g and g + 8 of the pooled planes and from weight rows g and g + 8 of the tile.
 // ---------------------------------------------------------------------------------------
-constexpr int kFcImgs = 8;
-constexpr int kFcMaxC = 2048;
-__global__ void __launch_bounds__(128)
-fc_kernel(const float* __restrict__ pooled, const bf16* __restrict__ w, const float* __restrict__ bias,
-          float* __restrict__ logits, int N, int C, int classes) {
-  extern __shared__ float4 x_s4[];  // [kFcImgs][C/4]
+constexpr int kFcClasses = 16;
+constexpr int kFcImages = 64;
+constexpr int kFcThreads = 512;
+
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                               uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(kFcThreads, 1)
+fc_kernel(const bf16* __restrict__ pooled_hi, const bf16* __restrict__ pooled_lo, const bf16* __restrict__ w,
+          const float* __restrict__ bias, float* __restrict__ logits, int N, int C, int classes) {
+  __shared__ float part[3][4][32][8];  // K quarters 1..3 -> [image group][lane][fragment]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int cls0 = blockIdx.x * 8 + warp * 2;
-  const int c4 = C / 4;
-  const int iters = (c4 + 31) / 32;  // 4 weights per lane per iteration; the last one may be partial
-  // blockIdx.y splits the images so that several CTAs share an SM and hide each other's latency
-  const int n_per = (N + gridDim.y - 1) / gridDim.y;
-  const int n_begin = blockIdx.y * n_per, n_end = min(N, n_begin + n_per);
-  float wr[2][kFcMaxC / 32];
-#pragma unroll
-  for (int q = 0; q < 2; ++q) {
-    const int cls = min(cls0 + q, classes - 1);
-    const uint2* row = reinterpret_cast<const uint2*>(w + (long long)cls * C);
-#pragma unroll
-    for (int i = 0; i < kFcMaxC / 128; ++i) {
-      wr[q][4 * i + 0] = wr[q][4 * i + 1] = wr[q][4 * i + 2] = wr[q][4 * i + 3] = 0.f;
-      if (i < iters && i * 32 + lane < c4) {
-        const uint2 v = __ldg(row + i * 32 + lane);
-        wr[q][4 * i + 0] = bf16_lo(v.x); wr[q][4 * i + 1] = bf16_hi(v.x);
-        wr[q][4 * i + 2] = bf16_lo(v.y); wr[q][4 * i + 3] = bf16_hi(v.y);
-      }
+  const int ig = warp & 3, kq = warp >> 2;
+  const int g = lane >> 2, t = lane & 3;
+  const int cls0 = blockIdx.x * kFcClasses;
+  const int img0 = blockIdx.y * kFcImages + ig * 16;
+  // the weights are constants: pull this CTA's 16 rows into L2 while the pooling kernel finishes
+  {
+    const int rows = min(kFcClasses, classes - cls0);
+    const long long bytes = (long long)rows * C * 2;
+    const char* base = reinterpret_cast<const char*>(w + (long long)cls0 * C);
+    for (long long off = (long long)threadIdx.x * 128; off < bytes; off += (long long)kFcThreads * 128)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(base + off));
+  }
+  pdl_launch_dependents();
+  pdl_wait();
+  const int r0 = img0 + g, r1 = img0 + g + 8;            // pooled rows (images) of this thread
+  const int k0c = cls0 + g, k1c = cls0 + 8 + g;           // weight rows (classes) of this thread
+  const bool vr0 = r0 < N, vr1 = r1 < N, vk0 = k0c < classes, vk1 = k1c < classes;
+  const uint4* xh0 = reinterpret_cast<const uint4*>(pooled_hi + (long long)(vr0 ? r0 : 0) * C) + t;
+  const uint4* xh1 = reinterpret_cast<const uint4*>(pooled_hi + (long long)(vr1 ? r1 : 0) * C) + t;
+  const uint4* xl0 = reinterpret_cast<const uint4*>(pooled_lo + (long long)(vr0 ? r0 : 0) * C) + t;
+  const uint4* xl1 = reinterpret_cast<const uint4*>(pooled_lo + (long long)(vr1 ? r1 : 0) * C) + t;
+  const uint4* w0 = reinterpret_cast<const uint4*>(w + (long long)(vk0 ? k0c : 0) * C) + t;
+  const uint4* w1 = reinterpret_cast<const uint4*>(w + (long long)(vk1 ? k1c : 0) * C) + t;
+  float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+  const uint4 z = make_uint4(0, 0, 0, 0);
+  const int kblocks = (C + 31) / 32;
+  if (img0 < N) {
+#pragma unroll 4
+    for (int kb = kq; kb < kblocks; kb += 4) {
+      const bool vk = kb * 32 + 8 * t + 8 <= C;  // C % 8 == 0: a thread's 8 elements are all in or all out
+      const int o = kb * 4;                       // in uint4 units
+      const uint4 ah0 = vk && vr0 ? __ldcg(xh0 + o) : z, ah1 = vk && vr1 ? __ldcg(xh1 + o) : z;
+      const uint4 al0 = vk && vr0 ? __ldcg(xl0 + o) : z, al1 = vk && vr1 ? __ldcg(xl1 + o) : z;
+      const uint4 b0 = vk && vk0 ? __ldg(w0 + o) : z, b1 = vk && vk1 ? __ldg(w1 + o) : z;
+      // k step 0: words x, y; k step 1: words z, w
+      mma_bf16_16816(acc[0], ah0.x, ah1.x, ah0.y, ah1.y, b0.x, b0.y);
+      mma_bf16_16816(acc[0], al0.x, al1.x, al0.y, al1.y, b0.x, b0.y);
+      mma_bf16_16816(acc[1], ah0.x, ah1.x, ah0.y, ah1.y, b1.x, b1.y);
+      mma_bf16_16816(acc[1], al0.x, al1.x, al0.y, al1.y, b1.x, b1.y);
+      mma_bf16_16816(acc[0], ah0.z, ah1.z, ah0.w, ah1.w, b0.z, b0.w);
+      mma_bf16_16816(acc[0], al0.z, al1.z, al0.w, al1.w, b0.z, b0.w);
+      mma_bf16_16816(acc[1], ah0.z, ah1.z, ah0.w, ah1.w, b1.z, b1.w);
+      mma_bf16_16816(acc[1], al0.z, al1.z, al0.w, al1.w, b1.z, b1.w);
     }
   }
-  const float b0 = bias[min(cls0, classes - 1)], b1 = bias[min(cls0 + 1, classes - 1)];
-  pdl_launch_dependents();  // the weights above are constants: loading them overlaps the pooling kernel
-  pdl_wait();
-  for (int n0 = n_begin; n0 < n_end; n0 += kFcImgs) {
-    const int nimg = min(kFcImgs, n_end - n0);
-    __syncthreads();
-    const float4* src = reinterpret_cast<const float4*>(pooled + (long long)n0 * C);
-    for (int i = threadIdx.x; i < nimg * c4; i += blockDim.x) x_s4[i] = __ldcg(src + i);
-    __syncthreads();
-    for (int im = 0; im < nimg; ++im) {
-      const float4* xp = x_s4 + im * c4 + lane;
-      float4 s0 = make_float4(0.f, 0.f, 0.f, 0.f), s1 = s0;  // four independent chains per class
+  if (kq > 0) {
 #pragma unroll
-      for (int i = 0; i < kFcMaxC / 128; ++i) {
-        if (i < iters) {
-          // lanes past the end of a partial last iteration hold zero weights; clamp their address
-          const float4 x = xp[min(i * 32, c4 - 1 - lane)];
-          s0.x = fmaf(wr[0][4 * i], x.x, s0.x); s0.y = fmaf(wr[0][4 * i + 1], x.y, s0.y);
-          s0.z = fmaf(wr[0][4 * i + 2], x.z, s0.z); s0.w = fmaf(wr[0][4 * i + 3], x.w, s0.w);
-          s1.x = fmaf(wr[1][4 * i], x.x, s1.x); s1.y = fmaf(wr[1][4 * i + 1], x.y, s1.y);
-          s1.z = fmaf(wr[1][4 * i + 2], x.z, s1.z); s1.w = fmaf(wr[1][4 * i + 3], x.w, s1.w);
-        }
-      }
-      float a0 = (s0.x + s0.y) + (s0.z + s0.w), a1 = (s1.x + s1.y) + (s1.z + s1.w);
+    for (int j = 0; j < 8; ++j) part[kq - 1][ig][lane][j] = acc[j >> 2][j & 3];
+  }
+  __syncthreads();
+  if (kq == 0) {
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-        a1 += __shfl_xor_sync(0xffffffffu, a1, o);
-      }
-      if (lane == 0) {
-        float* lrow = logits + (long long)(n0 + im) * classes;
-        if (cls0 < classes) lrow[cls0] = a0 + b0;
-        if (cls0 + 1 < classes) lrow[cls0 + 1] = a1 + b1;
+    for (int j = 0; j < 8; ++j)
+      acc[j >> 2][j & 3] += (part[0][ig][lane][j] + part[1][ig][lane][j]) + part[2][ig][lane][j];
+    // accumulator fragment: [0],[1] = row g, columns 2t, 2t+1; [2],[3] = row g + 8, same columns
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int row = (e < 2 ? r0 : r1), cls = cls0 + nt * 8 + 2 * t + (e & 1);
+        if (row < N && cls < classes) logits[(long long)row * classes + cls] = acc[nt][e] + __ldg(bias + cls);
       }
     }
   }
@@ -259,24 +288,17 @@ int launch_head(const void* in, int N, int HW, int C, const void* fc_w, const fl
                 int topk, cudaStream_t stream) {
   AI4E_REQUIRE(in && fc_w && fc_b && pooled_scratch && logits, "head: null pointer");
   AI4E_REQUIRE(N > 0 && HW > 0 && classes > 0, "head: bad geometry");
-  AI4E_REQUIRE(C % 8 == 0 && C <= kFcMaxC, "head: C %d must be a multiple of 8 and <= %d", C, kFcMaxC);
+  AI4E_REQUIRE(C % 8 == 0, "head: C %d must be a multiple of 8", C);
   AI4E_REQUIRE(classes <= kSmThreads * kSmMaxPerThread, "head: %d classes (max %d)", classes,
                kSmThreads * kSmMaxPerThread);
   AI4E_REQUIRE(topk >= 0 && topk <= 8 && topk <= classes, "head: topk %d unsupported", topk);
   const int C8 = C / 8;
+  bf16* pooled_hi = reinterpret_cast<bf16*>(pooled_scratch);  // N*C floats of scratch = two bf16 planes
+  bf16* pooled_lo = pooled_hi + (long long)N * C;
   AI4E_CUDA_TRY(launch_pdl(avgpool_kernel, dim3((C8 + 31) / 32, N), dim3(32 * kPoolParts), 0, stream,
-                           (const uint4*)in, pooled_scratch, HW, C8));
-  const size_t smem = (size_t)kFcImgs * C * sizeof(float);
-  static unsigned long long attr_done = 0;
-  int dev = 0;
-  AI4E_CUDA_TRY(cudaGetDevice(&dev));
-  if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       kFcImgs * kFcMaxC * (int)sizeof(float)));
-    attr_done |= 1ull << dev;
-  }
-  const int img_split = N >= 32 ? 4 : (N >= 16 ? 2 : 1);
-  AI4E_CUDA_TRY(launch_pdl(fc_kernel, dim3((classes + 7) / 8, img_split), dim3(128), smem, stream, (const float*)pooled_scratch,
+                           (const uint4*)in, pooled_hi, pooled_lo, HW, C8));
+  AI4E_CUDA_TRY(launch_pdl(fc_kernel, dim3((classes + kFcClasses - 1) / kFcClasses, (N + kFcImages - 1) / kFcImages),
+                           dim3(kFcThreads), 0, stream, (const bf16*)pooled_hi, (const bf16*)pooled_lo,
                            (const bf16*)fc_w, fc_b, logits, N, C, classes));
   if (topk > 0) {
     AI4E_REQUIRE(top_idx && top_prob, "head: null top-k outputs");
