@@ -369,31 +369,43 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         smem_raw + (epi_base + Cfg::kEpiFixed + (2 * side) * kChunkBytes - smem_u32(smem_raw)) + quad * kSliceBytes;
     const uint32_t sw = (uint32_t)(lane & 7);
     const uint32_t row_off = (uint32_t)lane * 128u;
+    // chunk q of this CTA -> tile, chunk within the tile, first row of this warp, first channel
+    struct Chunk { int tile, c, m0, n0c; uint32_t it; };
+    auto locate = [&](uint32_t q, Chunk& k) -> bool {
+      k.it = q / kChunks;
+      k.tile = blockIdx.x + (int)k.it * gridDim.x;
+      if (k.tile >= p.num_tiles) return false;
+      k.c = (int)(q % kChunks);
+      k.m0 = (kRows ? 0 : (k.tile / p.tiles_n) * kBlockM) + quad * 32;
+      k.n0c = (kRows ? 0 : (k.tile % p.tiles_n) * BLOCK_N) + k.c * kChunkN;
+      return true;
+    };
+    uint32_t v[64];
+    uint32_t (&vlo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+    uint32_t (&vhi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[32]);
+    auto issue_ld = [&](const Chunk& k) {
+      const uint32_t t_addr = tmem_base + (k.it & 1u) * BLOCK_N + k.c * kChunkN + ((uint32_t)(quad * 32) << 16);
+      tmem_ld_32x32b_x32(t_addr, vlo);
+      tmem_ld_32x32b_x32(t_addr + 32, vhi);
+    };
+    Chunk cur, nxt;
+    bool have = locate(side, cur);
+    bool ld_issued = false;  // the accumulator load of `cur` was already issued at the end of the previous chunk
+    float2 bias2 = make_float2(0.f, 0.f);
+    if (have) bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + cur.n0c) + lane);
     uint32_t gs = 0;  // chunks this warp has processed: selects the residual buffer and phase
-    for (uint32_t q = side;; q += 2, ++gs) {
-      const uint32_t it = q / kChunks;
-      const int tile = blockIdx.x + (int)it * gridDim.x;
-      if (tile >= p.num_tiles) break;
-      const int c = (int)(q % kChunks);
-      const int m0 = (kRows ? 0 : (tile / p.tiles_n) * kBlockM) + quad * 32;
-      const int n0c = (kRows ? 0 : (tile % p.tiles_n) * BLOCK_N) + c * kChunkN;
-      const uint32_t acc = it & 1u;
-      const float2 bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + n0c) + lane);  // lands during the waits
-      // first chunk of this tile for this warp: the tile's accumulator must be complete
-      if (c < 2) {
-        mbar_wait(tmem_full_bar(acc), (it >> 1) & 1u);
-        tc_fence_after();
-      }
-      const uint32_t t_addr = tmem_base + acc * BLOCK_N + c * kChunkN + ((uint32_t)(quad * 32) << 16);
+    for (uint32_t q = side; have; q += 2, ++gs) {
+      const uint32_t acc = cur.it & 1u;
       [[maybe_unused]] const bool etr = ew == 0 && lane == 0 && gs < 40;
-      AI4E_TRACE(etr, 768 + 6 * gs + 0);  // chunk start (tile's accumulator ready)
-      uint32_t v[64];
-      {
-        uint32_t (&lo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
-        uint32_t (&hi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[32]);
-        tmem_ld_32x32b_x32(t_addr, lo);
-        tmem_ld_32x32b_x32(t_addr + 32, hi);
+      if (!ld_issued) {
+        // first chunk of this tile for this warp: the tile's accumulator must be complete
+        if (cur.c < 2) {
+          mbar_wait(tmem_full_bar(acc), (cur.it >> 1) & 1u);
+          tc_fence_after();
+        }
+        issue_ld(cur);
       }
+      AI4E_TRACE(etr, 768 + 6 * gs + 0);  // chunk start (accumulator load issued)
       reinterpret_cast<float2*>(bias_gen)[lane] = bias2;  // (the previous chunk's readers passed a __syncwarp)
       const uint8_t* const res_row = res_gen0 + (gs & 1u) * kChunkBytes + row_off;
       if (has_res) mbar_wait(res_full_bar(2 * side + (gs & 1u)), (gs >> 1) & 1u);
@@ -403,10 +415,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       float4 ba = b4[0], bb = b4[1];
       uint4 r = make_uint4(0, 0, 0, 0);
       if (has_res) r = *reinterpret_cast<const uint4*>(res_row + (sw << 4));
-      tmem_wait_ld();
+      tmem_wait_ld_pin(vlo);
+      tmem_wait_ld_pin(vhi);
       AI4E_TRACE(etr, 768 + 6 * gs + 1);  // accumulators in registers, residual landed
       // last chunk of this tile for this warp: its TMEM reads are done, free the accumulator stage
-      if (c + 2 >= kChunks) {
+      if (cur.c + 2 >= kChunks) {
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
@@ -430,15 +443,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           x[0] += bf16_lo(r.x); x[1] += bf16_hi(r.x); x[2] += bf16_lo(r.y); x[3] += bf16_hi(r.y);
           x[4] += bf16_lo(r.z); x[5] += bf16_hi(r.z); x[6] += bf16_lo(r.w); x[7] += bf16_hi(r.w);
         }
-        if (relu) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) x[k] = fmaxf(x[k], 0.f);
-        }
         o[j] = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
                           pack_bf16x2(x[6], x[7]));
+        if (relu) {  // rounding is monotonic and keeps the sign: relu after packing = relu before
+          o[j].x = relu_bf16x2(o[j].x); o[j].y = relu_bf16x2(o[j].y);
+          o[j].z = relu_bf16x2(o[j].z); o[j].w = relu_bf16x2(o[j].w);
+        }
         ba = nba; bb = nbb; r = nr;
       }
       AI4E_TRACE(etr, 768 + 6 * gs + 2);  // arithmetic done
+      // this warp's next chunk: fetch its bias and, if its accumulator is already complete, start
+      // the TMEM load now so that it travels during the staging and the store below
+      have = locate(q + 2, nxt);
+      ld_issued = false;
+      if (have) {
+        bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + nxt.n0c) + lane);
+        bool ready = true;
+        if (nxt.c < 2) {
+          ready = __all_sync(0xffffffffu, mbar_test_wait(tmem_full_bar(nxt.it & 1u), (nxt.it >> 1) & 1u));
+          if (ready) tc_fence_after();
+        }
+        if (ready) {
+          issue_ld(nxt);
+          ld_issued = true;
+        }
+      }
       // the TMA store of this warp's previous chunk must have read the staging slice by now
       if (lane == 0) bulk_wait_group_read<0>();
       __syncwarp();
@@ -452,13 +481,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       AI4E_TRACE(etr, 768 + 6 * gs + 4);  // staged
       if (lane == 0) {
         if constexpr (kRows) {
-          if (quad * 32 < p.Q) tma_store_3d(&tmap_out, out_buf, 0, quad * 32, tile);  // row `tile` of [N*P][Q][64]
+          if (quad * 32 < p.Q) tma_store_3d(&tmap_out, out_buf, 0, quad * 32, cur.tile);  // row `tile` of [N*P][Q][64]
         } else {
-          if (m0 < p.M) tma_store_2d(&tmap_out, out_buf, n0c, m0);
+          if (cur.m0 < p.M) tma_store_2d(&tmap_out, out_buf, cur.n0c, cur.m0);
         }
         bulk_commit_group();
       }
       AI4E_TRACE(etr, 768 + 6 * gs + 5);  // store issued
+      cur = nxt;
     }
     if (lane == 0) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
   } else if (warp == 3 + kEpiWarps) {

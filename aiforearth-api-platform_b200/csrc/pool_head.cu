@@ -120,15 +120,17 @@ avgpool_kernel(const uint4* __restrict__ in, bf16* __restrict__ out_hi, bf16* __
 // too small to amortise a tcgen05/TMEM pipeline, and the kernel is bound by pulling the pooled
 // features out of L2.  pooled = hi + lo, so each k step issues two MMAs and the result carries
 // 16 mantissa bits of the fp32 mean (the products are exact, accumulation is fp32).
-// CTA = 16 classes x 64 images: 16 warps = 4 image groups of 16 x 4 interleaved quarters of K,
-// each warp a 16 x 16 tile (two n8 tiles); the four K partials meet in shared memory.
+// CTA = 16 classes x 32 images: 16 warps = 2 image groups of 16 x 8 interleaved slices of K,
+// each warp a 16 x 16 tile (two n8 tiles); the K partials meet in shared memory.
 // K is consumed 32 at a time with a permuted order so that a thread's fragment words are
 // contiguous in memory: thread (g = lane / 4, t = lane % 4) loads elements 8t .. 8t+7 of the block
 // (16 bytes) from rows g and g + 8 of the pooled planes and from weight rows g and g + 8 of the tile.
 // ---------------------------------------------------------------------------------------
 constexpr int kFcClasses = 16;
-constexpr int kFcImages = 64;
+constexpr int kFcImages = 32;
 constexpr int kFcThreads = 512;
+constexpr int kFcIG = kFcImages / 16;            // image groups (warps along M)
+constexpr int kFcKQ = kFcThreads / 32 / kFcIG;   // interleaved K slices (warps along K)
 
 __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                                uint32_t b0, uint32_t b1) {
@@ -140,9 +142,9 @@ __device__ __forceinline__ void mma_bf16_16816(float (&d)[4], uint32_t a0, uint3
 __global__ void __launch_bounds__(kFcThreads, 1)
 fc_kernel(const bf16* __restrict__ pooled_hi, const bf16* __restrict__ pooled_lo, const bf16* __restrict__ w,
           const float* __restrict__ bias, float* __restrict__ logits, int N, int C, int classes) {
-  __shared__ float part[3][4][32][8];  // K quarters 1..3 -> [image group][lane][fragment]
+  __shared__ float part[kFcKQ - 1][kFcIG][32][8];  // K slices 1.. -> [image group][lane][fragment]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ig = warp & 3, kq = warp >> 2;
+  const int ig = warp % kFcIG, kq = warp / kFcIG;
   const int g = lane >> 2, t = lane & 3;
   const int cls0 = blockIdx.x * kFcClasses;
   const int img0 = blockIdx.y * kFcImages + ig * 16;
@@ -170,7 +172,7 @@ fc_kernel(const bf16* __restrict__ pooled_hi, const bf16* __restrict__ pooled_lo
   const int kblocks = (C + 31) / 32;
   if (img0 < N) {
 #pragma unroll 4
-    for (int kb = kq; kb < kblocks; kb += 4) {
+    for (int kb = kq; kb < kblocks; kb += kFcKQ) {
       const bool vk = kb * 32 + 8 * t + 8 <= C;  // C % 8 == 0: a thread's 8 elements are all in or all out
       const int o = kb * 4;                       // in uint4 units
       const uint4 ah0 = vk && vr0 ? __ldcg(xh0 + o) : z, ah1 = vk && vr1 ? __ldcg(xh1 + o) : z;
@@ -194,8 +196,12 @@ fc_kernel(const bf16* __restrict__ pooled_hi, const bf16* __restrict__ pooled_lo
   __syncthreads();
   if (kq == 0) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      acc[j >> 2][j & 3] += (part[0][ig][lane][j] + part[1][ig][lane][j]) + part[2][ig][lane][j];
+    for (int j = 0; j < 8; ++j) {
+      float a = 0.f;
+#pragma unroll
+      for (int q = 0; q < kFcKQ - 1; ++q) a += part[q][ig][lane][j];
+      acc[j >> 2][j & 3] += a;
+    }
     // accumulator fragment: [0],[1] = row g, columns 2t, 2t+1; [2],[3] = row g + 8, same columns
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
