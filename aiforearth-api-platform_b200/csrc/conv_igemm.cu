@@ -44,6 +44,7 @@
 
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
 namespace ai4e {
 
@@ -82,12 +83,20 @@ constexpr int kRowsMaxGroups = 18;                       // 128-byte groups per 
 constexpr int kRowsStage = 7 * kRowsMaxGroups * 128 + 256;  // 16 KiB incl. over-read slack
 constexpr int kModeGeneric = 0, kModeStemIm2col = 1, kModeStemRows = 2;
 
-template <int BLOCK_N, int kMode = kModeGeneric>
+// kPair: the CTAs of a 2-CTA cluster work on one 256-row tile with tcgen05 cta_group::2 - each
+// brings its own 128 rows of A and HALF of the weight tile, the tensor cores of both SMs read both
+// halves.  Operand bytes pulled from L2 per MMA drop from 16 KB + BLOCK_N * 128 to 16 KB +
+// BLOCK_N * 64 per CTA, and that is the bound: with all 148 SMs streaming, L2 delivers ~73 bytes
+// per clock per SM (tools/l2_probe.cu; 126 B/clk with one SM alone), i.e. 449 cycles for the 32 KB
+// a 128 x 128 x 64 block needs against 268 cycles of MMA.
+template <int BLOCK_N, int kMode = kModeGeneric, bool kPair = false>
 struct IgemmCfg {
+  static_assert(!kPair || (kMode == kModeGeneric && BLOCK_N >= 128), "pair mode: generic convolution, BLOCK_N >= 128");
   static constexpr bool kStem = kMode == kModeStemIm2col;
   static constexpr bool kRows = kMode == kModeStemRows;
+  static constexpr int kCtas = kPair ? 2 : 1;
   static constexpr int kAStage = kStem ? kStemTaps * kStemSlabA : kRows ? kRowsStage : kABytes;
-  static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : kRows ? 0 : BLOCK_N * kBlockK * 2;
+  static constexpr int kBBytes = kStem ? kStemTaps * BLOCK_N * 16 : kRows ? 0 : BLOCK_N / kCtas * kBlockK * 2;
   static constexpr int kStageBytes = kAStage + kBBytes;
   static constexpr int kResidentB = kRows ? kStemKBlocks * kStemTaps * BLOCK_N * 16 : 0;  // 28 KiB
   // The K loop is latency-bound (measured on B200: a pipeline slot takes ~3100 cycles to go round -
@@ -111,14 +120,21 @@ struct IgemmCfg {
   }
 };
 
-template <int BLOCK_N, int kMode>
+template <int BLOCK_N, int kMode, bool kPair>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const IgemmParams p) {
-  using Cfg = IgemmCfg<BLOCK_N, kMode>;
+  using Cfg = IgemmCfg<BLOCK_N, kMode, kPair>;
   constexpr bool kStem = Cfg::kStem;
   constexpr bool kRows = Cfg::kRows;
+  constexpr int kCtas = Cfg::kCtas;
+  // tiles are handed out to "units" (a CTA, or a CTA pair); in pair mode a tile is 256 rows and this
+  // CTA owns rows [128 * rank, 128 * rank + 128) of it
+  const uint32_t cta_rank = kPair ? cluster_ctarank() : 0u;
+  const int unit = (int)blockIdx.x / kCtas;
+  const int unit_stride = (int)gridDim.x / kCtas;
+  const bool leader = cta_rank == 0;
   const int kStages = Cfg::stages(p.residual != nullptr);  // runtime: depends on the epilogue's needs
   // SWIZZLE_128B operand tiles need 1024-byte alignment.  The kernel has no static shared memory, so
   // the dynamic window starts at the CTA's shared base; the budget above has no slack for rounding up.
@@ -147,13 +163,16 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(full_bar(s), kMode == kModeGeneric ? 2 : 1);  // generic: A and B come from two producers
+      // generic: A and B come from two producers; pair: from two producers in each CTA, all
+      // arriving on the leader's barrier
+      mbar_init(full_bar(s), (kMode == kModeGeneric ? 2 : 1) * kCtas);
       mbar_init(empty_bar(s), 1);
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);
-      // one arrival per epilogue warp that reads the tile: a 64-wide tile is drained by one side
-      mbar_init(tmem_empty_bar(s), BLOCK_N == kChunkN ? 4 : kEpiWarps);
+      // one arrival per epilogue warp that reads the tile (pair: of both CTAs, on the leader's
+      // barrier): a 64-wide tile is drained by one side
+      mbar_init(tmem_empty_bar(s), (BLOCK_N == kChunkN ? 4 : kEpiWarps) * kCtas);
     }
     for (int s = 0; s < 4; ++s) {
       mbar_init(res_full_bar(s), 1);
@@ -165,11 +184,17 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_ptr_addr, Cfg::kTmemCols);
-    tmem_relinquish();
+    if constexpr (kPair) {
+      tmem_alloc_pair(tmem_ptr_addr, Cfg::kTmemCols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_ptr_addr, Cfg::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();  // the peer's barriers exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
   // everything above touched only this kernel's own shared memory / TMEM / parameters: it may
@@ -208,10 +233,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
       }
-      for (int tile = blockIdx.x; !kRows && tile < p.num_tiles; tile += gridDim.x) {
+      for (int tile = unit; !kRows && tile < p.num_tiles; tile += unit_stride) {
         const int tile_n = tile % p.tiles_n;
         const int tile_m = tile / p.tiles_n;
-        const int m0 = tile_m * kBlockM;
+        const int m0 = (tile_m * kCtas + (int)cta_rank) * kBlockM;
         const int n_img = m0 / p.PQ;
         const int rem = m0 - n_img * p.PQ;
         const int p0 = rem / p.Q;
@@ -227,7 +252,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           [[maybe_unused]] const uint32_t b_dst = a_dst + Cfg::kAStage;
           // generic mode: this warp brings A only; the B tile comes from the B-producer warp
           if (elect_one()) {
-            mbar_expect_tx(full_bar(stage), kMode == kModeGeneric ? Cfg::kAStage : Cfg::kStageBytes);
+            if constexpr (kPair) mbar_expect_tx_leader(full_bar(stage), Cfg::kAStage);
+            else mbar_expect_tx(full_bar(stage), kMode == kModeGeneric ? Cfg::kAStage : Cfg::kStageBytes);
             if constexpr (kStem) {
               // K block kb = filter row; one im2col load per super-pixel tap, one weight slab each
 #pragma unroll
@@ -236,6 +262,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                                    (uint16_t)t, (uint16_t)kb);
                 tma_load_2d(b_dst + t * BLOCK_N * 16, &tmap_b, full_bar(stage), kb * 32 + t * 8, tile_n * BLOCK_N);
               }
+            } else if constexpr (kPair) {
+              tma_load_im2col_4d_pair(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
+                                      (uint16_t)s, (uint16_t)r);
             } else {
               tma_load_im2col_4d(a_dst, &tmap_a, full_bar(stage), cb * kBlockK, w_base, h_base, n_img,
                                  (uint16_t)s, (uint16_t)r);
@@ -257,13 +286,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (kMode == kModeGeneric) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int n0 = (tile % p.tiles_n) * BLOCK_N;
+      for (int tile = unit; tile < p.num_tiles; tile += unit_stride) {
+        // pair: this CTA brings weight rows [n0, n0 + BLOCK_N / 2) of the tile's BLOCK_N
+        const int n0 = (tile % p.tiles_n) * BLOCK_N + (int)cta_rank * (BLOCK_N / kCtas);
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (elect_one()) {
-            mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
-            tma_load_2d(smem_base + stage * Cfg::kStageBytes + Cfg::kAStage, &tmap_b, full_bar(stage), kb * kBlockK, n0);
+            const uint32_t b_dst = smem_base + stage * Cfg::kStageBytes + Cfg::kAStage;
+            if constexpr (kPair) {
+              mbar_expect_tx_leader(full_bar(stage), Cfg::kBBytes);
+              tma_load_2d_pair(b_dst, &tmap_b, full_bar(stage), kb * kBlockK, n0);
+            } else {
+              mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
+              tma_load_2d(b_dst, &tmap_b, full_bar(stage), kb * kBlockK, n0);
+            }
           }
           __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -275,14 +311,14 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // The whole warp runs this loop convergently and one elected lane issues: every operand is then
     // provably warp-uniform and the compiler feeds tcgen05.mma straight from uniform registers.
     // (Under `if (lane == 0)` it wraps each MMA in a per-lane "waterfall" loop of ~12 instructions.)
-    {
-      constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM, BLOCK_N);
+    if (leader) {  // pair: the leader CTA issues for both
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM * kCtas, BLOCK_N);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t it = 0;
       [[maybe_unused]] int mtrace = 0;
       if constexpr (kRows) mbar_wait(b_full_bar, 0);
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = unit; tile < p.num_tiles; tile += unit_stride, ++it) {
         const uint32_t acc = it & 1u;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(tmem_empty_bar(acc), acc_phase ^ 1u);
@@ -331,16 +367,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
               for (int k = 0; k < 4; ++k) {
                 // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
                 // +2 in the (addr >> 4) start-address field
-                umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                if constexpr (kPair) umma_bf16_ss_pair(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                else umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
               }
             }
-            umma_commit(empty_bar(stage));  // smem stage reusable once these MMAs retire
+            // smem stage reusable once these MMAs retire (pair: in both CTAs)
+            if constexpr (kPair) umma_commit_pair(empty_bar(stage));
+            else umma_commit(empty_bar(stage));
           }
           __syncwarp();
           AI4E_TRACE(lane == 0 && mtrace < 192, 576 + mtrace); ++mtrace;  // MMAs issued
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        if (elect_one()) umma_commit(tmem_full_bar(acc));  // accumulator complete -> epilogue
+        if (elect_one()) {  // accumulator complete -> epilogue (pair: of both CTAs)
+          if constexpr (kPair) umma_commit_pair(tmem_full_bar(acc));
+          else umma_commit(tmem_full_bar(acc));
+        }
         __syncwarp();
       }
     }
@@ -373,10 +415,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     struct Chunk { int tile, c, m0, n0c; uint32_t it; };
     auto locate = [&](uint32_t q, Chunk& k) -> bool {
       k.it = q / kChunks;
-      k.tile = blockIdx.x + (int)k.it * gridDim.x;
+      k.tile = unit + (int)k.it * unit_stride;
       if (k.tile >= p.num_tiles) return false;
       k.c = (int)(q % kChunks);
-      k.m0 = (kRows ? 0 : (k.tile / p.tiles_n) * kBlockM) + quad * 32;
+      k.m0 = (kRows ? 0 : ((k.tile / p.tiles_n) * kCtas + (int)cta_rank) * kBlockM) + quad * 32;
       k.n0c = (kRows ? 0 : (k.tile % p.tiles_n) * BLOCK_N) + k.c * kChunkN;
       return true;
     };
@@ -422,7 +464,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       if (cur.c + 2 >= kChunks) {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
+        if (lane == 0) {
+          if constexpr (kPair) mbar_arrive_leader(tmem_empty_bar(acc));
+          else mbar_arrive(tmem_empty_bar(acc));
+        }
       }
       uint4 o[8];
 #pragma unroll
@@ -501,9 +546,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (p.residual != nullptr && lane == 0) {
       constexpr int kChunks = BLOCK_N / kChunkN;
       auto coords = [&](uint32_t q, int& m0, int& n0c) -> bool {
-        const int tile = blockIdx.x + (int)(q / kChunks) * gridDim.x;
+        const int tile = unit + (int)(q / kChunks) * unit_stride;
         if (tile >= p.num_tiles) return false;
-        m0 = (tile / p.tiles_n) * kBlockM;
+        m0 = ((tile / p.tiles_n) * kCtas + (int)cta_rank) * kBlockM;
         n0c = (tile % p.tiles_n) * BLOCK_N + (int)(q % kChunks) * kChunkN;
         return true;
       };
@@ -522,33 +567,67 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (kPair) cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still touch it
+  else __syncthreads();
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
-    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if constexpr (kPair) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    else tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
 // ----------------------------------------------------------------------------------------
 // host side
 // ----------------------------------------------------------------------------------------
-int igemm_pick_block_n(int Cout, long long M, bool has_res) {
+// Cost model behind the automatic tiling (cycles of the slowest CTA), from measured constants:
+//  * K loop: one 64-deep block costs max(MMA time, operand bytes / what L2 can feed, TMA latency /
+//    stages in flight).  MMA: 4 x 67 cycles up to N = 128, 512 at N = 256.  L2 -> SM: 126 B/clk for
+//    an SM alone, ~10.9 KB/clk for the whole GPU (tools/l2_probe.cu).  TMA latency ~2600 cycles.
+//  * epilogue: ~1050 cycles per 64-channel chunk (1250 with a residual), overlapped with the next
+//    tile's K loop, so a tile costs the longer of the two.
+//  * tiles are dealt round-robin to min(tiles, SMs) CTAs (or CTA pairs).
+static double igemm_model_cycles(int Cout, long long M, int num_k_blocks, bool has_res, int bn, bool pair) {
   const int sms = sm_count();
-  const long long tiles_m = (M + kBlockM - 1) / kBlockM;
-  // the widest tile that still leaves at least one tile per SM; wider tiles re-read A less.
-  // With a residual the epilogue needs 96 KB of shared memory, which would leave a 256-wide tile
-  // only two pipeline stages: those layers stop at 128 (measured: capping every layer at 128
-  // costs 0.4%).  AI4E_B200_MAX_BN lowers the cap for experiments.
-  static const int env_max_bn = [] { const char* v = getenv("AI4E_B200_MAX_BN"); return v ? atoi(v) : 256; }();
-  const int max_bn = std::min(env_max_bn, has_res ? 128 : 256);
-  for (int bn : {256, 128, 64}) {
-    if (Cout % bn || bn > max_bn) continue;
-    if (tiles_m * (Cout / bn) >= sms || bn == 64) return bn;
+  const int ctas = pair ? 2 : 1;
+  const long long tiles = ((M + kBlockM * ctas - 1) / (kBlockM * ctas)) * (Cout / bn);
+  const long long units = std::min<long long>(tiles, sms / ctas);
+  const double active = (double)units * ctas;
+  const double per_unit = (double)((tiles + units - 1) / units);
+  const double feed = std::min(120.0, 10900.0 / active);
+  const double bytes_kb = 16384.0 + bn * 128.0 / ctas;
+  const double mma = bn <= 128 ? 268.0 : 512.0;
+  const double room = 232448.0 - 34816.0 - (has_res ? 65536.0 : 0.0) - 300.0;
+  const double stages = std::max(1.0, std::min(12.0, std::floor(room / bytes_kb)));
+  const double kb = std::max({bytes_kb / feed, mma, 2600.0 / stages}) + (pair ? 40.0 : 25.0);
+  const double kloop = num_k_blocks * kb;
+  const double epi = (bn / 64) * (has_res ? 1250.0 : 1050.0);
+  return per_unit * std::max(kloop, epi) + std::min(kloop, epi) + 2500.0 + (pair ? 1500.0 : 0.0);
+}
+
+int igemm_tiling_candidates(int Cout, int out[8]) {
+  int n = 0;
+  for (int bn : {64, 128, 256}) {
+    if (Cout % bn) continue;
+    out[n++] = bn;
+    if (bn >= 128) out[n++] = bn + kTilingPair;
   }
-  for (int bn : {64, 128, 256})
-    if (Cout % bn == 0) return bn;
-  return 0;
+  return n;
+}
+
+int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res) {
+  int cand[8];
+  const int n = igemm_tiling_candidates(Cout, cand);
+  int best = 0;
+  double best_c = 0.0;
+  for (int i = 0; i < n; ++i) {
+    const bool pair = cand[i] >= kTilingPair;
+    const int bn = pair ? cand[i] - kTilingPair : cand[i];
+    // ties go to the later candidate only when it is clearly better: single-CTA and narrower first
+    const double c = igemm_model_cycles(Cout, M, num_k_blocks, has_res, bn, pair) * (pair ? 1.02 : 1.0);
+    if (best == 0 || c < best_c * 0.985) { best = cand[i]; best_c = c; }
+  }
+  return best;
 }
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad) {
@@ -581,6 +660,7 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   q.residual = (const bf16*)residual; q.out = (bf16*)out;
   plan->max_batch = N;
   plan->stem_mode = kModeGeneric;
+  plan->tuned_tiling = plan->tuned_batch = 0;
   q.stem_rb = 0; q.dbg = nullptr;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
@@ -645,6 +725,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   plan->max_batch = N;
   const bool rows = (W % 16 == 0) && Q <= kBlockM && !getenv("AI4E_B200_STEM_IM2COL");
   plan->stem_mode = rows ? kModeStemRows : kModeStemIm2col;
+  plan->tuned_tiling = plan->tuned_batch = 0;
   const uint32_t es4[4] = {1, 1, 1, 1};
   int rc;
   if (rows) {
@@ -689,25 +770,25 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   return AI4E_OK;
 }
 
-template <int BN, int kMode>
+template <int BN, int kMode, bool kPair = false>
 static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const IgemmParams& prm, int grid,
                            cudaStream_t stream) {
   static unsigned long long attr_done = 0;  // bit per device
   int dev = 0;
   AI4E_CUDA_TRY(cudaGetDevice(&dev));
   if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN, kMode>::kSmemLimit));
+    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       IgemmCfg<BN, kMode, kPair>::kSmemLimit));
     attr_done |= 1ull << dev;
   }
-  AI4E_CUDA_TRY(launch_pdl(conv_igemm_kernel<BN, kMode>, dim3(grid), dim3(kIgemmThreads),
-                           (size_t)IgemmCfg<BN, kMode>::smem_bytes(prm.residual != nullptr), stream, plan.tmap_a, tb,
-                           plan.tmap_out,
-                           plan.tmap_res, prm));
+  AI4E_CUDA_TRY(launch_pdl_cluster(conv_igemm_kernel<BN, kMode, kPair>, dim3(grid), dim3(kIgemmThreads),
+                                   (size_t)IgemmCfg<BN, kMode, kPair>::smem_bytes(prm.residual != nullptr), stream,
+                                   kPair ? 2 : 1, plan.tmap_a, tb, plan.tmap_out, plan.tmap_res, prm));
   return AI4E_OK;
 }
 
-int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream_t stream) {
+// `tiling`: 0 = automatic; otherwise BLOCK_N (64 / 128 / 256), + kTilingPair for the CTA-pair kernel.
+int igemm_launch(const IgemmPlan& plan, int batch, int tiling, cudaStream_t stream) {
   AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "conv(igemm): batch %d outside plan (max %d)", batch,
                plan.max_batch);
   IgemmParams prm = plan.prm;
@@ -726,19 +807,70 @@ int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream
     return igemm_launch_bn<64, kModeStemIm2col>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()),
                                                 stream);
   }
-  const int bn = force_block_n ? force_block_n : igemm_pick_block_n(prm.Cout, M, prm.residual != nullptr);
+  if (tiling == 0) {
+    if (const char* v = getenv("AI4E_B200_TILE")) {  // developer aid, e.g. "128" or "256p"
+      tiling = atoi(v);
+      if (strchr(v, 'p')) tiling += kTilingPair;
+    }
+  }
+  if (tiling == 0 && plan.tuned_tiling && batch == plan.tuned_batch) tiling = plan.tuned_tiling;
+  if (tiling == 0) tiling = igemm_pick_tiling(prm.Cout, M, prm.num_k_blocks, prm.residual != nullptr);
+  const bool pair = tiling >= kTilingPair;
+  const int bn = pair ? tiling - kTilingPair : tiling;
   const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
-  AI4E_REQUIRE(bi >= 0 && plan.has_bn[bi], "conv(igemm): BLOCK_N %d not available for Cout %d", bn, prm.Cout);
+  AI4E_REQUIRE(bi >= 0 && plan.has_bn[bi] && (!pair || bi > 0), "conv(igemm): tiling %d not available for Cout %d", tiling,
+               prm.Cout);
   prm.M = (int)M;
-  prm.tiles_m = (int)((M + kBlockM - 1) / kBlockM);
+  const int rows = kBlockM * (pair ? 2 : 1);
+  prm.tiles_m = (int)((M + rows - 1) / rows);
   prm.tiles_n = prm.Cout / bn;
   prm.num_tiles = prm.tiles_m * prm.tiles_n;
+  if (pair) {
+    // a pair tile's halves are loaded with the weight map whose box is BLOCK_N / 2 rows
+    const int grid = 2 * std::min(prm.num_tiles, sm_count() / 2);
+    if (bn == 128) return igemm_launch_bn<128, kModeGeneric, true>(plan, plan.tmap_b[bi - 1], prm, grid, stream);
+    return igemm_launch_bn<256, kModeGeneric, true>(plan, plan.tmap_b[bi - 1], prm, grid, stream);
+  }
   const int grid = std::min(prm.num_tiles, sm_count());
   switch (bn) {
     case 64: return igemm_launch_bn<64, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
     case 128: return igemm_launch_bn<128, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
     default: return igemm_launch_bn<256, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
   }
+}
+
+// Times every tiling of this layer on the plan's own buffers (their contents do not matter, the
+// work is data-independent) and keeps the fastest for launches with this batch.
+int igemm_autotune(IgemmPlan* plan, int batch, cudaStream_t stream, float* best_us_out) {
+  if (plan->stem_mode != kModeGeneric) return AI4E_OK;
+  int cand[8];
+  const int n = igemm_tiling_candidates(plan->prm.Cout, cand);
+  cudaEvent_t e0, e1;
+  AI4E_CUDA_TRY(cudaEventCreate(&e0));
+  AI4E_CUDA_TRY(cudaEventCreate(&e1));
+  constexpr int kReps = 4;
+  int best = 0, rc = AI4E_OK;
+  float best_ms = 0.f;
+  for (int i = 0; i < n && rc == AI4E_OK; ++i) {
+    for (int pass = 0; pass < 2 && rc == AI4E_OK; ++pass) {  // pass 0 warms up (attributes, instruction cache)
+      cudaEventRecord(e0, stream);
+      for (int r = 0; r < (pass ? kReps : 1) && rc == AI4E_OK; ++r) rc = igemm_launch(*plan, batch, cand[i], stream);
+      cudaEventRecord(e1, stream);
+      if (cudaEventSynchronize(e1) != cudaSuccess) rc = AI4E_ERR_CUDA;
+    }
+    float ms = 0.f;
+    if (rc == AI4E_OK && cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess && (best == 0 || ms < best_ms)) {
+      best = cand[i];
+      best_ms = ms;
+    }
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (rc != AI4E_OK) return rc;
+  plan->tuned_tiling = best;
+  plan->tuned_batch = batch;
+  if (best_us_out) *best_us_out = best_ms * 1e3f / kReps;
+  return AI4E_OK;
 }
 
 }  // namespace ai4e

@@ -453,6 +453,24 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
     if (rc) return fail(rc);
   }
 
+  // ---- per-layer tiling: time the candidates once, at the full micro-batch (smaller batches fall
+  // back to the cost model).  ~50 ms for ResNet-50.  AI4E_B200_NO_AUTOTUNE=1 skips it.
+  if (!getenv("AI4E_B200_NO_AUTOTUNE")) {
+    const bool log = getenv("AI4E_B200_TUNE_LOG") != nullptr;
+    for (LayerRt& L : e->layers) {
+      if (L.d.op != AI4E_OP_CONV || !L.igemm) continue;
+      float us = 0.f;
+      int rc = igemm_autotune(&L.plan, max_batch, nullptr, &us);
+      if (rc) return fail(rc);
+      if (log && L.plan.tuned_tiling)
+        fprintf(stderr, "ai4e_b200: %dx%d %d->%d k%d s%d%s: tiling %d%s (%.1f us)\n", L.in_h, L.in_w, L.d.cin, L.d.cout,
+                L.d.kh, L.d.stride, L.d.res_buf >= 0 ? " +res" : "", L.plan.tuned_tiling % kTilingPair,
+                L.plan.tuned_tiling >= kTilingPair ? " pair" : "", us);
+    }
+    // the timed launches wrote garbage into the activation buffers; nothing reads them before
+    // the next forward overwrites them
+  }
+
   // ---- staging: images up to 1.5x the model input area (covers a 256 -> 224 resize+crop)
   const size_t in_bytes = (size_t)desc->in_h * desc->in_w * desc->in_c;
   size_t slot = in_bytes + in_bytes / 2;

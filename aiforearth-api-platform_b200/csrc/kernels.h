@@ -45,14 +45,18 @@ struct IgemmPlan {
   IgemmParams prm;        // everything but the batch-dependent fields
   int max_batch;
   int stem_mode;          // 0 generic conv; 1 stem via im2col super-pixels; 2 stem via row buffers
+  int tuned_tiling;       // igemm_autotune's choice for launches with tuned_batch images (0 = none)
+  int tuned_batch;
 };
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
-int igemm_pick_block_n(int Cout, long long M, bool has_res);
+constexpr int kTilingPair = 1000;  // tiling code = BLOCK_N (+ kTilingPair: CTA-pair kernel, tcgen05 cta_group::2)
+int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res);
 int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
                     int pad, const void* residual, int relu, void* out);
-int igemm_launch(const IgemmPlan& plan, int batch, int force_block_n, cudaStream_t stream);
+int igemm_launch(const IgemmPlan& plan, int batch, int tiling, cudaStream_t stream);
+int igemm_autotune(IgemmPlan* plan, int batch, cudaStream_t stream, float* best_us_out);
 // tensor-core stem: 7x7 stride 2 pad 3, NHWC4 input, 64 outputs
 int stem_supported(int H, int W, int Cin, int Cout, int R, int S, int stride, int pad);
 void stem_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][7][7][4] -> [64][7][4][8]

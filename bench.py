@@ -15,9 +15,12 @@ Printed keys (one JSON line, rank 0):
   e2e           the same metric through the public API with HOST buffers: page-locked uint8
                 batches -> Engine.submit_batch / wait (H2D + kernels + D2H of top-5 inside the
                 timed region, three batches in flight)
-  roofline      dominant kernel = the tcgen05 implicit-GEMM convolution: algorithmic conv FLOPs
-                of one step / summed device time of its launches (per-layer CUDA events,
-                ai4e_engine_profile), against the measured bf16 peak in MEASURED_PEAKS.json
+  roofline      dominant kernel = the tcgen05 implicit-GEMM convolution (all 53 convolutions):
+                algorithmic conv FLOPs of one step / summed device time of its launches (per-layer
+                CUDA events, ai4e_engine_profile: each launch timed alone, so the overlap the
+                engine gets from programmatic dependent launch is NOT credited), against the
+                measured sustained bf16 peak in MEASURED_PEAKS.json; `traffic` = DRAM bytes of
+                those launches from the ncu capture recorded in profiles/ (null if absent)
   cpu_baseline  the CPU oracle (torchvision fp32, preprocessing included) on the host cores,
                 bounded sample, rank 0 at N=1 only
 `--impl reference` times that CPU path alone (the reference's own arithmetic lives in a
@@ -179,28 +182,15 @@ def main():
         return
 
     import torch
-    import torch.distributed as dist
     from ai4e_b200.engine import Engine
     from ai4e_b200.models import build_resnet_program, synthetic_state_dict
+    from ai4e_b200.replicas import ReplicaGroup
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x: float) -> float:
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    group = ReplicaGroup("nccl")  # measurement plumbing only: barrier + max of the per-rank times
+    barrier, max_over_ranks = group.barrier, group.max_over_ranks
 
     B, K, W = args.batch, args.steps, args.warmup
     prog = build_resnet_program(ARCH, synthetic_state_dict(ARCH, seed=0), HW, HW)
@@ -271,8 +261,9 @@ def main():
             continue
         p_, q_ = (h + 2 * l.pad - l.kh) // l.stride + 1, (w + 2 * l.pad - l.kw) // l.stride + 1
         shapes[l.out_buf] = (p_, q_)
-        if l.op == L.OP_CONV and l.cin % 64 == 0:
-            conv_flops += 2 * B * p_ * q_ * l.cout * l.cin * l.kh * l.kw
+        if l.op == L.OP_CONV:  # every convolution runs on conv_igemm_kernel (the stem in its row-buffer mode)
+            cin = IN_C if li == 0 else l.cin  # the stem's 4th input channel is padding, not work
+            conv_flops += 2 * B * p_ * q_ * l.cout * cin * l.kh * l.kw
             igemm_ms += float(ms[li + 1])
             igemm_launches += 1
     if args.dump_layers and rank == 0:
@@ -291,6 +282,10 @@ def main():
                          "ms": t, "tflops": fl / t / 1e9 if t > 0 else 0, "gbs": byt / t / 1e6 if t > 0 else 0,
                          "M": B * p_ * q_})
         json.dump({"batch": B, "preprocess_ms": float(ms[0]), "layers": rows}, open(args.dump_layers, "w"), indent=1)
+    traffic = None  # DRAM bytes of the conv launches of one step, from the committed ncu capture
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(tpath) and B == 64:
+        traffic = json.load(open(tpath)).get("dram_bytes_per_step")
     achieved = conv_flops / (igemm_ms / 1e3) / 1e12
     peak_t = peaks["bf16_tflops_sustained"]
     pre_bytes = B * (HW * HW * IN_C + HW * HW * 4 * 2)  # u8 in + bf16 NHWC4 out (the engine's layout)
@@ -305,14 +300,14 @@ def main():
                 "d2h_bytes_per_step": B * (5 * 4 + 5 * 4 + prog.num_classes * 4),
                 "api": "Engine.submit_batch/wait, page-locked host batches, 3 batches in flight"},
         "gpu_launches": stats["launches_per_forward"] * K,
-        "roofline": {"bound": "tensor", "kernel": "conv_igemm_kernel (52 launches per step)", "achieved": achieved,
-                     "peak": peak_t, "unit": "TFLOP/s", "frac": achieved / peak_t, "traffic": None,
+        "roofline": {"bound": "tensor", "kernel": f"conv_igemm_kernel ({igemm_launches} launches per step)", "achieved": achieved,
+                     "peak": peak_t, "unit": "TFLOP/s", "frac": achieved / peak_t, "traffic": traffic,
                      "peak_source": f"{peaks['source']} bf16 sustained", "ms_per_step_in_kernel": igemm_ms,
                      "flops_per_step": conv_flops},
         "roofline_preprocess": {"bound": "hbm", "kernel": "preprocess_lut_kernel", "achieved": pre_gbs,
                                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": pre_gbs / peaks["hbm_gbs"],
                                 "bytes_per_launch": pre_bytes, "ms": float(ms[0])},
-        "layer_ms": {"preprocess": float(ms[0]), "stem_direct": float(ms[1]), "maxpool": float(ms[2]),
+        "layer_ms": {"preprocess": float(ms[0]), "stem": float(ms[1]), "maxpool": float(ms[2]),
                      "igemm_convs": igemm_ms, "head": float(ms[-1]), "sum": float(ms.sum())},
         "latency_ms": {"p50": stats["lat_ms_p50"], "p99": stats["lat_ms_p99"], "of": "submit_batch -> results on host"},
         "clocks": clocks,
@@ -327,8 +322,7 @@ def main():
     eng.close()
     if rank == 0:
         print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    group.close()
 
 
 if __name__ == "__main__":

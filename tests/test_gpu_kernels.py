@@ -223,6 +223,34 @@ def test_conv_igemm_many_tiles_multi_wave():
     _check_conv(out, want)
 
 
+# CTA-pair kernel (tcgen05 cta_group::2, 256-row tiles): forced through the developer override,
+# whatever the automatic choice would be.  (tiling, case)
+PAIR_CASES = [
+    ("128p", (2, 56, 56, 64, 256, 1, 1, 0, True, True)),     # 24.5 pair tiles: the last one is half empty
+    ("256p", (2, 56, 56, 64, 256, 1, 1, 0, True, False)),
+    ("128p", (8, 56, 56, 256, 128, 1, 1, 0, True, False)),   # more pair tiles than SM pairs: phases wrap
+    ("128p", (2, 14, 14, 256, 256, 3, 1, 1, True, False)),
+    ("256p", (2, 14, 14, 256, 256, 3, 1, 1, True, True)),
+    ("128p", (3, 7, 7, 512, 512, 3, 1, 1, True, False)),     # M = 147: one pair tile, second CTA mostly padding
+    ("128p", (1, 7, 7, 512, 2048, 1, 1, 0, True, True)),     # M = 49: the second CTA of every pair has no rows
+    ("256p", (5, 13, 17, 128, 256, 3, 2, 1, False, True)),   # ragged geometry, stride 2
+    ("256p", (6, 56, 56, 128, 256, 3, 1, 1, True, True)),    # 18 K blocks, 74 pair tiles
+    ("128p", (64, 14, 14, 1024, 256, 1, 1, 0, True, False)), # ResNet-50 layer3 conv1 at full batch
+]
+
+
+@pytest.mark.parametrize("tiling,case", PAIR_CASES, ids=lambda c: c if isinstance(c, str) else "x".join(str(v) for v in c[:8]))
+def test_conv_igemm_cta_pair_vs_oracle(tiling, case, monkeypatch):
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, cin, cout, k, stride, pad, relu, residual = case
+    x, wt, bias, res, want = _conv_case(*case, seed=sum(case[:8]) + 1)
+    monkeypatch.setenv("AI4E_B200_TILE", tiling)
+    out = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), stride, pad, res.cuda() if res is not None else None,
+                         relu, algo=L.CONV_IGEMM)
+    torch.cuda.synchronize()
+    _check_conv(out, want)
+
+
 def test_conv_igemm_rejects_unsupported():
     from ai4e_b200 import ops, _lib as L, Ai4eError
     x = torch.zeros((1, 8, 8, 48), dtype=torch.bfloat16, device="cuda")
