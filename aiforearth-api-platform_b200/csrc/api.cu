@@ -91,6 +91,8 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
       for (int i = 0; i < 40; ++i)  // epilogue leader, per 64-channel chunk
         fprintf(f, "E %d %lld %lld %lld %lld %lld %lld\n", i, h[768 + 6 * i], h[769 + 6 * i], h[770 + 6 * i], h[771 + 6 * i],
                 h[772 + 6 * i], h[773 + 6 * i]);
+      // phases of CTA 0: entry, set-up done, previous kernel finished, MMAs issued, epilogue done, all warps done
+      fprintf(f, "T %lld %lld %lld %lld %lld %lld\n", h[1008], h[1009], h[1010], h[1011], h[1012], h[1013]);
       fclose(f);
     }
     return rc;

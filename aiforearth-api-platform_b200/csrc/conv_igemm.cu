@@ -158,6 +158,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  AI4E_TRACE(threadIdx.x == 0, 1008);  // kernel entry
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -197,11 +198,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
+  AI4E_TRACE(threadIdx.x == 0, 1009);  // set-up done
   // everything above touched only this kernel's own shared memory / TMEM / parameters: it may
-  // overlap the previous layer's tail.  From here on we read its output and overwrite buffers
-  // it may still read.
+  // overlap the previous layer's tail.  From here on the roles that read the previous layer's
+  // output or overwrite buffers it may still read (activation loads, residual loads, output
+  // stores) first wait for it (griddepcontrol.wait is per thread); the weight producer does not -
+  // weights are constants, so the first stages of B fill while the previous kernel drains.
   pdl_launch_dependents();
-  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
@@ -218,6 +221,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             tma_load_2d(bres_base + i * BLOCK_N * 16, &tmap_b, b_full_bar, i * 8, 0);
         }
         __syncwarp();
+      }
+      pdl_wait();
+      AI4E_TRACE(threadIdx.x == 0, 1010);  // previous kernel finished
+      if constexpr (kRows) {
         for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
           const int n_img = tile / p.P;
           const int y0 = (tile - n_img * p.P) * 2 - 3;
@@ -385,6 +392,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
         __syncwarp();
       }
+      AI4E_TRACE(lane == 0, 1011);  // all MMAs issued
     }
   } else if (warp < 2 + kEpiWarps) {
     // ------------------------------- epilogue -----------------------------------
@@ -430,6 +438,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       tmem_ld_32x32b_x32(t_addr, vlo);
       tmem_ld_32x32b_x32(t_addr + 32, vhi);
     };
+    pdl_wait();
     Chunk cur, nxt;
     bool have = locate(side, cur);
     bool ld_issued = false;  // the accumulator load of `cur` was already issued at the end of the previous chunk
@@ -536,6 +545,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       cur = nxt;
     }
     if (lane == 0) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
+    AI4E_TRACE(ew == 0 && lane == 0, 1012);  // epilogue done
   } else if (warp == 3 + kEpiWarps) {
     // ------------------------------- residual warp -------------------------------
     // One thread walks the CTA's chunks in order and keeps two 128-row x 64-channel residual
@@ -544,6 +554,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     // so the chunk four ahead is also pulled into L2.  (Issued from the epilogue warps these
     // TMA instructions cost each of them ~600 cycles per chunk.)
     if (p.residual != nullptr && lane == 0) {
+      pdl_wait();
       constexpr int kChunks = BLOCK_N / kChunkN;
       auto coords = [&](uint32_t q, int& m0, int& n0c) -> bool {
         const int tile = unit + (int)(q / kChunks) * unit_stride;
@@ -569,6 +580,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   tc_fence_before();
   if constexpr (kPair) cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still touch it
   else __syncthreads();
+  AI4E_TRACE(threadIdx.x == 0, 1013);  // every warp done
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
