@@ -46,22 +46,36 @@ __device__ __forceinline__ uint16_t norm_to_bf16(float v, float mean, float stdv
   return __bfloat16_as_ushort(__float2bfloat16_rn(x));
 }
 
+// Shared-memory budget of the streaming kernel: the look-up table is replicated per lane
+// (entry (c, v) for lane l lives in word (c * 256 + v) * 32 + l, i.e. always in bank l), so the
+// random byte-indexed look-ups never conflict.  (With one 512-byte table per channel ncu showed the
+// kernel bound by the shared-memory queue: mio_throttle 19 of 37 stall cycles per issue, 537 k bank
+// conflicts, 15 % issue utilisation, 19.9 us for 35 MB.)  One CTA per SM; the source chunks of a CTA
+// are all requested up front, kLutStages deep, because one chunk converts in a fraction of the
+// ~1.5 us its load takes.
 template <int C>
-__global__ void __launch_bounds__(kLutThreads)
-preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chunks) {
-  extern __shared__ __align__(128) uint8_t smem_raw[];
-  // layout: [2 stages][kChunkPix*C bytes] | lut[C][256] u16 | 2 mbarriers
-  uint8_t* stage_buf = smem_raw;
-  uint16_t* lut = reinterpret_cast<uint16_t*>(smem_raw + 2 * kChunkPix * C);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + 2 * kChunkPix * C + C * 256 * 2);
+struct LutCfg {
+  static constexpr int kStages = C == 3 ? 6 : 5;
+  static constexpr int kLutBytes = C * 256 * 32 * 4;      // 96 / 128 KiB
+  static constexpr int kStageBytes = kChunkPix * C;       // 12 / 16 KiB
+  static constexpr int kSmem = kLutBytes + kStages * kStageBytes + kStages * 8;
+};
 
-  const int tid = threadIdx.x;
+template <int C>
+__global__ void __launch_bounds__(kLutThreads, 1)
+preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chunks) {
+  using Cfg = LutCfg<C>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  // layout: lut[C][256][32] u32 | [kStages][kChunkPix*C bytes] | mbarriers
+  uint32_t* lut = reinterpret_cast<uint32_t*>(smem_raw);
+  uint8_t* stage_buf = smem_raw + Cfg::kLutBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + Cfg::kLutBytes + kStages * Cfg::kStageBytes);
+
+  const int tid = threadIdx.x, lane = tid & 31;
   pdl_launch_dependents();  // the stem may start its prologue while this kernel streams
-#pragma unroll
-  for (int c = 0; c < C; ++c) lut[c * 256 + tid] = norm_to_bf16((float)tid, p.mean[c], p.stdv[c]);
   if (tid == 0) {
-    mbar_init(smem_u32(&bars[0]), 1);
-    mbar_init(smem_u32(&bars[1]), 1);
+    for (int s = 0; s < kStages; ++s) mbar_init(smem_u32(&bars[s]), 1);
     fence_mbar_init();
   }
   __syncthreads();
@@ -76,68 +90,101 @@ preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chu
     const uint8_t* g = p.src + (long long)img * p.src_image_stride + (long long)px0 * C;
     const uint32_t bar = smem_u32(&bars[stage]);
     mbar_expect_tx(bar, bytes);
-    bulk_load_1d(smem_u32(stage_buf + stage * kChunkPix * C), g, bytes, bar);
+    bulk_load_1d(smem_u32(stage_buf + stage * Cfg::kStageBytes), g, bytes, bar);
   };
+  if (tid == 0) {  // the source is the caller's buffer, not a predecessor kernel's output
+    for (int s = 0; s < kStages; ++s) {
+      const int chunk = blockIdx.x + s * gridDim.x;
+      if (chunk < total_chunks) issue(chunk, s);
+    }
+  }
+  // table: thread v computes entry v of each channel once and writes its 32 copies, lane l starting
+  // at copy l so that the 32 lanes of a warp hit 32 different banks
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const uint32_t e = norm_to_bf16((float)tid, p.mean[c], p.stdv[c]);
+    uint32_t* row = lut + (c * 256 + tid) * 32;
+#pragma unroll 8
+    for (int k = 0; k < 32; ++k) row[(k + lane) & 31] = e;
+  }
+  __syncthreads();
+  const uint32_t* lut_lane = lut + lane;
 
-  int chunk = blockIdx.x;
-  if (tid == 0 && chunk < total_chunks) issue(chunk, 0);
   uint32_t it = 0;
-  for (; chunk < total_chunks; chunk += gridDim.x, ++it) {
-    const int stage = it & 1;
-    const int next = chunk + gridDim.x;
-    if (tid == 0 && next < total_chunks) issue(next, stage ^ 1);
-    mbar_wait(smem_u32(&bars[stage]), (it >> 1) & 1);
+  for (int chunk = blockIdx.x; chunk < total_chunks; chunk += gridDim.x, ++it) {
+    const int stage_i = it % kStages;
+    mbar_wait(smem_u32(&bars[stage_i]), (it / kStages) & 1);
 
     const int img = chunk / chunks_per_image;
     const int cj = chunk - img * chunks_per_image;
-    const int px = cj * kChunkPix + tid * kPixPerThread;
-    if (px < hw) {
-      // 16 pixels of C interleaved bytes = C 16-byte vectors; stride 16*C bytes between
-      // lanes is bank-conflict free for C = 3 and C = 4
-      const uint4* s4 = reinterpret_cast<const uint4*>(stage_buf + stage * kChunkPix * C +
-                                                       tid * kPixPerThread * C);
-      uint32_t w[4 * C];
+    auto look = [&](int c, uint32_t v) -> uint32_t { return lut_lane[(c * 256 + v) * 32]; };
+    const uint8_t* stage = stage_buf + stage_i * Cfg::kStageBytes;
+    if (p.layout == 0) {
+      // NCHW planes: a thread converts 16 consecutive pixels (C 16-byte vectors; the 16*C-byte stride
+      // between lanes is bank-conflict free for C = 3 and C = 4) and writes 32 contiguous bytes per plane
+      const int px = cj * kChunkPix + tid * kPixPerThread;
+      if (px < hw) {
+        const uint4* s4 = reinterpret_cast<const uint4*>(stage + tid * kPixPerThread * C);
+        uint32_t w[4 * C];
 #pragma unroll
-      for (int i = 0; i < C; ++i) {
-        uint4 v = s4[i];
-        w[4 * i + 0] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
-      }
-      auto byte_at = [&](int k) -> uint32_t { return (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu; };
-      if (p.layout == 0) {
+        for (int i = 0; i < C; ++i) {
+          uint4 v = s4[i];
+          w[4 * i + 0] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+        }
+        auto byte_at = [&](int k) -> uint32_t { return (w[k >> 2] >> ((k & 3) * 8)) & 0xFFu; };
 #pragma unroll
         for (int c = 0; c < C; ++c) {
           uint32_t o[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const uint32_t lo = lut[c * 256 + byte_at((2 * j) * C + c)];
-            const uint32_t hi = lut[c * 256 + byte_at((2 * j + 1) * C + c)];
+            const uint32_t lo = look(c, byte_at((2 * j) * C + c));
+            const uint32_t hi = look(c, byte_at((2 * j + 1) * C + c));
             o[j] = lo | (hi << 16);
           }
           uint4* d = reinterpret_cast<uint4*>(p.dst + ((long long)(img * C + c) * hw + px));
           d[0] = make_uint4(o[0], o[1], o[2], o[3]);
           d[1] = make_uint4(o[4], o[5], o[6], o[7]);
         }
-      } else {
-        // NHWC with channel padding to 4 (C == 3: pad lane is +0.0; C == 4: all real)
-        uint4* d = reinterpret_cast<uint4*>(p.dst + ((long long)img * hw + px) * 4);
+      }
+    } else {
+      // NHWC with channel padding to 4 (C == 3: pad lane is +0.0; C == 4: all real).  Two pixels
+      // make one 16-byte store; in each of 8 rounds a warp converts 64 consecutive pixels, lane l the
+      // pair l, so the warp writes 512 contiguous bytes.  (16 consecutive pixels per thread made every
+      // store instruction touch 32 different 128-byte lines.)
+      const int npx = min(kChunkPix, hw - cj * kChunkPix);
+      uint4* d = reinterpret_cast<uint4*>(p.dst + ((long long)img * hw + cj * kChunkPix) * 4);
+      const int warp_px0 = (tid >> 5) * 32 * kPixPerThread;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {  // two pixels per 16-byte store
+      for (int j = 0; j < 8; ++j) {
+        const int pix = warp_px0 + j * 64 + lane * 2;
+        if (pix < npx) {
+          uint32_t b[2 * C];  // the bytes of the two pixels
+          if constexpr (C == 3) {
+            const uint16_t* sp = reinterpret_cast<const uint16_t*>(stage + pix * 3);
+            const uint32_t h0 = sp[0], h1 = sp[1], h2 = sp[2];
+            b[0] = h0 & 0xFF; b[1] = h0 >> 8; b[2] = h1 & 0xFF; b[3] = h1 >> 8; b[4] = h2 & 0xFF; b[5] = h2 >> 8;
+          } else {
+            const uint2 v = *reinterpret_cast<const uint2*>(stage + pix * 4);
+            b[0] = v.x & 0xFF; b[1] = (v.x >> 8) & 0xFF; b[2] = (v.x >> 16) & 0xFF; b[3] = v.x >> 24;
+            b[4] = v.y & 0xFF; b[5] = (v.y >> 8) & 0xFF; b[6] = (v.y >> 16) & 0xFF; b[7] = v.y >> 24;
+          }
           uint32_t o[4];
 #pragma unroll
           for (int q = 0; q < 2; ++q) {
-            const int pix = 2 * j + q;
-            const uint32_t c0 = lut[0 * 256 + byte_at(pix * C + 0)];
-            const uint32_t c1 = lut[1 * 256 + byte_at(pix * C + 1)];
-            const uint32_t c2 = lut[2 * 256 + byte_at(pix * C + 2)];
-            const uint32_t c3 = (C == 4) ? lut[3 * 256 + byte_at(pix * C + (C - 1))] : 0u;
+            const uint32_t c0 = look(0, b[q * C + 0]);
+            const uint32_t c1 = look(1, b[q * C + 1]);
+            const uint32_t c2 = look(2, b[q * C + 2]);
+            const uint32_t c3 = (C == 4) ? look(C - 1, b[q * C + (C - 1)]) : 0u;
             o[2 * q] = c0 | (c1 << 16);
             o[2 * q + 1] = c2 | (c3 << 16);
           }
-          d[j] = make_uint4(o[0], o[1], o[2], o[3]);
+          d[pix >> 1] = make_uint4(o[0], o[1], o[2], o[3]);
         }
       }
     }
-    __syncthreads();  // stage buffer is free for the copy issued next iteration
+    __syncthreads();  // every thread has read this stage: refill it with the chunk kStages ahead
+    const int next = chunk + kStages * gridDim.x;
+    if (tid == 0 && next < total_chunks) issue(next, stage_i);
   }
 }
 
@@ -259,17 +306,15 @@ int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int
     const int chunks_per_image = (int)((hw + kChunkPix - 1) / kChunkPix);
     const long long total_chunks = (long long)chunks_per_image * batch;
     AI4E_REQUIRE(total_chunks < (1ll << 31), "preprocess: batch too large");
-    const size_t smem = 2 * (size_t)kChunkPix * channels + (size_t)channels * 256 * 2 + 16;
-    const int ctas_per_sm = 4;
-    const int grid = (int)std::min<long long>(total_chunks, (long long)sm_count() * ctas_per_sm);
+    const int grid = (int)std::min<long long>(total_chunks, (long long)sm_count());  // one CTA per SM (shared memory)
     if (channels == 3) {
       static bool attr3 = false;
-      if (!attr3) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr3 = true; }
-      preprocess_lut_kernel<3><<<grid, kLutThreads, smem, stream>>>(p, chunks_per_image, (int)total_chunks);
+      if (!attr3) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LutCfg<3>::kSmem)); attr3 = true; }
+      preprocess_lut_kernel<3><<<grid, kLutThreads, LutCfg<3>::kSmem, stream>>>(p, chunks_per_image, (int)total_chunks);
     } else {
       static bool attr4 = false;
-      if (!attr4) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr4 = true; }
-      preprocess_lut_kernel<4><<<grid, kLutThreads, smem, stream>>>(p, chunks_per_image, (int)total_chunks);
+      if (!attr4) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, LutCfg<4>::kSmem)); attr4 = true; }
+      preprocess_lut_kernel<4><<<grid, kLutThreads, LutCfg<4>::kSmem, stream>>>(p, chunks_per_image, (int)total_chunks);
     }
     AI4E_CUDA_TRY(cudaGetLastError());
     return 1;
