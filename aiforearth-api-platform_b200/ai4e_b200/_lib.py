@@ -62,6 +62,7 @@ SIGNATURES = {
     "ai4e_device_count": (_i, [C.POINTER(C.c_int)]),
     "ai4e_preprocess": (_i, [_vp, _i, _i, _i, _i, _i64, _i, _i, _i, _i, _i, _fp, _fp, _i, _i, _vp, _vp]),
     "ai4e_conv_layer": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp]),
+    "ai4e_bottleneck_tail": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp]),
     "ai4e_maxpool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ai4e_head": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),
     "ai4e_head_noalloc": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),

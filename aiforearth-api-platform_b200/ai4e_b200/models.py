@@ -208,8 +208,10 @@ def build_resnet_program(arch: str, state_dict: dict, in_h: int = 224, in_w: int
             if kind == "bottleneck":
                 t1 = conv(pre + ".conv1", pre + ".bn1", x)
                 t2 = conv(pre + ".conv2", pre + ".bn2", t1, stride=stride, pad=1)
-                release(t1)
+                # conv2 and conv3 may run as one kernel that reads t1 while it writes y (K4b): y must
+                # not land in t1's slot, so t1 is released only after y has its own
                 y = conv(pre + ".conv3", pre + ".bn3", t2, res=identity)
+                release(t1)
                 release(t2)
             else:
                 t1 = conv(pre + ".conv1", pre + ".bn1", x, stride=stride, pad=1)

@@ -66,6 +66,25 @@ def conv_layer(x_nhwc: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tens
     return out
 
 
+def bottleneck_tail(x_nhwc: torch.Tensor, w2_krsc: torch.Tensor, b2: torch.Tensor, stride: int, pad: int,
+                    w3_kc: torch.Tensor, b3: torch.Tensor, residual: torch.Tensor, stream=None) -> torch.Tensor:
+    """relu(conv1x1(relu(conv(x; w2) + b2); w3) + b3 + residual) in one kernel (K4b).
+    x [B,H,W,Cin] bf16, w2 [Cmid,kh,kw,Cin] bf16, w3 [Cout,Cmid] bf16, residual [B,P,Q,Cout] bf16."""
+    lib = L.load()
+    for t in (x_nhwc, w2_krsc, w3_kc, residual):
+        assert t.is_contiguous() and t.dtype == torch.bfloat16
+    b, h, w, cin = x_nhwc.shape
+    cmid, kh, kw, _ = w2_krsc.shape
+    cout = w3_kc.shape[0]
+    p = (h + 2 * pad - kh) // stride + 1
+    q = (w + 2 * pad - kw) // stride + 1
+    assert tuple(residual.shape) == (b, p, q, cout)
+    out = torch.empty((b, p, q, cout), dtype=torch.bfloat16, device=x_nhwc.device)
+    L.check(lib.ai4e_bottleneck_tail(_ptr(x_nhwc), b, h, w, cin, _ptr(w2_krsc), _ptr(b2), cmid, kh, kw, stride, pad,
+                                     _ptr(w3_kc), _ptr(b3), cout, _ptr(residual), _ptr(out), _stream_ptr(stream)))
+    return out
+
+
 def maxpool(x_nhwc: torch.Tensor, k: int = 3, stride: int = 2, pad: int = 1, stream=None) -> torch.Tensor:
     lib = L.load()
     assert x_nhwc.is_contiguous() and x_nhwc.dtype == torch.bfloat16

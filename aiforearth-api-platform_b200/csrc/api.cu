@@ -100,6 +100,20 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 
+int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w, int cin, const void* d_w2_krsc,
+                         const float* d_bias2, int cmid, int kh, int kw, int stride, int pad, const void* d_w3_kc,
+                         const float* d_bias3, int cout, const void* d_residual, void* d_out_nhwc, void* stream) {
+  AI4E_REQUIRE(d_in_nhwc && d_w2_krsc && d_bias2 && d_w3_kc && d_bias3 && d_residual && d_out_nhwc,
+               "bottleneck tail: null pointer");
+  AI4E_REQUIRE(batch > 0 && h > 0 && w > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0, "bottleneck tail: bad geometry");
+  AI4E_REQUIRE(h + 2 * pad >= kh && w + 2 * pad >= kw, "bottleneck tail: filter larger than padded input");
+  FusedPlan plan;
+  int rc = fused_tail_make_plan(&plan, d_in_nhwc, batch, h, w, cin, d_w2_krsc, d_bias2, cmid, kh, kw, stride, pad, d_w3_kc,
+                                d_bias3, cout, d_residual, d_out_nhwc);
+  if (rc) return rc;
+  return fused_tail_launch(plan, batch, (cudaStream_t)stream);
+}
+
 int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
                  void* d_out_nhwc, void* stream) {
   return launch_maxpool(d_in_nhwc, batch, h, w, c, k, stride, pad, d_out_nhwc, (cudaStream_t)stream);

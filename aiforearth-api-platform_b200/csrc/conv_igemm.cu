@@ -32,6 +32,7 @@
 //            `warp_id % 4`; warps w and w+4 split the 64 channels of a chunk between them.
 #include "common.cuh"
 #include "kernels.h"
+#include "igemm_tiles.cuh"
 
 // Developer aid: -DAI4E_PIPE_TRACE makes CTA 0 record clock64 stamps of its pipeline into
 // IgemmParams::dbg (dumped by ai4e_conv_layer when AI4E_B200_PIPE_TRACE=<file> is set).  Compiled out
@@ -48,16 +49,6 @@
 
 namespace ai4e {
 
-constexpr int kBlockM = 128;
-constexpr int kBlockK = 64;  // 64 bf16 = 128 bytes = one swizzle row
-constexpr int kUmmaK = 16;
-constexpr int kEpiWarps = 8;                              // two warps per TMEM lane quadrant
-constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kIgemmThreads = 64 + kEpiThreads + 64;      // + A-producer warp, MMA warp, B-producer warp, residual warp
-constexpr int kABytes = kBlockM * kBlockK * 2;  // 16 KiB
-constexpr int kChunkN = 64;                               // epilogue works on 64 channels at a time
-constexpr int kChunkBytes = kBlockM * kChunkN * 2;        // 16 KiB: 128 rows x 128 bytes, swizzled
-constexpr int kSliceBytes = 32 * kChunkN * 2;             // 4 KiB: one epilogue warp's 32 rows of a chunk
 
 // Stem (7x7 stride 2, 3/4 input channels -> 64): the NHWC4 image is read as an [H][W/2][8] grid
 // of "super-pixels" (two adjacent pixels = 8 channels = 16 bytes, the smallest unit im2col-mode

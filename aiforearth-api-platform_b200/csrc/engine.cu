@@ -41,6 +41,9 @@ struct LayerRt {
   int in_h, in_w, out_h, out_w;
   bool igemm;
   IgemmPlan plan;
+  bool fused_first = false;  // this layer and the next run as one bottleneck_tail_kernel (fplan)
+  bool fused_second = false; // computed by the previous layer's launch
+  FusedPlan fplan;
 };
 
 struct BatchCtx {
@@ -159,7 +162,11 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
   for (LayerRt& L : e->layers) {
     const ai4e_layer_desc& d = L.d;
     if (d.op == AI4E_OP_CONV) {
-      if (L.igemm) {
+      if (L.fused_second) {
+        rc = AI4E_OK;
+      } else if (L.fused_first) {
+        rc = fused_tail_launch(L.fplan, batch, stream);
+      } else if (L.igemm) {
         rc = igemm_launch(L.plan, batch, 0, stream);
       } else {
         rc = launch_conv_direct(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
@@ -453,12 +460,43 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
     if (rc) return fail(rc);
   }
 
+  // ---- bottleneck tails: a convolution + ReLU whose only consumer is a 1x1 convolution with a
+  // residual runs with it in one kernel (conv_fused.cu); the intermediate buffer is never written.
+  if (!getenv("AI4E_B200_NO_FUSE")) {
+    for (size_t i = 0; i + 1 < e->layers.size(); ++i) {
+      LayerRt& A = e->layers[i];
+      LayerRt& B = e->layers[i + 1];
+      const ai4e_layer_desc& a = A.d;
+      const ai4e_layer_desc& b = B.d;
+      if (a.op != AI4E_OP_CONV || b.op != AI4E_OP_CONV || !A.igemm || A.plan.stem_mode != 0 || A.fused_second) continue;
+      if (a.res_buf >= 0 || !a.relu || b.in_buf != a.out_buf || b.kh != 1 || b.kw != 1 || b.stride != 1 || b.pad != 0 ||
+          b.res_buf < 0 || !b.relu || b.res_buf == a.out_buf || b.out_buf == a.out_buf || b.out_buf == a.in_buf)
+        continue;
+      if (!fused_tail_supported(a.cin, a.cout, b.cout, a.kh, a.kw, a.stride, a.pad)) continue;
+      bool sole_consumer = true;  // nobody else reads the intermediate before it is overwritten
+      for (size_t k = i + 2; k < e->layers.size() && sole_consumer; ++k) {
+        const ai4e_layer_desc& c = e->layers[k].d;
+        if (c.in_buf == a.out_buf || c.res_buf == a.out_buf) sole_consumer = false;
+        if (c.out_buf == a.out_buf) break;
+      }
+      if (!sole_consumer) continue;
+      int rc = fused_tail_make_plan(&A.fplan, e->bufs[a.in_buf], max_batch, A.in_h, A.in_w, a.cin, e->d_blob + a.w_off,
+                                    (const float*)(e->d_blob + a.b_off), a.cout, a.kh, a.kw, a.stride, a.pad,
+                                    e->d_blob + b.w_off, (const float*)(e->d_blob + b.b_off), b.cout, e->bufs[b.res_buf],
+                                    e->bufs[b.out_buf]);
+      if (rc) return fail(rc);
+      A.fused_first = true;
+      B.fused_second = true;
+      e->launches -= 1;
+    }
+  }
+
   // ---- per-layer tiling: time the candidates once, at the full micro-batch (smaller batches fall
   // back to the cost model).  ~50 ms for ResNet-50.  AI4E_B200_NO_AUTOTUNE=1 skips it.
   if (!getenv("AI4E_B200_NO_AUTOTUNE")) {
     const bool log = getenv("AI4E_B200_TUNE_LOG") != nullptr;
     for (LayerRt& L : e->layers) {
-      if (L.d.op != AI4E_OP_CONV || !L.igemm) continue;
+      if (L.d.op != AI4E_OP_CONV || !L.igemm || L.fused_first || L.fused_second) continue;
       float us = 0.f;
       int rc = igemm_autotune(&L.plan, max_batch, nullptr, &us);
       if (rc) return fail(rc);

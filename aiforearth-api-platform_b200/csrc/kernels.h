@@ -49,6 +49,31 @@ struct IgemmPlan {
   int tuned_batch;
 };
 
+// K4b bottleneck tail (conv RxS + relu, then conv 1x1 + residual + relu, one kernel): conv_fused.cu
+struct FusedParams {
+  int M, P, Q, PQ;
+  int Cmid, Cout;
+  int S, stride, pad;
+  int cin_blocks, num_k_blocks;
+  int num_tiles;
+  const float* bias2;
+  const float* bias3;
+};
+struct FusedPlan {
+  CUtensorMap tmap_a;    // im2col-mode map over the input activations
+  CUtensorMap tmap_w2;   // first convolution's weights, [Cmid][R*S*Cin], box 64 x Cmid
+  CUtensorMap tmap_w3;   // second (1x1) convolution's weights, [Cout][Cmid], box 64 x 128
+  CUtensorMap tmap_out;  // z, 32 rows x 64 channels per store
+  CUtensorMap tmap_res;  // residual, 128 rows x 64 channels per load
+  FusedParams prm;
+  int max_batch;
+};
+int fused_tail_supported(int Cin, int Cmid, int Cout, int R, int S, int stride, int pad);
+int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, int Cin, const void* w2,
+                         const float* bias2, int Cmid, int R, int S, int stride, int pad, const void* w3,
+                         const float* bias3, int Cout, const void* residual, void* out);
+int fused_tail_launch(const FusedPlan& plan, int batch, cudaStream_t stream);
+
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
 constexpr int kTilingPair = 1000;  // tiling code = BLOCK_N (+ kTilingPair: CTA-pair kernel, tcgen05 cta_group::2)
 int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res);

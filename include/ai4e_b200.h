@@ -98,6 +98,19 @@ AI4E_API int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int
                     int stride, int pad, const void* d_residual_or_null, int relu,
                     void* d_out_nhwc, int algo, void* stream);
 
+/* K4b.  The tail of a ResNet bottleneck block in one kernel:
+ *   y = relu(conv_khxkw(x; w2) + bias2)       [batch][p][q][cmid]   (conv2 + bn2 + relu, BN folded)
+ *   z = relu(y * w3^T + bias3 + residual)     [batch][p][q][cout]   (conv3 1x1 + bn3 + add + relu)
+ * y is rounded to bf16 exactly as if the two layers ran separately through ai4e_conv_layer, but
+ * never leaves the SM.  cin % 64 == 0, cmid is 64 or 128, cout % 128 == 0; d_w2 is [cmid][kh][kw][cin],
+ * d_w3 is [cout][cmid], residual and z are [batch][p][q][cout] bf16.  Stands in for the same
+ * torchvision modules as ai4e_conv_layer (Bottleneck.conv2..relu, torchvision resnet.py), i.e. the
+ * model the callback at APIs/1.0/base-py/ai4e_service.py:203 runs. */
+AI4E_API int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w, int cin, const void* d_w2_krsc,
+                         const float* d_bias2, int cmid, int kh, int kw, int stride, int pad,
+                         const void* d_w3_kc, const float* d_bias3, int cout, const void* d_residual,
+                         void* d_out_nhwc, void* stream);
+
 /* K3.  Max pooling (padding = -inf).  Stands in for torchvision's `maxpool`. */
 AI4E_API int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
                  void* d_out_nhwc, void* stream);

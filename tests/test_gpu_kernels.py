@@ -251,6 +251,50 @@ def test_conv_igemm_cta_pair_vs_oracle(tiling, case, monkeypatch):
     _check_conv(out, want)
 
 
+# K4b: conv (3x3) + relu + conv 1x1 + residual + relu in one kernel.  (b, h, w, cin, cmid, k, stride, pad, cout)
+TAIL_CASES = [
+    (2, 56, 56, 64, 64, 3, 1, 1, 256),      # ResNet-50 layer1 conv2+conv3, 49 tiles
+    (2, 28, 28, 128, 128, 3, 1, 1, 512),    # layer2
+    (2, 56, 56, 128, 128, 3, 2, 1, 512),    # layer2.0 (stride 2)
+    (1, 7, 9, 64, 64, 3, 1, 1, 128),        # one ragged tile, a single 128-channel pass
+    (3, 13, 17, 192, 128, 3, 2, 1, 384),    # ragged geometry, three passes
+    (2, 14, 14, 64, 64, 1, 1, 0, 256),      # 1x1 first convolution: one K block per tile
+    (16, 56, 56, 64, 64, 3, 1, 1, 256),     # 392 tiles: every CTA loops, all barrier phases wrap
+    (24, 28, 28, 128, 128, 3, 1, 1, 512),   # 147 tiles of the Cmid = 128 variant
+]
+
+
+@pytest.mark.parametrize("case", TAIL_CASES, ids=lambda c: "x".join(str(v) for v in c))
+def test_bottleneck_tail_vs_oracle_and_unfused(case):
+    """the fused kernel against (a) the fp32 oracle with y rounded to bf16 between the layers and
+    (b) the two layers run separately through ai4e_conv_layer: (b) must match bit for bit."""
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, cin, cmid, k, stride, pad, cout = case
+    g = torch.Generator().manual_seed(sum(case))
+    x = (torch.randn((b, h, w, cin), generator=g) * 0.7).to(torch.bfloat16)
+    w2 = (torch.randn((cmid, k, k, cin), generator=g) * (2.0 / (k * k * cin)) ** 0.5).to(torch.bfloat16)
+    b2 = torch.randn((cmid,), generator=g) * 0.1
+    w3 = (torch.randn((cout, cmid), generator=g) * (2.0 / cmid) ** 0.5).to(torch.bfloat16)
+    b3 = torch.randn((cout,), generator=g) * 0.1
+    p, q = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    res = (torch.randn((b, p, q, cout), generator=g) * 0.5).to(torch.bfloat16)
+    y = torch.relu(torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w2.float().permute(0, 3, 1, 2), b2, stride, pad))
+    y = y.to(torch.bfloat16).float()  # the intermediate activation is bf16 in both implementations
+    want = torch.relu(torch.nn.functional.conv2d(y, w3.float()[:, :, None, None], b3).permute(0, 2, 3, 1) + res.float())
+    xd, w2d, b2d, w3d, b3d, resd = (t.cuda() for t in (x, w2, b2, w3, b3, res))
+    out = ops.bottleneck_tail(xd, w2d, b2d, stride, pad, w3d, b3d, resd)
+    torch.cuda.synchronize()
+    y_dev = ops.conv_layer(xd, w2d, b2d, stride, pad, None, True, algo=L.CONV_IGEMM)
+    z_dev = ops.conv_layer(y_dev, w3d.reshape(cout, 1, 1, cmid).contiguous(), b3d, 1, 0, resd, True, algo=L.CONV_IGEMM)
+    torch.cuda.synchronize()
+    assert torch.equal(out, z_dev), f"{int((out != z_dev).sum())} elements differ from the unfused path"
+    # a bf16 flip of y (rounding of a slightly different fp32 sum) moves z by |w3| * ulp(y): looser than _check_conv
+    got = out.float().cpu()
+    tol = 2.0 ** -6 * want.abs() + 2e-2
+    bad = (got - want.contiguous()).abs() > tol
+    assert not bad.any(), f"{int(bad.sum())} of {bad.numel()} outside tolerance; max err {(got - want).abs().max():.4f}"
+
+
 def test_conv_igemm_rejects_unsupported():
     from ai4e_b200 import ops, _lib as L, Ai4eError
     x = torch.zeros((1, 8, 8, 48), dtype=torch.bfloat16, device="cuda")
