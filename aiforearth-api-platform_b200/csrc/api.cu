@@ -88,9 +88,11 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
     cudaFree(d);
     if (FILE* f = fopen(trace, "w")) {  // columns: slot free, A issued (producer) | data seen, MMAs issued (MMA warp)
       for (int i = 0; i < 192; ++i) fprintf(f, "%d %lld %lld %lld %lld\n", i, h[i], h[192 + i], h[384 + i], h[576 + i]);
-      for (int i = 0; i < 40; ++i)  // epilogue leader, per 64-channel chunk
-        fprintf(f, "E %d %lld %lld %lld %lld %lld %lld\n", i, h[768 + 6 * i], h[769 + 6 * i], h[770 + 6 * i], h[771 + 6 * i],
-                h[772 + 6 * i], h[773 + 6 * i]);
+      for (int i = 0; i < 30; ++i) {  // epilogue warp 0, per 64-channel chunk: 8 stamps
+        fprintf(f, "E %d", i);
+        for (int j = 0; j < 8; ++j) fprintf(f, " %lld", h[768 + 8 * i + j]);
+        fprintf(f, "\n");
+      }
       // phases of CTA 0: entry, set-up done, previous kernel finished, MMAs issued, epilogue done, all warps done
       fprintf(f, "T %lld %lld %lld %lld %lld %lld\n", h[1008], h[1009], h[1010], h[1011], h[1012], h[1013]);
       fclose(f);

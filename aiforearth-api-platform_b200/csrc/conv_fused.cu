@@ -58,37 +58,6 @@ struct FusedCfg {
   static constexpr int kE1Warps = 4 * (kKB2 < 2 ? kKB2 : 2);  // epilogue warps that take part in step 2
 };
 
-// acc (+ bias) (+ residual) (relu) -> eight 16-byte units of packed bf16 for one 64-channel row
-template <bool kRes>
-__device__ __forceinline__ void epi_row(const uint32_t (&v)[64], const float4* b4, const uint8_t* res_row, uint32_t sw,
-                                        uint4 (&o)[8]) {
-  float4 ba = b4[0], bb = b4[1];
-  uint4 r = make_uint4(0, 0, 0, 0);
-  if (kRes) r = *reinterpret_cast<const uint4*>(res_row + (sw << 4));
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    float4 nba = ba, nbb = bb;
-    uint4 nr = r;
-    if (j < 7) {  // operands of unit j + 1 are fetched before the arithmetic of unit j
-      nba = b4[2 * j + 2];
-      nbb = b4[2 * j + 3];
-      if (kRes) nr = *reinterpret_cast<const uint4*>(res_row + ((((uint32_t)(j + 1)) ^ sw) << 4));
-    }
-    float x[8];
-    x[0] = __uint_as_float(v[8 * j + 0]) + ba.x; x[1] = __uint_as_float(v[8 * j + 1]) + ba.y;
-    x[2] = __uint_as_float(v[8 * j + 2]) + ba.z; x[3] = __uint_as_float(v[8 * j + 3]) + ba.w;
-    x[4] = __uint_as_float(v[8 * j + 4]) + bb.x; x[5] = __uint_as_float(v[8 * j + 5]) + bb.y;
-    x[6] = __uint_as_float(v[8 * j + 6]) + bb.z; x[7] = __uint_as_float(v[8 * j + 7]) + bb.w;
-    if (kRes) {
-      x[0] += bf16_lo(r.x); x[1] += bf16_hi(r.x); x[2] += bf16_lo(r.y); x[3] += bf16_hi(r.y);
-      x[4] += bf16_lo(r.z); x[5] += bf16_hi(r.z); x[6] += bf16_lo(r.w); x[7] += bf16_hi(r.w);
-    }
-    o[j] = make_uint4(relu_bf16x2(pack_bf16x2(x[0], x[1])), relu_bf16x2(pack_bf16x2(x[2], x[3])),
-                      relu_bf16x2(pack_bf16x2(x[4], x[5])), relu_bf16x2(pack_bf16x2(x[6], x[7])));
-    ba = nba; bb = nbb; r = nr;
-  }
-}
-
 template <int N1>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
 bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w2,
@@ -321,7 +290,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           __syncwarp();
           tmem_wait_ld_pin(vlo);
           tmem_wait_ld_pin(vhi);
-          epi_row<false>(v, b4, nullptr, sw, o);
+          epi_row<false, true>(v, b4, nullptr, sw, o);
           uint8_t* dst = smem_raw + (mid_base - smem_base) + c * kChunkBytes + row_off;
 #pragma unroll
           for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(dst + ((((uint32_t)j) ^ sw) << 4)) = o[j];
@@ -355,7 +324,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(acc2_empty(b));
-        epi_row<true>(v, b4, res_row, sw, o);
+        epi_row<true, true>(v, b4, res_row, sw, o);
         // the store of the previous chunk has read its buffer by now: hand that buffer back
         if (lane == 0 && pending_buf >= 0) {
           bulk_wait_group_read<0>();

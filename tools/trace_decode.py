@@ -18,6 +18,6 @@ for name in sys.argv[1:]:
     prev = None
     for i, r in enumerate(E[:16]):
         if not r[0]: break
-        d = [r[j] - r[0] for j in range(6)]
+        d = [r[j] - r[0] for j in range(len(r))]
         print('  E', i, 'start', r[0] - t0, 'd', d[1:], 'period', (r[0] - prev) if prev else '-')
         prev = r[0]
