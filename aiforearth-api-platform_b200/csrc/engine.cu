@@ -44,6 +44,10 @@ struct LayerRt {
   bool fused_first = false;  // this layer and the next run as one bottleneck_tail_kernel (fplan)
   bool fused_second = false; // computed by the previous layer's launch
   FusedPlan fplan;
+  // side branch (a block's downsample convolution): runs on the engine's second stream next to the
+  // layers that follow it; `wait_ev` makes its first consumer wait for it
+  bool side = false;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, wait_ev = nullptr;
 };
 
 struct BatchCtx {
@@ -80,6 +84,7 @@ struct ai4e_engine {
   std::mutex launch_mu;
   cudaEvent_t ev_chain = nullptr;
   bool chain_valid = false;
+  cudaStream_t side_stream = nullptr;
 
   // synchronous path
   std::mutex sync_mu;
@@ -161,6 +166,16 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   for (LayerRt& L : e->layers) {
     const ai4e_layer_desc& d = L.d;
+    const bool branch = !marks && e->side_stream;  // per-layer timing runs everything in order on one stream
+    if (branch && L.wait_ev) AI4E_CUDA_TRY(cudaStreamWaitEvent(stream, L.wait_ev, 0));
+    if (branch && L.side) {
+      AI4E_CUDA_TRY(cudaEventRecord(L.ev_fork, stream));
+      AI4E_CUDA_TRY(cudaStreamWaitEvent(e->side_stream, L.ev_fork, 0));
+      rc = igemm_launch(L.plan, batch, 0, e->side_stream);
+      if (rc) return rc;
+      AI4E_CUDA_TRY(cudaEventRecord(L.ev_join, e->side_stream));
+      continue;
+    }
     if (d.op == AI4E_OP_CONV) {
       if (L.fused_second) {
         rc = AI4E_OK;
@@ -491,6 +506,36 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
     }
   }
 
+  // ---- side branches: a convolution whose output the next layer does not read, while that next
+  // layer reads the same input (a block's downsample path), goes to a second stream and overlaps
+  // the layers up to its first consumer.  Those layers rarely fill all SMs at micro-batch 64.
+  if (!getenv("AI4E_B200_NO_SIDE_STREAM")) {
+    const int n = (int)e->layers.size();
+    for (int i = 0; i + 1 < n; ++i) {
+      LayerRt& A = e->layers[i];
+      const ai4e_layer_desc& a = A.d;
+      const ai4e_layer_desc& b = e->layers[i + 1].d;
+      if (a.op != AI4E_OP_CONV || !A.igemm || A.plan.stem_mode != 0 || A.fused_first || A.fused_second) continue;
+      if (b.in_buf != a.in_buf || b.in_buf == a.out_buf || b.res_buf == a.out_buf || b.out_buf == a.out_buf) continue;
+      int consumer = -1;
+      bool ok = true;
+      for (int k = i + 1; k < n && ok; ++k) {
+        const ai4e_layer_desc& c = e->layers[k].d;
+        if (c.in_buf == a.out_buf || c.res_buf == a.out_buf) { consumer = k; break; }
+        if (c.out_buf == a.in_buf || c.out_buf == a.out_buf) ok = false;  // someone overwrites a buffer the branch uses
+        if (a.res_buf >= 0 && c.out_buf == a.res_buf) ok = false;
+      }
+      if (!ok || consumer < 0) continue;
+      if (e->layers[consumer].fused_second) --consumer;  // that layer runs inside the previous launch
+      if (consumer <= i) continue;
+      if (!e->side_stream) TRY_OR_FAIL(cudaStreamCreateWithFlags(&e->side_stream, cudaStreamNonBlocking));
+      TRY_OR_FAIL(cudaEventCreateWithFlags(&A.ev_fork, cudaEventDisableTiming));
+      TRY_OR_FAIL(cudaEventCreateWithFlags(&A.ev_join, cudaEventDisableTiming));
+      A.side = true;
+      e->layers[consumer].wait_ev = A.ev_join;
+    }
+  }
+
   // ---- per-layer tiling: time the candidates once, at the full micro-batch (smaller batches fall
   // back to the cost model).  ~50 ms for ResNet-50.  AI4E_B200_NO_AUTOTUNE=1 skips it.
   if (!getenv("AI4E_B200_NO_AUTOTUNE")) {
@@ -572,6 +617,11 @@ int ai4e_engine_destroy(ai4e_engine* e) {
   if (e->d_blob) cudaFree(e->d_blob);
   if (e->d_stem_w) cudaFree(e->d_stem_w);
   if (e->ev_chain) cudaEventDestroy(e->ev_chain);
+  for (LayerRt& L : e->layers) {
+    if (L.ev_fork) cudaEventDestroy(L.ev_fork);
+    if (L.ev_join) cudaEventDestroy(L.ev_join);
+  }
+  if (e->side_stream) cudaStreamDestroy(e->side_stream);
   delete e;
   return AI4E_OK;
 }
