@@ -10,26 +10,39 @@
 // inside the callback the reference invokes at APIs/1.0/base-py/ai4e_service.py:203;
 // oracle: torch.nn.functional.conv2d in oracle/resnet_oracle.py (_conv_bf16).
 //
-// Structure (one persistent CTA per SM, 320 threads, warp-specialised):
-//   warp 0   TMA producer.  A tiles come straight from the NHWC activation tensor through an
+// Structure (one persistent CTA per SM, 384 threads, warp-specialised; tiles are dealt round-robin):
+//   warp 0   A producer.  A tiles come straight from the NHWC activation tensor through an
 //            IM2COL-mode tensor map: one `cp.async.bulk.tensor.4d...im2col` per K block
 //            fetches 128 consecutive output pixels x 64 channels for filter tap (r, s), with
 //            stride, padding (zero fill) and the wrap across rows / images done by the TMA
-//            unit.  B tiles are plain 2-D tiles of the weight matrix.  Both land in
-//            128-byte-swizzled shared memory, STAGES deep, mbarrier `full`/`empty` rings.
-//   warp 1   allocates TMEM and issues `tcgen05.mma.cta_group::1.kind::f16` (M = 128,
-//            N = BLOCK_N, K = 16) from one elected lane; `tcgen05.commit` releases smem
-//            stages and signals the epilogue.  Two accumulator stages in TMEM
-//            (2 x BLOCK_N fp32 columns) let the epilogue of tile i overlap the MMAs of
-//            tile i+1.
-//   warps 2-9  epilogue, 64 output channels at a time: `tcgen05.ld` (each thread owns one pixel
-//            row), + bias, + residual, ReLU, pack to bf16 into a 128-byte-swizzled staging
-//            tile in shared memory, which one thread hands to the TMA unit
-//            (`cp.async.bulk.tensor.2d.global.shared::cta`): stores to HBM are full 128-byte
-//            lines, asynchronous, and rows past the tensor end are clipped by hardware.  The
-//            residual tile arrives the same way (TMA load, two chunks ahead).  Staging and
-//            residual tiles are double-buffered.  A warp may only touch the TMEM lane quadrant
-//            `warp_id % 4`; warps w and w+4 split the 64 channels of a chunk between them.
+//            unit.  128-byte-swizzled shared memory, as many stages as fit (3-8), mbarrier
+//            `full`/`empty` rings.  Waits for the previous layer (griddepcontrol.wait) first.
+//   warp 10  B producer: 2-D tiles of the weight matrix into the same stages.  Weights are
+//            constants, so it does NOT wait for the previous layer: the first stages of B fill
+//            while that kernel drains (programmatic dependent launch).
+//   warp 1   allocates TMEM and issues `tcgen05.mma.kind::f16` (M = 128, N = BLOCK_N, K = 16)
+//            from one elected lane of the convergent warp; `tcgen05.commit` releases smem stages
+//            and signals the epilogue.  Two accumulator stages in TMEM (2 x BLOCK_N fp32
+//            columns) let the epilogue of tile i overlap the MMAs of tile i+1.
+//   warps 2-9  epilogue: eight INDEPENDENT warps, no block-level barriers.  A warp reads only its
+//            TMEM lane quadrant (warp % 4); the 64-channel chunks of the CTA's tiles alternate
+//            between the two warps of a quadrant.  Per chunk: `tcgen05.ld` (thread = pixel row),
+//            + bias (staged in 256 warp-private bytes of shared memory), + residual, ReLU, pack to
+//            bf16 into the warp's own 4 KB swizzled staging slice, `cp.async.bulk.tensor` store of
+//            32 rows x 64 channels.  HBM sees full 128-byte lines, rows past the tensor end are
+//            clipped by hardware.  Arithmetic is compiled per (residual, ReLU) combination.
+//   warp 11  residual loader: 128-row x 64-channel residual chunks by TMA, two buffers per epilogue
+//            side released through `res_empty` barriers, and an L2 prefetch four chunks ahead.
+//
+// CTA-pair mode (kPair): the two CTAs of a 2-CTA cluster share one 256 x BLOCK_N tile through
+// `tcgen05.mma.cta_group::2`: each loads its own 128 rows of A and HALF of the weight tile, the
+// leader CTA issues the MMAs for both and commits (multicast) to the barriers of both; the TMA
+// loads of both CTAs signal the leader's `full` barrier.  Fewer operand bytes per MMA is what
+// matters: L2 -> shared-memory ingest is the K loop's bound (tools/l2_probe.cu).
+//
+// The tiling (BLOCK_N 64 / 128 / 256, single CTA or pair) comes from a cost model
+// (igemm_pick_tiling) or, in the engine, from timing the candidates once per layer
+// (igemm_autotune).  The stem (7x7, 3-4 input channels) has two modes of its own, below.
 #include "common.cuh"
 #include "kernels.h"
 #include "igemm_tiles.cuh"
