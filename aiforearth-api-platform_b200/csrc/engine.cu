@@ -68,23 +68,35 @@ struct BatchCtx {
 
 }  // namespace
 
-struct ai4e_engine {
-  int device = 0, max_batch = 0, max_wait_us = 0;
-  ai4e_model_desc desc{};
+// A lane = one set of activation slots with the tensor maps that point into them.  Forwards that
+// use different lanes run concurrently (each on its caller's / batch context's stream): at
+// micro-batch 64 many layers leave SMs idle (25-98 M tiles, launch fill and epilogue tails), and a
+// second micro-batch in flight fills them.  Forwards on the same lane are chained by an event.
+struct Lane {
   std::vector<LayerRt> layers;
   std::vector<void*> bufs;
-  std::vector<size_t> buf_elems_per_image;
-  uint8_t* d_blob = nullptr;
-  uint16_t* d_stem_w = nullptr;  // stem weights repacked for the tensor-core stem
   float* d_pooled = nullptr;
-  size_t slot_bytes = 0;  // staging bytes per image
-  int launches = 0;
-
-  // forwards share activation slots: chain them
-  std::mutex launch_mu;
+  float* d_logits = nullptr;  // where the logits go when the caller of forward_device passes no buffer
   cudaEvent_t ev_chain = nullptr;
   bool chain_valid = false;
   cudaStream_t side_stream = nullptr;
+};
+
+struct ai4e_engine {
+  int device = 0, max_batch = 0, max_wait_us = 0;
+  ai4e_model_desc desc{};
+  std::vector<LayerRt> layers;  // validated program (shapes, igemm flag); each lane has its own copy with plans
+  std::vector<Lane> lanes;
+  std::vector<size_t> buf_elems_per_image;
+  uint8_t* d_blob = nullptr;
+  uint16_t* d_stem_w = nullptr;  // stem weights repacked for the tensor-core stem
+  size_t slot_bytes = 0;  // staging bytes per image
+  int launches = 0;
+
+  // lanes are handed out round-robin under launch_mu
+  std::mutex launch_mu;
+  unsigned next_lane = 0;
+  int last_lane = 0;  // lane of the most recent forward (ai4e_engine_read_activation reads it)
 
   // synchronous path
   std::mutex sync_mu;
@@ -152,10 +164,10 @@ void free_ctx(BatchCtx& c) {
 }
 
 // preprocess + every layer, enqueued on `stream`.  Caller holds e->launch_mu.
-int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
+int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batch, int src_h, int src_w,
                     int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream,
                     cudaEvent_t* marks = nullptr) {
-  const ai4e_model_desc& m = e->desc;
+  const ai4e_model_desc& m = eng->desc;
   int mark = 0;
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   const bool resize = src_h != m.in_h || src_w != m.in_w;
@@ -184,8 +196,8 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
       } else if (L.igemm) {
         rc = igemm_launch(L.plan, batch, 0, stream);
       } else {
-        rc = launch_conv_direct(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
-                                (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
+        rc = launch_conv_direct(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, eng->d_blob + d.w_off,
+                                (const float*)(eng->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
                                 d.res_buf >= 0 ? e->bufs[d.res_buf] : nullptr, d.relu, e->bufs[d.out_buf],
                                 stream);
       }
@@ -193,13 +205,29 @@ int forward_enqueue(ai4e_engine* e, const uint8_t* d_images, int batch, int src_
       rc = launch_maxpool(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, d.kh, d.stride, d.pad,
                           e->bufs[d.out_buf], stream);
     } else {
-      rc = launch_head(e->bufs[d.in_buf], batch, L.in_h * L.in_w, d.cin, e->d_blob + d.w_off,
-                       (const float*)(e->d_blob + d.b_off), d.cout, e->d_pooled, d_logits, d_idx, d_prob,
+      rc = launch_head(e->bufs[d.in_buf], batch, L.in_h * L.in_w, d.cin, eng->d_blob + d.w_off,
+                       (const float*)(eng->d_blob + d.b_off), d.cout, e->d_pooled, d_logits, d_idx, d_prob,
                        AI4E_TOPK, stream);
     }
     if (rc) return rc;
     if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   }
+  return AI4E_OK;
+}
+
+// Next lane (round-robin) with `stream` made to wait for that lane's previous forward.  Caller
+// holds e->launch_mu and calls lane_done() after enqueueing.
+int lane_begin(ai4e_engine* e, cudaStream_t stream, Lane** out, int force_lane = -1) {
+  const int li = force_lane >= 0 ? force_lane : (int)(e->next_lane++ % e->lanes.size());
+  Lane& ln = e->lanes[li];
+  if (ln.chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(stream, ln.ev_chain, 0));
+  e->last_lane = li;
+  *out = &ln;
+  return AI4E_OK;
+}
+int lane_done(Lane* ln, cudaStream_t stream) {
+  AI4E_CUDA_TRY(cudaEventRecord(ln->ev_chain, stream));
+  ln->chain_valid = true;
   return AI4E_OK;
 }
 
@@ -211,13 +239,15 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
   AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
   {
     std::lock_guard<std::mutex> lk(e->launch_mu);
-    if (e->chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(c.stream, e->ev_chain, 0));
+    Lane* ln = nullptr;
+    int rc = lane_begin(e, c.stream, &ln);
+    if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_start, c.stream));
-    int rc = forward_enqueue(e, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream);
+    rc = forward_enqueue(e, ln, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream);
     if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_fwd, c.stream));
-    AI4E_CUDA_TRY(cudaEventRecord(e->ev_chain, c.stream));
-    e->chain_valid = true;
+    rc = lane_done(ln, c.stream);
+    if (rc) return rc;
   }
   AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, (size_t)c.count * AI4E_TOPK * sizeof(int32_t),
                                 cudaMemcpyDeviceToHost, c.stream));
@@ -439,22 +469,29 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   } while (0)
   TRY_OR_FAIL(cudaMalloc((void**)&e->d_blob, blob_bytes));
   TRY_OR_FAIL(cudaMemcpy(e->d_blob, blob, blob_bytes, cudaMemcpyHostToDevice));
-  e->bufs.assign(desc->n_bufs, nullptr);
+  int n_lanes = 2;
+  if (const char* v = getenv("AI4E_B200_LANES")) n_lanes = std::max(1, std::min(4, atoi(v)));
+  e->lanes.resize(n_lanes);
+  for (int li = 0; li < n_lanes; ++li) {
+  Lane& ln = e->lanes[li];
+  ln.layers = e->layers;
+  ln.bufs.assign(desc->n_bufs, nullptr);
   for (int b = 0; b < desc->n_bufs; ++b) {
     if (!e->buf_elems_per_image[b]) continue;
     const size_t bytes = e->buf_elems_per_image[b] * 2 * (size_t)max_batch;
-    TRY_OR_FAIL(cudaMalloc(&e->bufs[b], bytes));
-    TRY_OR_FAIL(cudaMemset(e->bufs[b], 0, bytes));
+    TRY_OR_FAIL(cudaMalloc(&ln.bufs[b], bytes));
+    TRY_OR_FAIL(cudaMemset(ln.bufs[b], 0, bytes));
   }
-  int head_c = e->layers.back().d.cin;
-  TRY_OR_FAIL(cudaMalloc((void**)&e->d_pooled, (size_t)max_batch * head_c * sizeof(float)));
-  TRY_OR_FAIL(cudaEventCreateWithFlags(&e->ev_chain, cudaEventDisableTiming));
+  int head_c = ln.layers.back().d.cin;
+  TRY_OR_FAIL(cudaMalloc((void**)&ln.d_pooled, (size_t)max_batch * head_c * sizeof(float)));
+  TRY_OR_FAIL(cudaMalloc((void**)&ln.d_logits, (size_t)max_batch * desc->num_classes * sizeof(float)));
+  TRY_OR_FAIL(cudaEventCreateWithFlags(&ln.ev_chain, cudaEventDisableTiming));
 
   // ---- tensor maps for the tcgen05 layers (batch-independent, see igemm_make_plan)
-  e->launches = 1;  // preprocess
-  for (LayerRt& L : e->layers) {
+  if (li == 0) e->launches = 1;  // preprocess
+  for (LayerRt& L : ln.layers) {
     const ai4e_layer_desc& d = L.d;
-    e->launches += d.op == AI4E_OP_HEAD ? 3 : 1;
+    if (li == 0) e->launches += d.op == AI4E_OP_HEAD ? 3 : 1;
     if (d.op != AI4E_OP_CONV) continue;
     if (!L.igemm && d.res_buf < 0 && stem_supported(L.in_h, L.in_w, d.cin, d.cout, d.kh, d.kw, d.stride, d.pad) &&
         !getenv("AI4E_B200_DIRECT_STEM")) {
@@ -462,25 +499,25 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
       stem_repack_weights(reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(blob) + d.w_off), w_sp.data());
       if (!e->d_stem_w) TRY_OR_FAIL(cudaMalloc((void**)&e->d_stem_w, w_sp.size() * 2));
       TRY_OR_FAIL(cudaMemcpy(e->d_stem_w, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice));
-      int rc = igemm_make_plan_stem(&L.plan, e->bufs[d.in_buf], max_batch, L.in_h, L.in_w, e->d_stem_w,
-                                    (const float*)(e->d_blob + d.b_off), d.relu, e->bufs[d.out_buf]);
+      int rc = igemm_make_plan_stem(&L.plan, ln.bufs[d.in_buf], max_batch, L.in_h, L.in_w, e->d_stem_w,
+                                    (const float*)(e->d_blob + d.b_off), d.relu, ln.bufs[d.out_buf]);
       if (rc) return fail(rc);
       L.igemm = true;
       continue;
     }
     if (!L.igemm) continue;
-    int rc = igemm_make_plan(&L.plan, e->bufs[d.in_buf], max_batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
+    int rc = igemm_make_plan(&L.plan, ln.bufs[d.in_buf], max_batch, L.in_h, L.in_w, d.cin, e->d_blob + d.w_off,
                              (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
-                             d.res_buf >= 0 ? e->bufs[d.res_buf] : nullptr, d.relu, e->bufs[d.out_buf]);
+                             d.res_buf >= 0 ? ln.bufs[d.res_buf] : nullptr, d.relu, ln.bufs[d.out_buf]);
     if (rc) return fail(rc);
   }
 
   // ---- bottleneck tails: a convolution + ReLU whose only consumer is a 1x1 convolution with a
   // residual runs with it in one kernel (conv_fused.cu); the intermediate buffer is never written.
   if (!getenv("AI4E_B200_NO_FUSE")) {
-    for (size_t i = 0; i + 1 < e->layers.size(); ++i) {
-      LayerRt& A = e->layers[i];
-      LayerRt& B = e->layers[i + 1];
+    for (size_t i = 0; i + 1 < ln.layers.size(); ++i) {
+      LayerRt& A = ln.layers[i];
+      LayerRt& B = ln.layers[i + 1];
       const ai4e_layer_desc& a = A.d;
       const ai4e_layer_desc& b = B.d;
       if (a.op != AI4E_OP_CONV || b.op != AI4E_OP_CONV || !A.igemm || A.plan.stem_mode != 0 || A.fused_second) continue;
@@ -489,20 +526,20 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
         continue;
       if (!fused_tail_supported(a.cin, a.cout, b.cout, a.kh, a.kw, a.stride, a.pad)) continue;
       bool sole_consumer = true;  // nobody else reads the intermediate before it is overwritten
-      for (size_t k = i + 2; k < e->layers.size() && sole_consumer; ++k) {
-        const ai4e_layer_desc& c = e->layers[k].d;
+      for (size_t k = i + 2; k < ln.layers.size() && sole_consumer; ++k) {
+        const ai4e_layer_desc& c = ln.layers[k].d;
         if (c.in_buf == a.out_buf || c.res_buf == a.out_buf) sole_consumer = false;
         if (c.out_buf == a.out_buf) break;
       }
       if (!sole_consumer) continue;
-      int rc = fused_tail_make_plan(&A.fplan, e->bufs[a.in_buf], max_batch, A.in_h, A.in_w, a.cin, e->d_blob + a.w_off,
+      int rc = fused_tail_make_plan(&A.fplan, ln.bufs[a.in_buf], max_batch, A.in_h, A.in_w, a.cin, e->d_blob + a.w_off,
                                     (const float*)(e->d_blob + a.b_off), a.cout, a.kh, a.kw, a.stride, a.pad,
-                                    e->d_blob + b.w_off, (const float*)(e->d_blob + b.b_off), b.cout, e->bufs[b.res_buf],
-                                    e->bufs[b.out_buf]);
+                                    e->d_blob + b.w_off, (const float*)(e->d_blob + b.b_off), b.cout, ln.bufs[b.res_buf],
+                                    ln.bufs[b.out_buf]);
       if (rc) return fail(rc);
       A.fused_first = true;
       B.fused_second = true;
-      e->launches -= 1;
+      if (li == 0) e->launches -= 1;
     }
   }
 
@@ -510,37 +547,42 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   // layer reads the same input (a block's downsample path), goes to a second stream and overlaps
   // the layers up to its first consumer.  Those layers rarely fill all SMs at micro-batch 64.
   if (!getenv("AI4E_B200_NO_SIDE_STREAM")) {
-    const int n = (int)e->layers.size();
+    const int n = (int)ln.layers.size();
     for (int i = 0; i + 1 < n; ++i) {
-      LayerRt& A = e->layers[i];
+      LayerRt& A = ln.layers[i];
       const ai4e_layer_desc& a = A.d;
-      const ai4e_layer_desc& b = e->layers[i + 1].d;
+      const ai4e_layer_desc& b = ln.layers[i + 1].d;
       if (a.op != AI4E_OP_CONV || !A.igemm || A.plan.stem_mode != 0 || A.fused_first || A.fused_second) continue;
       if (b.in_buf != a.in_buf || b.in_buf == a.out_buf || b.res_buf == a.out_buf || b.out_buf == a.out_buf) continue;
       int consumer = -1;
       bool ok = true;
       for (int k = i + 1; k < n && ok; ++k) {
-        const ai4e_layer_desc& c = e->layers[k].d;
+        const ai4e_layer_desc& c = ln.layers[k].d;
         if (c.in_buf == a.out_buf || c.res_buf == a.out_buf) { consumer = k; break; }
         if (c.out_buf == a.in_buf || c.out_buf == a.out_buf) ok = false;  // someone overwrites a buffer the branch uses
         if (a.res_buf >= 0 && c.out_buf == a.res_buf) ok = false;
       }
       if (!ok || consumer < 0) continue;
-      if (e->layers[consumer].fused_second) --consumer;  // that layer runs inside the previous launch
+      if (ln.layers[consumer].fused_second) --consumer;  // that layer runs inside the previous launch
       if (consumer <= i) continue;
-      if (!e->side_stream) TRY_OR_FAIL(cudaStreamCreateWithFlags(&e->side_stream, cudaStreamNonBlocking));
+      if (!ln.side_stream) TRY_OR_FAIL(cudaStreamCreateWithFlags(&ln.side_stream, cudaStreamNonBlocking));
       TRY_OR_FAIL(cudaEventCreateWithFlags(&A.ev_fork, cudaEventDisableTiming));
       TRY_OR_FAIL(cudaEventCreateWithFlags(&A.ev_join, cudaEventDisableTiming));
       A.side = true;
-      e->layers[consumer].wait_ev = A.ev_join;
+      ln.layers[consumer].wait_ev = A.ev_join;
     }
   }
 
   // ---- per-layer tiling: time the candidates once, at the full micro-batch (smaller batches fall
   // back to the cost model).  ~50 ms for ResNet-50.  AI4E_B200_NO_AUTOTUNE=1 skips it.
-  if (!getenv("AI4E_B200_NO_AUTOTUNE")) {
+  if (li > 0) {  // same shapes, same tilings as lane 0 measured
+    for (size_t i = 0; i < ln.layers.size(); ++i) {
+      ln.layers[i].plan.tuned_tiling = e->lanes[0].layers[i].plan.tuned_tiling;
+      ln.layers[i].plan.tuned_batch = e->lanes[0].layers[i].plan.tuned_batch;
+    }
+  } else if (!getenv("AI4E_B200_NO_AUTOTUNE")) {
     const bool log = getenv("AI4E_B200_TUNE_LOG") != nullptr;
-    for (LayerRt& L : e->layers) {
+    for (LayerRt& L : ln.layers) {
       if (L.d.op != AI4E_OP_CONV || !L.igemm || L.fused_first || L.fused_second) continue;
       float us = 0.f;
       int rc = igemm_autotune(&L.plan, max_batch, nullptr, &us);
@@ -553,6 +595,8 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
     // the timed launches wrote garbage into the activation buffers; nothing reads them before
     // the next forward overwrites them
   }
+
+  }  // lanes
 
   // ---- staging: images up to 1.5x the model input area (covers a 256 -> 224 resize+crop)
   const size_t in_bytes = (size_t)desc->in_h * desc->in_w * desc->in_c;
@@ -611,17 +655,20 @@ int ai4e_engine_destroy(ai4e_engine* e) {
   cudaDeviceSynchronize();
   free_ctx(e->sync_ctx);
   for (int i = 0; i < kNumCtx; ++i) free_ctx(e->ctx[i]);
-  for (void* b : e->bufs)
-    if (b) cudaFree(b);
-  if (e->d_pooled) cudaFree(e->d_pooled);
+  for (Lane& ln : e->lanes) {
+    for (void* b : ln.bufs)
+      if (b) cudaFree(b);
+    if (ln.d_pooled) cudaFree(ln.d_pooled);
+    if (ln.d_logits) cudaFree(ln.d_logits);
+    if (ln.ev_chain) cudaEventDestroy(ln.ev_chain);
+    for (LayerRt& L : ln.layers) {
+      if (L.ev_fork) cudaEventDestroy(L.ev_fork);
+      if (L.ev_join) cudaEventDestroy(L.ev_join);
+    }
+    if (ln.side_stream) cudaStreamDestroy(ln.side_stream);
+  }
   if (e->d_blob) cudaFree(e->d_blob);
   if (e->d_stem_w) cudaFree(e->d_stem_w);
-  if (e->ev_chain) cudaEventDestroy(e->ev_chain);
-  for (LayerRt& L : e->layers) {
-    if (L.ev_fork) cudaEventDestroy(L.ev_fork);
-    if (L.ev_join) cudaEventDestroy(L.ev_join);
-  }
-  if (e->side_stream) cudaStreamDestroy(e->side_stream);
   delete e;
   return AI4E_OK;
 }
@@ -667,13 +714,14 @@ int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images, int batc
   AI4E_CUDA_TRY(cudaSetDevice(e->device));
   cudaStream_t s = (cudaStream_t)stream;
   std::lock_guard<std::mutex> lk(e->launch_mu);
-  if (e->chain_valid) AI4E_CUDA_TRY(cudaStreamWaitEvent(s, e->ev_chain, 0));
-  int rc = forward_enqueue(e, d_images, batch, src_h, src_w, d_top_idx, d_top_prob,
-                           d_logits_or_null ? d_logits_or_null : e->sync_ctx.d_logits, s);
+  Lane* ln = nullptr;
+  int rc = lane_begin(e, s, &ln);
   if (rc) return rc;
-  AI4E_CUDA_TRY(cudaEventRecord(e->ev_chain, s));
-  e->chain_valid = true;
-  return AI4E_OK;
+  // without a caller buffer the logits go to the lane's own scratch (never read back)
+  rc = forward_enqueue(e, ln, d_images, batch, src_h, src_w, d_top_idx, d_top_prob,
+                       d_logits_or_null ? d_logits_or_null : ln->d_logits, s);
+  if (rc) return rc;
+  return lane_done(ln, s);
 }
 
 int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
@@ -803,10 +851,10 @@ int ai4e_engine_profile(ai4e_engine* e, const uint8_t* d_images, int batch, int 
   for (int r = 0; r < reps && rc == AI4E_OK; ++r) {
     {
       std::lock_guard<std::mutex> lk(e->launch_mu);
-      if (e->chain_valid) cudaStreamWaitEvent(c.stream, e->ev_chain, 0);
-      rc = forward_enqueue(e, d_images, batch, src_h, src_w, c.d_idx, c.d_prob, c.d_logits, c.stream, ev.data());
-      cudaEventRecord(e->ev_chain, c.stream);
-      e->chain_valid = true;
+      Lane* ln = nullptr;
+      rc = lane_begin(e, c.stream, &ln, 0);  // lane 0 holds the autotuned plans' buffers; any lane would do
+      if (rc == AI4E_OK) rc = forward_enqueue(e, ln, d_images, batch, src_h, src_w, c.d_idx, c.d_prob, c.d_logits, c.stream, ev.data());
+      if (rc == AI4E_OK) rc = lane_done(ln, c.stream);
     }
     if (rc) break;
     cudaError_t ce = cudaStreamSynchronize(c.stream);
@@ -874,11 +922,13 @@ int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out) {
 
 int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t bytes) {
   AI4E_REQUIRE(e && h_dst, "read_activation: null pointer");
-  AI4E_REQUIRE(buf >= 0 && buf < (int)e->bufs.size() && e->bufs[buf], "read_activation: no slot %d", buf);
+  std::lock_guard<std::mutex> lk_lane(e->launch_mu);
+  Lane& lane_r = e->lanes[e->last_lane];  // the lane the most recent forward ran on
+  AI4E_REQUIRE(buf >= 0 && buf < (int)lane_r.bufs.size() && lane_r.bufs[buf], "read_activation: no slot %d", buf);
   AI4E_REQUIRE(bytes <= e->buf_elems_per_image[buf] * 2 * (uint64_t)e->max_batch, "read_activation: too many bytes");
   AI4E_CUDA_TRY(cudaSetDevice(e->device));
   AI4E_CUDA_TRY(cudaDeviceSynchronize());
-  AI4E_CUDA_TRY(cudaMemcpy(h_dst, e->bufs[buf], bytes, cudaMemcpyDeviceToHost));
+  AI4E_CUDA_TRY(cudaMemcpy(h_dst, lane_r.bufs[buf], bytes, cudaMemcpyDeviceToHost));
   return AI4E_OK;
 }
 
