@@ -295,7 +295,7 @@ def main():
         json.dump({"batch": B, "preprocess_ms": float(ms[0]), "layers": rows}, open(args.dump_layers, "w"), indent=1)
     traffic = None  # DRAM bytes of the conv launches of one step, from the committed ncu capture
     tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(tpath) and B == 64:
+    if os.path.exists(tpath) and B == 64 and ARCH == "resnet50":
         traffic = json.load(open(tpath)).get("dram_bytes_per_step")
     achieved = conv_flops / (igemm_ms / 1e3) / 1e12
     peak_t = peaks["bf16_tflops_sustained"]
@@ -311,7 +311,8 @@ def main():
                 "d2h_bytes_per_step": B * (5 * 4 + 5 * 4 + prog.num_classes * 4),
                 "api": "Engine.submit_batch/wait, page-locked host batches, 3 batches in flight"},
         "gpu_launches": stats["launches_per_forward"] * K,
-        "roofline": {"bound": "tensor", "kernel": f"conv_igemm_kernel ({igemm_launches} launches per step)", "achieved": achieved,
+        "roofline": {"bound": "tensor", "kernel": f"tcgen05 convolutions: conv_igemm_kernel + bottleneck_tail_kernel ({igemm_launches} layers in "
+                               f"{stats['launches_per_forward'] - 5} launches per step)", "achieved": achieved,
                      "peak": peak_t, "unit": "TFLOP/s", "frac": achieved / peak_t, "traffic": traffic,
                      "peak_source": f"{peaks['source']} bf16 sustained", "ms_per_step_in_kernel": igemm_ms,
                      "flops_per_step": conv_flops,
