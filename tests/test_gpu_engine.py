@@ -237,3 +237,39 @@ def test_async_endpoint_drives_the_engine():
             assert json.loads(st["Status"][len("completed - "):])["top5"] == g["top5_idx"][k].tolist()
         hist = e.stats()["batch_hist"]
         assert sum(hist[1:]) > 0, f"no batch larger than one image was formed: {hist}"
+
+
+def test_two_lanes_concurrent_forward_device():
+    """Two micro-batches in flight on two streams (the engine's lanes) give, bit for bit, what each
+    gives alone: lanes own separate activation slots and are chained by their own events."""
+    import torch
+    g, imgs = util.load_golden("resnet50")
+    n = len(imgs)
+    a = torch.from_numpy(np.ascontiguousarray(imgs)).cuda()
+    b = torch.from_numpy(np.ascontiguousarray(imgs[::-1].copy())).cuda()
+    h, w = imgs.shape[1], imgs.shape[2]
+
+    def outs():
+        return (torch.empty((n, 5), dtype=torch.int32, device="cuda"), torch.empty((n, 5), dtype=torch.float32, device="cuda"),
+                torch.zeros((n, 1000), dtype=torch.float32, device="cuda"))
+
+    with _engine("resnet50", max_batch=n) as e:
+        ref = {}
+        for key, x in (("a", a), ("b", b)):  # one at a time, fully synchronised
+            o = outs()
+            e.forward_device(x, n, h, w, *o)
+            torch.cuda.synchronize()
+            ref[key] = [t.clone() for t in o]
+        _check_against_golden(g, ref["a"][0].cpu().numpy(), ref["a"][1].cpu().numpy(), ref["a"][2].cpu().numpy())
+        s0, s1 = torch.cuda.Stream(), torch.cuda.Stream()
+        runs = []
+        for rep in range(6):  # a on stream 0 and b on stream 1, enqueued back to back, no sync in between
+            oa, ob = outs(), outs()
+            e.forward_device(a, n, h, w, *oa, stream=s0)
+            e.forward_device(b, n, h, w, *ob, stream=s1)
+            runs.append((oa, ob))
+        torch.cuda.synchronize()
+        for oa, ob in runs:
+            for got, want in zip(oa + ob, ref["a"] + ref["b"]):
+                assert torch.equal(got, want)
+        assert e.stats()["healthy"]
