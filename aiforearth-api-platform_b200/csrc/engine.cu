@@ -31,7 +31,7 @@ using Clock = std::chrono::steady_clock;
 
 namespace {
 
-constexpr int kNumCtx = 3;
+constexpr int kNumCtx = 4;
 constexpr uint64_t kResultRing = 1ull << 16;
 constexpr uint64_t kLogitRing = 1ull << 12;
 constexpr int kLatRing = 4096;

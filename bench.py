@@ -238,6 +238,7 @@ def main():
 
     # ------------------------------------------------------------------ end to end, host buffers
     host_np = host.numpy()
+    E2E_INFLIGHT = int(os.environ.get("AI4E_BENCH_E2E_INFLIGHT", "3"))
     in_flight = []
 
     def drain(n_keep):
@@ -252,7 +253,7 @@ def main():
     t0 = time.perf_counter()
     for i in range(K):
         in_flight.append(eng.submit_batch(host_np[i % POOL_BATCHES]))
-        drain(2)
+        drain(E2E_INFLIGHT - 1)
     drain(0)
     torch.cuda.synchronize()
     dt_e2e = max_over_ranks(time.perf_counter() - t0)
@@ -309,7 +310,7 @@ def main():
         "config": workload_config(B, world),
         "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": B * HW * HW * IN_C,
                 "d2h_bytes_per_step": B * (5 * 4 + 5 * 4 + prog.num_classes * 4),
-                "api": "Engine.submit_batch/wait, page-locked host batches, 3 batches in flight"},
+                "api": f"Engine.submit_batch/wait, page-locked host batches, {E2E_INFLIGHT} batches in flight"},
         "gpu_launches": stats["launches_per_forward"] * K,
         "roofline": {"bound": "tensor", "kernel": f"tcgen05 convolutions: conv_igemm_kernel + bottleneck_tail_kernel ({igemm_launches} layers in "
                                f"{stats['launches_per_forward'] - 5} launches per step)", "achieved": achieved,
