@@ -408,6 +408,7 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0;
   q.bias2 = bias2; q.bias3 = bias3;
   plan->max_batch = N;
+  plan->grid_sms = 0;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint32_t es[2] = {1, 1};
@@ -461,7 +462,7 @@ int fused_tail_launch(const FusedPlan& plan, int batch, cudaStream_t stream) {
   const long long M = (long long)batch * prm.PQ;
   prm.M = (int)M;
   prm.num_tiles = (int)((M + kBlockM - 1) / kBlockM);
-  const int grid = std::min(prm.num_tiles, sm_count());
+  const int grid = std::min(prm.num_tiles, plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count());
   if (prm.Cmid == 64) return fused_launch_n1<64>(plan, prm, grid, stream);
   return fused_launch_n1<128>(plan, prm, grid, stream);
 }

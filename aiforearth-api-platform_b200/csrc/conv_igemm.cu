@@ -600,8 +600,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
 //  * epilogue: ~1050 cycles per 64-channel chunk (1250 with a residual), overlapped with the next
 //    tile's K loop, so a tile costs the longer of the two.
 //  * tiles are dealt round-robin to min(tiles, SMs) CTAs (or CTA pairs).
-static double igemm_model_cycles(int Cout, long long M, int num_k_blocks, bool has_res, int bn, bool pair) {
-  const int sms = sm_count();
+static double igemm_model_cycles(int Cout, long long M, int num_k_blocks, bool has_res, int bn, bool pair, int sms) {
   const int ctas = pair ? 2 : 1;
   const long long tiles = ((M + kBlockM * ctas - 1) / (kBlockM * ctas)) * (Cout / bn);
   const long long units = std::min<long long>(tiles, sms / ctas);
@@ -628,7 +627,8 @@ int igemm_tiling_candidates(int Cout, int out[8]) {
   return n;
 }
 
-int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res) {
+int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res, int sms) {
+  if (sms <= 0) sms = sm_count();
   int cand[8];
   const int n = igemm_tiling_candidates(Cout, cand);
   int best = 0;
@@ -637,7 +637,7 @@ int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res) {
     const bool pair = cand[i] >= kTilingPair;
     const int bn = pair ? cand[i] - kTilingPair : cand[i];
     // ties go to the later candidate only when it is clearly better: single-CTA and narrower first
-    const double c = igemm_model_cycles(Cout, M, num_k_blocks, has_res, bn, pair) * (pair ? 1.02 : 1.0);
+    const double c = igemm_model_cycles(Cout, M, num_k_blocks, has_res, bn, pair, sms) * (pair ? 1.02 : 1.0);
     if (best == 0 || c < best_c * 0.985) { best = cand[i]; best_c = c; }
   }
   return best;
@@ -674,6 +674,7 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   plan->max_batch = N;
   plan->stem_mode = kModeGeneric;
   plan->tuned_tiling = plan->tuned_batch = 0;
+  plan->grid_sms = 0;
   q.stem_rb = 0; q.dbg = nullptr;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
@@ -739,6 +740,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   const bool rows = (W % 16 == 0) && Q <= kBlockM && !getenv("AI4E_B200_STEM_IM2COL");
   plan->stem_mode = rows ? kModeStemRows : kModeStemIm2col;
   plan->tuned_tiling = plan->tuned_batch = 0;
+  plan->grid_sms = 0;
   const uint32_t es4[4] = {1, 1, 1, 1};
   int rc;
   if (rows) {
@@ -806,18 +808,20 @@ int igemm_launch(const IgemmPlan& plan, int batch, int tiling, cudaStream_t stre
                plan.max_batch);
   IgemmParams prm = plan.prm;
   const long long M = (long long)batch * prm.PQ;
+  // CTAs of a persistent grid: every SM, or fewer when the engine leaves room for its other lane
+  const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   if (plan.stem_mode == kModeStemRows) {
     prm.M = (int)M;
     prm.tiles_m = prm.num_tiles = batch * prm.P;  // one tile per output row
     prm.tiles_n = 1;
-    return igemm_launch_bn<64, kModeStemRows>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()), stream);
+    return igemm_launch_bn<64, kModeStemRows>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sms), stream);
   }
   if (plan.stem_mode == kModeStemIm2col) {
     prm.M = (int)M;
     prm.tiles_m = (int)((M + kBlockM - 1) / kBlockM);
     prm.tiles_n = 1;
     prm.num_tiles = prm.tiles_m;
-    return igemm_launch_bn<64, kModeStemIm2col>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sm_count()),
+    return igemm_launch_bn<64, kModeStemIm2col>(plan, plan.tmap_b[0], prm, std::min(prm.num_tiles, sms),
                                                 stream);
   }
   if (tiling == 0) {
@@ -827,7 +831,7 @@ int igemm_launch(const IgemmPlan& plan, int batch, int tiling, cudaStream_t stre
     }
   }
   if (tiling == 0 && plan.tuned_tiling && batch == plan.tuned_batch) tiling = plan.tuned_tiling;
-  if (tiling == 0) tiling = igemm_pick_tiling(prm.Cout, M, prm.num_k_blocks, prm.residual != nullptr);
+  if (tiling == 0) tiling = igemm_pick_tiling(prm.Cout, M, prm.num_k_blocks, prm.residual != nullptr, sms);
   const bool pair = tiling >= kTilingPair;
   const int bn = pair ? tiling - kTilingPair : tiling;
   const int bi = bn == 64 ? 0 : bn == 128 ? 1 : bn == 256 ? 2 : -1;
@@ -840,11 +844,11 @@ int igemm_launch(const IgemmPlan& plan, int batch, int tiling, cudaStream_t stre
   prm.num_tiles = prm.tiles_m * prm.tiles_n;
   if (pair) {
     // a pair tile's halves are loaded with the weight map whose box is BLOCK_N / 2 rows
-    const int grid = 2 * std::min(prm.num_tiles, sm_count() / 2);
+    const int grid = 2 * std::min(prm.num_tiles, sms / 2);
     if (bn == 128) return igemm_launch_bn<128, kModeGeneric, true>(plan, plan.tmap_b[bi - 1], prm, grid, stream);
     return igemm_launch_bn<256, kModeGeneric, true>(plan, plan.tmap_b[bi - 1], prm, grid, stream);
   }
-  const int grid = std::min(prm.num_tiles, sm_count());
+  const int grid = std::min(prm.num_tiles, sms);
   switch (bn) {
     case 64: return igemm_launch_bn<64, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);
     case 128: return igemm_launch_bn<128, kModeGeneric>(plan, plan.tmap_b[bi], prm, grid, stream);

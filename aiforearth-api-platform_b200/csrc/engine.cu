@@ -472,6 +472,11 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   int n_lanes = 2;
   if (const char* v = getenv("AI4E_B200_LANES")) n_lanes = std::max(1, std::min(4, atoi(v)));
   e->lanes.resize(n_lanes);
+  // With two lanes a kernel that occupies every SM keeps the other lane's next kernel from even
+  // starting its prologue and weight prefetch; grids sized for 16 fewer SMs measured +2 % (sweep in
+  // DESIGN.md).  AI4E_B200_GRID_SMS overrides.
+  int grid_sms = n_lanes > 1 ? std::max(2, sm_count() - 16) : 0;
+  if (const char* v = getenv("AI4E_B200_GRID_SMS")) grid_sms = atoi(v);
   for (int li = 0; li < n_lanes; ++li) {
   Lane& ln = e->lanes[li];
   ln.layers = e->layers;
@@ -502,6 +507,7 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
       int rc = igemm_make_plan_stem(&L.plan, ln.bufs[d.in_buf], max_batch, L.in_h, L.in_w, e->d_stem_w,
                                     (const float*)(e->d_blob + d.b_off), d.relu, ln.bufs[d.out_buf]);
       if (rc) return fail(rc);
+      L.plan.grid_sms = grid_sms;
       L.igemm = true;
       continue;
     }
@@ -510,6 +516,7 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
                              (const float*)(e->d_blob + d.b_off), d.cout, d.kh, d.kw, d.stride, d.pad,
                              d.res_buf >= 0 ? ln.bufs[d.res_buf] : nullptr, d.relu, ln.bufs[d.out_buf]);
     if (rc) return fail(rc);
+    L.plan.grid_sms = grid_sms;
   }
 
   // ---- bottleneck tails: a convolution + ReLU whose only consumer is a 1x1 convolution with a
@@ -537,6 +544,7 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
                                     e->d_blob + b.w_off, (const float*)(e->d_blob + b.b_off), b.cout, ln.bufs[b.res_buf],
                                     ln.bufs[b.out_buf]);
       if (rc) return fail(rc);
+      A.fplan.grid_sms = grid_sms;
       A.fused_first = true;
       B.fused_second = true;
       if (li == 0) e->launches -= 1;

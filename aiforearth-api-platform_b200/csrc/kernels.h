@@ -47,6 +47,7 @@ struct IgemmPlan {
   int stem_mode;          // 0 generic conv; 1 stem via im2col super-pixels; 2 stem via row buffers
   int tuned_tiling;       // igemm_autotune's choice for launches with tuned_batch images (0 = none)
   int tuned_batch;
+  int grid_sms;           // persistent grid sized for this many SMs (0 = all)
 };
 
 // K4b bottleneck tail (conv RxS + relu, then conv 1x1 + residual + relu, one kernel): conv_fused.cu
@@ -67,6 +68,7 @@ struct FusedPlan {
   CUtensorMap tmap_res;  // residual, 128 rows x 64 channels per load
   FusedParams prm;
   int max_batch;
+  int grid_sms;          // persistent grid sized for this many SMs (0 = all)
 };
 int fused_tail_supported(int Cin, int Cmid, int Cout, int R, int S, int stride, int pad);
 int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, int Cin, const void* w2,
@@ -76,7 +78,7 @@ int fused_tail_launch(const FusedPlan& plan, int batch, cudaStream_t stream);
 
 int igemm_supported(int Cin, int Cout, int R, int S, int stride, int pad);
 constexpr int kTilingPair = 1000;  // tiling code = BLOCK_N (+ kTilingPair: CTA-pair kernel, tcgen05 cta_group::2)
-int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res);
+int igemm_pick_tiling(int Cout, long long M, int num_k_blocks, bool has_res, int sms = 0);
 int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Cin,
                     const void* weight, const float* bias, int Cout, int R, int S, int stride,
                     int pad, const void* residual, int relu, void* out);

@@ -17,6 +17,7 @@
 //     one thread per output pixel, same fp32 operation order as the oracle, no FMA
 //     contraction.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace ai4e {
 
