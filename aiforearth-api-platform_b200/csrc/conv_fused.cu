@@ -127,6 +127,12 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   // this CTA's tiles: blockIdx.x, + gridDim.x, ...
   const int my_tiles = p.num_tiles > (int)blockIdx.x ? (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int passes = p.Cout / 128;
+  // first pixel row of this CTA's i-th tile; the engine alternates the direction from layer to layer
+  // so that a consumer starts with what its producer wrote last (still in L2)
+  auto tile_row = [&](int i) {
+    const int t = (int)blockIdx.x + i * (int)gridDim.x;
+    return (p.reverse ? p.num_tiles - 1 - t : t) * kBlockM;
+  };
   const int units2 = passes * kKB2;  // w3 tiles per pixel tile
 
   if (warp == 0) {
@@ -136,7 +142,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     bool waited = false;
     for (int st = 0; st <= my_tiles; ++st) {
       if (st < my_tiles) {
-        const int m0 = ((int)blockIdx.x + st * (int)gridDim.x) * kBlockM;
+        const int m0 = tile_row(st);
         const int n_img = m0 / p.PQ;
         const int rem = m0 - n_img * p.PQ;
         const int p0 = rem / p.Q;
@@ -274,7 +280,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     uint32_t gs = 0;          // second-step chunks this warp has processed (= passes so far)
     int pending_buf = -1;     // residual/staging buffer whose TMA store may still be reading it
     for (int i = 0; i < my_tiles; ++i) {
-      const int m0 = ((int)blockIdx.x + i * (int)gridDim.x) * kBlockM;
+      const int m0 = tile_row(i);
       // ---- step 2: acc1 -> relu(. + b2) -> bf16 `mid` tile (chunks c = side, side + 2, ...)
       if (side < kKB2) {
         const uint32_t a = i & 1u;
@@ -354,7 +360,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const int total = my_tiles * passes;  // chunks per side
       auto coords = [&](int n, int sd, int& m0, int& n0c) {
         const int i = n / passes;
-        m0 = ((int)blockIdx.x + i * (int)gridDim.x) * kBlockM;
+        m0 = tile_row(i);
         n0c = (n - i * passes) * 128 + sd * kChunkN;
       };
       int m0, n0c;
@@ -405,7 +411,7 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "bottleneck tail: M too large");
   FusedParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cmid = Cmid; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
-  q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0;
+  q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0; q.reverse = 0;
   q.bias2 = bias2; q.bias3 = bias3;
   plan->max_batch = N;
   plan->grid_sms = 0;

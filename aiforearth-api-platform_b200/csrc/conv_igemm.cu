@@ -139,6 +139,10 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const int unit = (int)blockIdx.x / kCtas;
   const int unit_stride = (int)gridDim.x / kCtas;
   const bool leader = cta_rank == 0;
+  // Row-tile order.  The engine alternates it from layer to layer: a consumer that starts with the
+  // rows its producer wrote last finds them still in L2 (write-back), which matters for the 103 MB
+  // activations of layer1 that do not fit next to everything else.
+  auto m_index = [&](int tile_m) { return p.reverse ? p.tiles_m - 1 - tile_m : tile_m; };
   const int kStages = Cfg::stages(p.residual != nullptr);  // runtime: depends on the epilogue's needs
   // SWIZZLE_128B operand tiles need 1024-byte alignment.  The kernel has no static shared memory, so
   // the dynamic window starts at the CTA's shared base; the budget above has no slack for rounding up.
@@ -246,7 +250,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       for (int tile = unit; !kRows && tile < p.num_tiles; tile += unit_stride) {
         const int tile_n = tile % p.tiles_n;
-        const int tile_m = tile / p.tiles_n;
+        const int tile_m = m_index(tile / p.tiles_n);
         const int m0 = (tile_m * kCtas + (int)cta_rank) * kBlockM;
         const int n_img = m0 / p.PQ;
         const int rem = m0 - n_img * p.PQ;
@@ -429,7 +433,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int stride_m = unit_stride / p.tiles_n, stride_n = unit_stride - stride_m * p.tiles_n;
     auto place = [&](Chunk& k) -> bool {  // fills the coordinates from (tile, tile_m, tile_n, c)
       if (k.tile >= p.num_tiles) return false;
-      k.m0 = (kRows ? 0 : (k.tile_m * kCtas + (int)cta_rank) * kBlockM) + quad * 32;
+      k.m0 = (kRows ? 0 : (m_index(k.tile_m) * kCtas + (int)cta_rank) * kBlockM) + quad * 32;
       k.n0c = (kRows ? 0 : k.tile_n * BLOCK_N) + k.c * kChunkN;
       return true;
     };
@@ -560,7 +564,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       auto coords = [&](uint32_t q, int& m0, int& n0c) -> bool {
         const int tile = unit + (int)(q / kChunks) * unit_stride;
         if (tile >= p.num_tiles) return false;
-        m0 = ((tile / p.tiles_n) * kCtas + (int)cta_rank) * kBlockM;
+        m0 = (m_index(tile / p.tiles_n) * kCtas + (int)cta_rank) * kBlockM;
         n0c = (tile % p.tiles_n) * BLOCK_N + (int)(q % kChunks) * kChunkN;
         return true;
       };
@@ -675,7 +679,7 @@ int igemm_make_plan(IgemmPlan* plan, const void* in, int N, int H, int W, int Ci
   plan->stem_mode = kModeGeneric;
   plan->tuned_tiling = plan->tuned_batch = 0;
   plan->grid_sms = 0;
-  q.stem_rb = 0; q.dbg = nullptr;
+  q.stem_rb = 0; q.dbg = nullptr; q.reverse = 0;
   int rc = tmap_encode_im2col_nhwc(&plan->tmap_a, in, N, H, W, Cin, R, S, stride, pad, kBlockK, kBlockM);
   if (rc) return rc;
   const uint64_t ktot = (uint64_t)R * S * Cin;
@@ -734,7 +738,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
   AI4E_REQUIRE((long long)N * P * Q < (1ll << 31) - kBlockM, "conv(stem): M too large");
   IgemmParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cout = 64; q.S = kStemTaps; q.stride = 2; q.pad = 3;
-  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks; q.stem_rb = 0; q.dbg = nullptr;
+  q.cin_blocks = 1; q.num_k_blocks = kStemKBlocks; q.stem_rb = 0; q.dbg = nullptr; q.reverse = 0;
   q.tiles_m = q.tiles_n = q.num_tiles = 0; q.relu = relu; q.bias = bias; q.residual = nullptr; q.out = (bf16*)out;
   plan->max_batch = N;
   const bool rows = (W % 16 == 0) && Q <= kBlockM && !getenv("AI4E_B200_STEM_IM2COL");

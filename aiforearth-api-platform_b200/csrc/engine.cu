@@ -47,6 +47,7 @@ struct LayerRt {
   // side branch (a block's downsample convolution): runs on the engine's second stream next to the
   // layers that follow it; `wait_ev` makes its first consumer wait for it
   bool side = false;
+  bool reverse = false;      // walks its row tiles last-to-first (opposite to the producer of its input)
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, wait_ev = nullptr;
 };
 
@@ -203,7 +204,7 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
       }
     } else if (d.op == AI4E_OP_MAXPOOL) {
       rc = launch_maxpool(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, d.kh, d.stride, d.pad,
-                          e->bufs[d.out_buf], stream);
+                          e->bufs[d.out_buf], stream, L.reverse ? 1 : 0);
     } else {
       rc = launch_head(e->bufs[d.in_buf], batch, L.in_h * L.in_w, d.cin, eng->d_blob + d.w_off,
                        (const float*)(eng->d_blob + d.b_off), d.cout, e->d_pooled, d_logits, d_idx, d_prob,
@@ -548,6 +549,27 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
       A.fused_first = true;
       B.fused_second = true;
       if (li == 0) e->launches -= 1;
+    }
+  }
+
+  // ---- row-tile direction: opposite to the layer that wrote the input, so that a layer starts with
+  // the rows still in L2.  Slot 0 (the preprocessed image) is written first-to-last.
+  if (!getenv("AI4E_B200_NO_REVERSE")) {
+    std::vector<char> dir(desc->n_bufs, 0);  // direction in which each slot was last written
+    for (size_t i = 0; i < ln.layers.size(); ++i) {
+      LayerRt& L = ln.layers[i];
+      const ai4e_layer_desc& d = L.d;
+      if (d.op == AI4E_OP_HEAD) continue;
+      if (L.fused_second) {  // written by the previous layer's launch, in that launch's order
+        L.reverse = ln.layers[i - 1].reverse;
+      } else {
+        const bool stem = d.op == AI4E_OP_CONV && L.igemm && L.plan.stem_mode != 0;
+        const bool can = d.op == AI4E_OP_MAXPOOL || (d.op == AI4E_OP_CONV && L.igemm && !stem);
+        L.reverse = can && !dir[d.in_buf];
+        if (d.op == AI4E_OP_CONV && L.igemm) L.plan.prm.reverse = L.reverse;
+        if (L.fused_first) L.fplan.prm.reverse = L.reverse;
+      }
+      dir[d.out_buf] = L.reverse;
     }
   }
 

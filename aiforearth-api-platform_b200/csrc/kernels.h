@@ -29,6 +29,7 @@ struct IgemmParams {
   int num_k_blocks;
   int tiles_m, tiles_n, num_tiles;
   int relu;
+  int reverse;     // walk the row tiles from the last to the first (set per layer by the engine)
   int stem_rb;     // row-mode stem: bytes per input-row buffer in shared memory
   long long* dbg;  // developer aid: clock64 stamps of CTA 0's pipeline (768 slots), null in production
   const float* bias;
@@ -57,6 +58,7 @@ struct FusedParams {
   int S, stride, pad;
   int cin_blocks, num_k_blocks;
   int num_tiles;
+  int reverse;  // walk the row tiles from the last to the first
   const float* bias2;
   const float* bias3;
 };
@@ -92,7 +94,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
 
 // ---- K3 / K5 (pool_head.cu)
 int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,
-                   cudaStream_t stream);
+                   cudaStream_t stream, int reverse = 0);
 int launch_head(const void* in, int N, int HW, int C, const void* fc_w, const float* fc_b,
                 int classes, float* pooled_scratch, float* logits, int32_t* top_idx, float* top_prob,
                 int topk, cudaStream_t stream);

@@ -67,11 +67,12 @@ __device__ __forceinline__ uint32_t max_bf16x2(uint32_t a, uint32_t b) {
 // (q, 8-channel group) pairs in 32-bit arithmetic.  (The first version used the generic kernel's
 // 64-bit flat index: 340 instructions per item, 62 % issue-slot utilisation under ncu.)
 __global__ void __launch_bounds__(256)
-maxpool3s2_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int H, int W, int C8, int P, int Q) {
+maxpool3s2_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int H, int W, int C8, int P, int Q, int reverse) {
   pdl_launch_dependents();
   pdl_wait();
   constexpr uint32_t kNegInf2 = 0xFF80FF80u;  // two bf16 -inf
-  const int row = blockIdx.x;                 // n * P + p
+  const int row = reverse ? (int)gridDim.x - 1 - (int)blockIdx.x : (int)blockIdx.x;  // n * P + p; last rows first
+                                                                                     // when the producer wrote them last
   const int n = row / P, pp = row - n * P;
   const int h0 = pp * 2 - 1;
   const uint4* src = in + (long long)n * H * W * C8;
@@ -101,7 +102,7 @@ maxpool3s2_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int H, 
 }
 
 int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, int reverse) {
   AI4E_REQUIRE(in && out, "maxpool: null pointer");
   AI4E_REQUIRE(C % 8 == 0, "maxpool: C %d not a multiple of 8", C);
   AI4E_REQUIRE(N > 0 && H > 0 && W > 0 && k > 0 && stride > 0 && pad >= 0 && 2 * pad <= k,
@@ -111,7 +112,7 @@ int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride
   const int grid = (int)std::min<long long>((total + 255) / 256, (long long)sm_count() * 16);
   if (k == 3 && stride == 2 && pad == 1 && (long long)H * W * (C / 8) < (1ll << 31) && (long long)N * P < (1ll << 31)) {
     AI4E_CUDA_TRY(launch_pdl(maxpool3s2_kernel, dim3(N * P), dim3(256), 0, stream, (const uint4*)in, (uint4*)out, H, W,
-                             C / 8, P, Q));
+                             C / 8, P, Q, reverse));
     return AI4E_OK;
   }
   AI4E_CUDA_TRY(launch_pdl(maxpool_kernel, dim3(grid), dim3(256), 0, stream, (const uint4*)in, (uint4*)out, N, H, W,
