@@ -10,8 +10,9 @@ preprocess -> 53 convolutions -> head.  Weights are seeded random values
 (ai4e_b200.models.synthetic_state_dict); images are SURVEY 8(d)'s uniform-noise generator (content does not change the work).
 
 Printed keys (one JSON line, rank 0):
-  value         images/s with the uint8 batch already resident in HBM (ai4e_engine_forward_device),
-                CUDA events on the launching stream, max over ranks
+  value         images/s with the uint8 batches already resident in HBM (ai4e_engine_forward_device),
+                two micro-batches in flight on two streams (the engine's lanes), CUDA events
+                bracketing both streams, max over ranks
   e2e           the same metric through the public API with HOST buffers: page-locked uint8
                 batches -> Engine.submit_batch / wait (H2D + kernels + D2H of top-5 inside the
                 timed region, three batches in flight)

@@ -194,7 +194,11 @@ AI4E_API int ai4e_engine_forward_host(ai4e_engine* e, const uint8_t* h_images, i
                              float* h_logits_or_null);
 
 /* Same with the uint8 batch already resident on the engine's device and results left on the
- * device (no host copies); returns after the work is enqueued on `stream`. */
+ * device (no host copies); returns after the work is enqueued on `stream`.  The engine owns
+ * AI4E_B200_LANES (default 2) sets of activation buffers and hands them out round-robin: calls
+ * on DIFFERENT streams overlap on the GPU (the second micro-batch fills the SMs the first leaves
+ * idle), calls on one stream run in order.  Inputs and outputs of calls that may overlap must be
+ * distinct buffers. */
 AI4E_API int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h,
                                int src_w, int32_t* d_top_idx, float* d_top_prob,
                                float* d_logits_or_null, void* stream);
