@@ -1,0 +1,51 @@
+#!/usr/bin/env python
+"""Mint the JPEG fixtures of tests/golden/jpeg/ with Pillow (libjpeg-turbo), the decoder a PyTorch
+API container uses: small synthetic images saved with different chroma subsampling, quality,
+restart intervals and (optimised) Huffman tables, plus Pillow's decode of each as .npy.
+    python tests/golden/make_jpeg_goldens.py
+"""
+import io
+import os
+import sys
+
+import numpy as np
+from PIL import Image
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+from oracle import resnet_oracle as ro  # noqa: E402
+
+OUT = os.path.join(HERE, "jpeg")
+CASES = [  # name, (h, w), save kwargs
+    ("q90_420_64x64", (64, 64), dict(quality=90, subsampling=2)),
+    ("q75_420_ragged_61x83", (61, 83), dict(quality=75, subsampling=2)),
+    ("q85_422_50x70", (50, 70), dict(quality=85, subsampling=1)),
+    ("q95_444_33x47", (33, 47), dict(quality=95, subsampling=0)),
+    ("q60_420_rst2_72x104", (72, 104), dict(quality=60, subsampling=2, restart_marker_blocks=2)),
+    ("q80_420_opt_rstrow_96x80", (96, 80), dict(quality=80, subsampling=2, optimize=True, restart_marker_rows=1)),
+    ("q30_420_40x40", (40, 40), dict(quality=30, subsampling=2)),
+    ("q92_gray_45x37", (45, 37), dict(quality=92)),
+    ("q90_420_224x224", (224, 224), dict(quality=90, subsampling=2)),
+]
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    rng = np.random.default_rng(11)
+    for i, (name, (h, w), kw) in enumerate(CASES):
+        img = ro.synthetic_images(1, h, w, 3, seed=100 + i)[0]
+        img = np.clip(img.astype(np.int32) + rng.integers(-12, 13, img.shape), 0, 255).astype(np.uint8)  # some texture
+        pil = Image.fromarray(img)
+        if "gray" in name:
+            pil = pil.convert("L")
+        buf = io.BytesIO()
+        pil.save(buf, format="JPEG", **kw)
+        data = buf.getvalue()
+        open(os.path.join(OUT, name + ".jpg"), "wb").write(data)
+        dec = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        np.save(os.path.join(OUT, name + ".npy"), dec)
+        print(name, len(data), "bytes", dec.shape)
+
+
+if __name__ == "__main__":
+    main()
