@@ -44,6 +44,15 @@ class ModelDesc(C.Structure):
                 ("layers", C.POINTER(LayerDesc))]
 
 
+class JpegInfo(C.Structure):
+    """ai4e_jpeg_info of include/ai4e_b200.h"""
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("components", C.c_int32), ("hmax", C.c_int32),
+                ("vmax", C.c_int32), ("h", C.c_int32 * 3), ("v", C.c_int32 * 3), ("blocks_w", C.c_int32 * 3),
+                ("blocks_h", C.c_int32 * 3), ("comp_w", C.c_int32 * 3), ("comp_h", C.c_int32 * 3),
+                ("restart_interval", C.c_int32), ("coef_off", C.c_int64 * 3), ("record_int16", C.c_int64),
+                ("plane_bytes", C.c_int64)]
+
+
 class EngineStats(C.Structure):
     _fields_ = [("images", C.c_uint64), ("batches", C.c_uint64), ("batch_hist", C.c_uint64 * 11),
                 ("queue_depth", C.c_uint64), ("gpu_ms_total", C.c_double), ("lat_ms_p50", C.c_double),
@@ -62,6 +71,9 @@ SIGNATURES = {
     "ai4e_device_count": (_i, [C.POINTER(C.c_int)]),
     "ai4e_preprocess": (_i, [_vp, _i, _i, _i, _i, _i64, _i, _i, _i, _i, _i, _fp, _fp, _i, _i, _vp, _vp]),
     "ai4e_conv_layer": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp]),
+    "ai4e_jpeg_entropy_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(JpegInfo)]),
+    "ai4e_jpeg_reconstruct": (_i, [_vp, _i, C.POINTER(JpegInfo), _vp, _vp, _vp]),
+    "ai4e_jpeg_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp]),
     "ai4e_bottleneck_tail": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp]),
     "ai4e_maxpool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ai4e_head": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),

@@ -66,6 +66,48 @@ def conv_layer(x_nhwc: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tens
     return out
 
 
+def jpeg_entropy_decode(data: bytes):
+    """host only: baseline JPEG bytes -> (JpegInfo, int16 record [3 x 64 quantisation values, then
+    the quantised coefficients per component, natural order]).  Raises Ai4eError for unsupported
+    streams (progressive, CMYK, ...)."""
+    import ctypes as C
+    import numpy as np
+    lib = L.load()
+    info = L.JpegInfo()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    L.check(lib.ai4e_jpeg_entropy_decode(buf, len(data), None, 0, C.byref(info)))
+    rec = np.zeros(int(info.record_int16), np.int16)
+    L.check(lib.ai4e_jpeg_entropy_decode(buf, len(data), rec.ctypes.data_as(C.c_void_p), rec.size, C.byref(info)))
+    return info, rec
+
+
+def jpeg_decode(data: bytes, stream=None) -> torch.Tensor:
+    """baseline JPEG bytes -> uint8 [H, W, 3] RGB on the GPU, bit-identical to Pillow / libjpeg-turbo
+    (entropy decode on this thread, IDCT + upsampling + colour conversion on the device)."""
+    import ctypes as C
+    lib = L.load()
+    info = L.JpegInfo()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    L.check(lib.ai4e_jpeg_entropy_decode(buf, len(data), None, 0, C.byref(info)))
+    out = torch.empty((info.height, info.width, 3), dtype=torch.uint8, device="cuda")
+    h, w = C.c_int32(), C.c_int32()
+    L.check(lib.ai4e_jpeg_decode(buf, len(data), _ptr(out), out.numel(), C.byref(h), C.byref(w), _stream_ptr(stream)))
+    return out
+
+
+def jpeg_reconstruct(records: torch.Tensor, info, stream=None) -> torch.Tensor:
+    """[batch, record_int16] int16 records of ONE geometry on the GPU -> uint8 [batch, H, W, 3]."""
+    import ctypes as C
+    lib = L.load()
+    assert records.is_cuda and records.dtype == torch.int16 and records.is_contiguous()
+    b = records.shape[0]
+    assert records.shape[1] == info.record_int16
+    scratch = torch.empty((b, int(info.plane_bytes)), dtype=torch.uint8, device=records.device)
+    out = torch.empty((b, info.height, info.width, 3), dtype=torch.uint8, device=records.device)
+    L.check(lib.ai4e_jpeg_reconstruct(_ptr(records), b, C.byref(info), _ptr(scratch), _ptr(out), _stream_ptr(stream)))
+    return out
+
+
 def bottleneck_tail(x_nhwc: torch.Tensor, w2_krsc: torch.Tensor, b2: torch.Tensor, stride: int, pad: int,
                     w3_kc: torch.Tensor, b3: torch.Tensor, residual: torch.Tensor, stream=None) -> torch.Tensor:
     """relu(conv1x1(relu(conv(x; w2) + b2); w3) + b3 + residual) in one kernel (K4b).

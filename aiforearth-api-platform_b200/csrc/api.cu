@@ -102,6 +102,42 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 
+int ai4e_jpeg_entropy_decode(const uint8_t* jpeg, uint64_t len, int16_t* h_record, uint64_t capacity_int16,
+                             ai4e_jpeg_info* out) {
+  return jpeg_host_decode(jpeg, len, h_record, capacity_int16, out);
+}
+
+int ai4e_jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry, uint8_t* d_scratch,
+                          uint8_t* d_rgb_hwc, void* stream) {
+  return jpeg_reconstruct(d_records, batch, geometry, d_scratch, d_rgb_hwc, (cudaStream_t)stream);
+}
+
+int ai4e_jpeg_decode(const uint8_t* jpeg, uint64_t len, uint8_t* d_rgb_hwc, uint64_t capacity_bytes, int32_t* out_height,
+                     int32_t* out_width, void* stream) {
+  AI4E_REQUIRE(jpeg && d_rgb_hwc, "jpeg_decode: null pointer");
+  ai4e_jpeg_info info;
+  int rc = jpeg_host_decode(jpeg, len, nullptr, 0, &info);
+  if (rc) return rc;
+  if (out_height) *out_height = info.height;
+  if (out_width) *out_width = info.width;
+  AI4E_REQUIRE(capacity_bytes >= (uint64_t)info.width * info.height * 3, "jpeg_decode: output needs %lld bytes",
+               (long long)info.width * info.height * 3);
+  std::vector<int16_t> rec((size_t)info.record_int16);
+  rc = jpeg_host_decode(jpeg, len, rec.data(), rec.size(), &info);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  int16_t* d_rec = nullptr;
+  uint8_t* d_scratch = nullptr;
+  AI4E_CUDA_TRY(cudaMallocAsync((void**)&d_rec, rec.size() * sizeof(int16_t), s));
+  AI4E_CUDA_TRY(cudaMallocAsync((void**)&d_scratch, (size_t)info.plane_bytes, s));
+  AI4E_CUDA_TRY(cudaMemcpyAsync(d_rec, rec.data(), rec.size() * sizeof(int16_t), cudaMemcpyHostToDevice, s));
+  rc = jpeg_reconstruct(d_rec, 1, &info, d_scratch, d_rgb_hwc, s);
+  AI4E_CUDA_TRY(cudaStreamSynchronize(s));  // `rec` is a stack-lifetime host buffer
+  cudaFreeAsync(d_rec, s);
+  cudaFreeAsync(d_scratch, s);
+  return rc;
+}
+
 int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w, int cin, const void* d_w2_krsc,
                          const float* d_bias2, int cmid, int kh, int kw, int stride, int pad, const void* d_w3_kc,
                          const float* d_bias3, int cout, const void* d_residual, void* d_out_nhwc, void* stream) {

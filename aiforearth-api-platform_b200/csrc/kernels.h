@@ -4,6 +4,8 @@
 
 #include "common.cuh"
 
+struct ai4e_jpeg_info;  // include/ai4e_b200.h
+
 namespace ai4e {
 
 int sm_count();
@@ -13,6 +15,11 @@ int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int
                       long long src_image_stride, int src_row_stride, int resize_h, int resize_w,
                       int out_h, int out_w, const float* mean, const float* stdv, int layout,
                       int out_channels, void* d_dst, cudaStream_t stream);
+
+// ---- K0 baseline JPEG (jpeg.cu): host headers + entropy decode, device IDCT / upsampling / colour
+int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_t capacity_int16, ai4e_jpeg_info* out);
+int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry, uint8_t* d_scratch,
+                     uint8_t* d_rgb_hwc, cudaStream_t stream);
 
 // ---- direct convolution on CUDA cores (conv_direct.cu)
 int launch_conv_direct(const void* in, int N, int H, int W, int Cin, const void* weight,

@@ -98,6 +98,46 @@ AI4E_API int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int
                     int stride, int pad, const void* d_residual_or_null, int relu,
                     void* d_out_nhwc, int algo, void* stream);
 
+/* K0.  Baseline JPEG decode (requests carry encoded images; the reference
+ * gates on image MIME types at APIs/1.0/base-py/ai4e_service.py:72,127-129 and leaves decoding to
+ * the callback it calls at :203 - Pillow / libjpeg-turbo in a PyTorch container, which this
+ * matches bit for bit: accurate integer IDCT, fancy chroma upsampling, fixed-point YCbCr->RGB).
+ * Split like a hybrid decoder: the entropy (Huffman) decode is sequential and runs on the
+ * submitting thread's host core; dequantisation, IDCT, upsampling and colour conversion run on the
+ * GPU.  8-bit baseline / extended sequential Huffman, 1 or 3 components, 4:4:4 / 4:2:2 / 4:2:0,
+ * restart intervals; anything else -> AI4E_ERR_UNSUPPORTED.
+ *
+ * A decoded image travels as a RECORD of int16: 3 x 64 quantisation values (natural order, per
+ * component), then the quantised coefficients, component after component, block rows padded to
+ * whole MCUs, 64 per block in natural order.  Images with equal geometry (ai4e_jpeg_info up to
+ * `record_int16`) share one launch. */
+typedef struct ai4e_jpeg_info {
+  int32_t width, height, components;
+  int32_t hmax, vmax;
+  int32_t h[3], v[3];                 /* sampling factors */
+  int32_t blocks_w[3], blocks_h[3];   /* 8x8 blocks per component, padded to whole MCUs */
+  int32_t comp_w[3], comp_h[3];       /* real size of each component in samples */
+  int32_t restart_interval;
+  int64_t coef_off[3];                /* int16 offset of each component's coefficients in the record */
+  int64_t record_int16;               /* int16 per record (multiple of 64) */
+  int64_t plane_bytes;                /* scratch bytes per image for ai4e_jpeg_reconstruct */
+} ai4e_jpeg_info;
+
+/* Host only: parses the headers; with h_record != NULL also entropy-decodes into it
+ * (capacity in int16, must be >= info.record_int16: call once with NULL to size it). */
+AI4E_API int ai4e_jpeg_entropy_decode(const uint8_t* jpeg, uint64_t len, int16_t* h_record,
+                                      uint64_t capacity_int16, ai4e_jpeg_info* out);
+
+/* GPU: `batch` records of one geometry (device memory, record_int16 apart) -> dense uint8
+ * [batch][height][width][3] RGB.  d_scratch: batch * plane_bytes. */
+AI4E_API int ai4e_jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry,
+                                   uint8_t* d_scratch, uint8_t* d_rgb_hwc, void* stream);
+
+/* Convenience (tests, single images): entropy decode on the calling thread, H2D, reconstruct.
+ * Scratch comes from the stream's memory pool. */
+AI4E_API int ai4e_jpeg_decode(const uint8_t* jpeg, uint64_t len, uint8_t* d_rgb_hwc, uint64_t capacity_bytes,
+                              int32_t* out_height, int32_t* out_width, void* stream);
+
 /* K4b.  The tail of a ResNet bottleneck block in one kernel:
  *   y = relu(conv_khxkw(x; w2) + bias2)       [batch][p][q][cmid]   (conv2 + bn2 + relu, BN folded)
  *   z = relu(y * w3^T + bias3 + residual)     [batch][p][q][cout]   (conv3 1x1 + bn3 + add + relu)

@@ -53,3 +53,73 @@ def test_oracle_rejects_progressive():
     PIL.fromarray(np.zeros((16, 16, 3), np.uint8)).save(buf, format="JPEG", progressive=True)
     with pytest.raises(ValueError):
         jo.decode(buf.getvalue())
+
+
+# ------------------------------------------------------------------ library, host side (no GPU needed)
+@pytest.mark.parametrize("path", FIXTURES, ids=_name)
+def test_host_entropy_decoder_matches_oracle_coefficients(path):
+    """ai4e_jpeg_entropy_decode runs on the host: its record must hold exactly the oracle's
+    quantisation tables and quantised coefficients."""
+    from ai4e_b200 import ops
+    data = open(path, "rb").read()
+    info, rec = ops.jpeg_entropy_decode(data)
+    f = jo.parse(data)
+    assert (info.width, info.height, info.components, info.hmax, info.vmax, info.restart_interval) == \
+           (f.width, f.height, len(f.comps), f.hmax, f.vmax, f.restart_interval)
+    assert info.record_int16 % 64 == 0 and rec.size == info.record_int16
+    for c, comp in enumerate(f.comps):
+        assert (info.blocks_w[c], info.blocks_h[c], info.comp_w[c], info.comp_h[c]) == \
+               (comp.blocks_w, comp.blocks_h, comp.width, comp.height)
+        n = comp.blocks_w * comp.blocks_h * 64
+        got = rec[info.coef_off[c]:info.coef_off[c] + n].reshape(comp.blocks_h, comp.blocks_w, 64)
+        assert np.array_equal(got, comp.coefs)
+        assert np.array_equal(rec[c * 64:(c + 1) * 64].astype(np.uint16), f.qt[comp.tq])
+
+
+def test_host_decoder_rejects_what_it_does_not_support():
+    from ai4e_b200 import ops, Ai4eError
+    PIL = pytest.importorskip("PIL.Image")
+    buf = io.BytesIO()
+    PIL.fromarray(np.zeros((16, 16, 3), np.uint8)).save(buf, format="JPEG", progressive=True)
+    with pytest.raises(Ai4eError, match="progressive"):
+        ops.jpeg_entropy_decode(buf.getvalue())
+    with pytest.raises(Ai4eError, match="SOI"):
+        ops.jpeg_entropy_decode(b"\x89PNG\r\n\x1a\n" + b"\0" * 32)
+    good = open(FIXTURES[0], "rb").read()
+    with pytest.raises(Ai4eError):
+        ops.jpeg_entropy_decode(good[:200])  # truncated inside the tables / scan
+
+
+# ------------------------------------------------------------------ GPU: bit-exact reconstruction
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", FIXTURES, ids=_name)
+def test_gpu_decode_is_bit_exact_with_pillow(path):
+    from ai4e_b200 import ops
+    want = np.load(path[:-4] + ".npy")
+    got = ops.jpeg_decode(open(path, "rb").read()).cpu().numpy()
+    assert got.shape == want.shape
+    assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ, max {np.abs(got.astype(int) - want).max()}"
+
+
+@pytest.mark.gpu
+def test_gpu_reconstruct_batch_of_one_geometry():
+    """several images of one geometry (different content and quality -> different quantisation
+    tables) reconstructed by one launch pair, each bit-exact with Pillow."""
+    import torch
+    from ai4e_b200 import ops
+    PIL = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(3)
+    recs, wants, info0 = [], [], None
+    for i, q in enumerate((35, 60, 75, 90, 97)):
+        img = rng.integers(0, 256, (120, 200, 3), dtype=np.uint8)
+        img = (img // 3 + np.linspace(0, 160, 200, dtype=np.int32)[None, :, None] + 5 * i).astype(np.uint8)
+        buf = io.BytesIO()
+        PIL.fromarray(img).save(buf, format="JPEG", quality=q, subsampling=2)
+        wants.append(np.asarray(PIL.open(io.BytesIO(buf.getvalue())).convert("RGB")))
+        info, rec = ops.jpeg_entropy_decode(buf.getvalue())
+        info0 = info0 or info
+        assert info.record_int16 == info0.record_int16
+        recs.append(rec)
+    out = ops.jpeg_reconstruct(torch.from_numpy(np.stack(recs)).cuda(), info0).cpu().numpy()
+    for got, want in zip(out, wants):
+        assert np.array_equal(got, want)
