@@ -83,6 +83,7 @@ SIGNATURES = {
     "ai4e_engine_forward_host": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
     "ai4e_engine_forward_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "ai4e_engine_submit": (_i, [_vp, _vp, _i, _i, _i, _i, _u64, _u64p]),
+    "ai4e_engine_submit_jpeg": (_i, [_vp, _vp, _u64, _u64, C.POINTER(_u64)]),
     "ai4e_engine_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
     "ai4e_engine_profile": (_i, [_vp, _vp, _i, _i, _i, _i, _fp, _i]),
     "ai4e_engine_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),

@@ -91,6 +91,18 @@ class Engine(_Base):
                                              a.strides[0], tag, C.byref(t)))
         return t.value
 
+    def submit_jpeg(self, data: bytes, tag: int = 0) -> int:
+        """one baseline JPEG (bytes) -> ticket.  The Huffman decode runs on this thread with the GIL
+        released; the GPU reconstructs the pixels (bit-identical to Pillow) in front of the model."""
+        buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+        t = C.c_uint64()
+        L.check(self._lib.ai4e_engine_submit_jpeg(self._h, buf, len(data), tag, C.byref(t)))
+        return t.value
+
+    def classify_jpeg(self, data: bytes, want_logits: bool = False):
+        """blocking: submit_jpeg + wait."""
+        return self.wait(self.submit_jpeg(data), want_logits)
+
     def submit_batch(self, images_u8: np.ndarray) -> range:
         """dense [B,H,W,C] uint8 host array -> tickets (a range).  Page-locked arrays are read in
         place by the H2D copy: keep them unchanged until the last ticket has been waited for."""

@@ -65,6 +65,12 @@ struct BatchCtx {
   Clock::time_point t_first;
   int launch_rc = 0;
   const uint8_t* ext_src = nullptr;  // zero-copy source (page-locked caller memory), else h_in
+  // JPEG batches: h_in holds entropy-decoded records of one geometry instead of pixels
+  int kind = 0;                      // 0 = raw pixels; else a key of the JPEG geometry (see jpeg_kind)
+  ai4e_jpeg_info jinfo{};
+  int16_t* d_rec = nullptr;          // device copy of the records, grown on demand
+  uint8_t* d_planes = nullptr;       // component planes between the IDCT and the colour kernel
+  size_t d_rec_bytes = 0, d_planes_bytes = 0;
 };
 
 }  // namespace
@@ -147,6 +153,9 @@ int alloc_ctx(ai4e_engine* e, BatchCtx& c) {
 void free_ctx(BatchCtx& c) {
   if (c.h_in) cudaFreeHost(c.h_in);
   if (c.d_in) cudaFree(c.d_in);
+  if (c.d_rec) cudaFree(c.d_rec);
+  if (c.d_planes) cudaFree(c.d_planes);
+  c.d_rec = nullptr; c.d_planes = nullptr; c.d_rec_bytes = c.d_planes_bytes = 0;
   if (c.h_idx) cudaFreeHost(c.h_idx);
   if (c.h_prob) cudaFreeHost(c.h_prob);
   if (c.h_logits) cudaFreeHost(c.h_logits);
@@ -237,7 +246,29 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
   const int K = e->desc.num_classes;
   const size_t img_bytes = (size_t)c.src_h * c.src_w * e->desc.in_c;
   const uint8_t* h_src = c.ext_src ? c.ext_src : c.h_in;  // ext_src: caller's page-locked buffer
-  AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+  if (c.kind != 0) {
+    // K0: the slots hold entropy-decoded JPEG records (one geometry per batch): copy them, then
+    // dequantise + IDCT + upsample + colour-convert straight into the pixel slots K1 reads
+    const size_t rec_bytes = (size_t)c.jinfo.record_int16 * sizeof(int16_t);
+    const size_t need_rec = rec_bytes * e->max_batch, need_planes = (size_t)c.jinfo.plane_bytes * e->max_batch;
+    if (c.d_rec_bytes < need_rec) {
+      if (c.d_rec) AI4E_CUDA_TRY(cudaFree(c.d_rec));
+      c.d_rec = nullptr; c.d_rec_bytes = 0;
+      AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_rec, need_rec));
+      c.d_rec_bytes = need_rec;
+    }
+    if (c.d_planes_bytes < need_planes) {
+      if (c.d_planes) AI4E_CUDA_TRY(cudaFree(c.d_planes));
+      c.d_planes = nullptr; c.d_planes_bytes = 0;
+      AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_planes, need_planes));
+      c.d_planes_bytes = need_planes;
+    }
+    AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_rec, c.h_in, rec_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+    int rcj = jpeg_reconstruct(c.d_rec, c.count, &c.jinfo, c.d_planes, c.d_in, c.stream);
+    if (rcj) return rcj;
+  } else {
+    AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+  }
   {
     std::lock_guard<std::mutex> lk(e->launch_mu);
     Lane* ln = nullptr;
@@ -715,7 +746,7 @@ int ai4e_engine_forward_host(ai4e_engine* e, const uint8_t* h_images, int batch,
   AI4E_CUDA_TRY(cudaSetDevice(e->device));
   std::lock_guard<std::mutex> lk(e->sync_mu);
   BatchCtx& c = e->sync_ctx;
-  c.count = batch; c.src_h = src_h; c.src_w = src_w;
+  c.count = batch; c.src_h = src_h; c.src_w = src_w; c.kind = 0;
   c.ext_src = is_page_locked(h_images) ? h_images : nullptr;  // page-locked input: H2D straight from it
   if (!c.ext_src) memcpy(c.h_in, h_images, img_bytes * batch);
   int rc = launch_batch(e, c, h_logits_or_null != nullptr);
@@ -780,7 +811,7 @@ int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c
         e->open_ctx->copied.store(0);
       }
       ctx = e->open_ctx;
-      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w)) {  // a batch holds one image size
+      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w || ctx->kind != 0)) {  // a batch holds one image size and kind
         e->closed_q.push_back(ctx);
         e->open_ctx = nullptr;
         e->cv_work.notify_one();
@@ -790,6 +821,7 @@ int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c
     }
     if (ctx->count == 0) {
       ctx->src_h = h; ctx->src_w = w;
+      ctx->kind = 0;
       ctx->t_first = Clock::now();
       ctx->first_ticket = e->next_ticket;
     }
@@ -809,6 +841,73 @@ int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c
   } else {
     for (int y = 0; y < h; ++y) memcpy(dst + (size_t)y * w * c, h_hwc + (size_t)y * row_stride, (size_t)w * c);
   }
+  ctx->copied.fetch_add(1, std::memory_order_release);
+  return AI4E_OK;
+}
+
+// geometry key of a JPEG batch: images whose records have the same layout share a launch
+static int jpeg_kind(const ai4e_jpeg_info& j) { return 1 + j.components * 64 + j.hmax * 16 + j.vmax * 4 + (j.h[0] * 2 + j.v[0]) % 4; }
+
+int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
+  (void)tag;
+  AI4E_REQUIRE(e && jpeg && out_ticket, "submit_jpeg: null pointer");
+  AI4E_REQUIRE(e->desc.in_c == 3, "submit_jpeg: the model takes %d channels, a JPEG decodes to 3", e->desc.in_c);
+  // entropy decode on the caller's thread, into a thread-local record: nothing is reserved if it fails
+  thread_local std::vector<int16_t> rec;
+  ai4e_jpeg_info info;
+  int rc = jpeg_host_decode(jpeg, len, nullptr, 0, &info);
+  if (rc) return rc;
+  const size_t rec_bytes = (size_t)info.record_int16 * sizeof(int16_t);
+  const size_t rgb_bytes = (size_t)info.width * info.height * 3;
+  AI4E_REQUIRE(rec_bytes <= e->slot_bytes && rgb_bytes <= e->slot_bytes,
+               "submit_jpeg: a %d x %d image needs %zu bytes of staging, the slot holds %zu (AI4E_B200_MAX_SRC_BYTES)",
+               info.width, info.height, std::max(rec_bytes, rgb_bytes), e->slot_bytes);
+  if (rec.size() < (size_t)info.record_int16) rec.resize((size_t)info.record_int16);
+  rc = jpeg_host_decode(jpeg, len, rec.data(), rec.size(), &info);
+  if (rc) return rc;
+  const int kind = jpeg_kind(info), h = info.height, w = info.width;
+  BatchCtx* ctx = nullptr;
+  int slot = 0;
+  {
+    std::unique_lock<std::mutex> lk(e->mu);
+    for (;;) {
+      if (e->stopping) { set_last_error("submit_jpeg: engine is shutting down"); return AI4E_ERR_STATE; }
+      if (!e->healthy.load()) { set_last_error("submit_jpeg: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
+      if (!e->open_ctx) {
+        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
+        e->open_ctx = e->free_q.front();
+        e->free_q.pop_front();
+        e->open_ctx->count = 0;
+        e->open_ctx->copied.store(0);
+      }
+      ctx = e->open_ctx;
+      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w || ctx->kind != kind ||
+                             ctx->jinfo.record_int16 != info.record_int16)) {
+        e->closed_q.push_back(ctx);
+        e->open_ctx = nullptr;
+        e->cv_work.notify_one();
+        continue;
+      }
+      break;
+    }
+    if (ctx->count == 0) {
+      ctx->src_h = h; ctx->src_w = w;
+      ctx->kind = kind;
+      ctx->jinfo = info;
+      ctx->t_first = Clock::now();
+      ctx->first_ticket = e->next_ticket;
+    }
+    slot = ctx->count++;
+    *out_ticket = e->next_ticket++;
+    e->r_submit[*out_ticket % kResultRing] = Clock::now();
+    e->r_status[*out_ticket % kResultRing] = 1;  // pending
+    if (ctx->count == e->max_batch) {
+      e->closed_q.push_back(ctx);
+      e->open_ctx = nullptr;
+    }
+    e->cv_work.notify_one();
+  }
+  memcpy(ctx->h_in + (size_t)slot * rec_bytes, rec.data(), rec_bytes);
   ctx->copied.fetch_add(1, std::memory_order_release);
   return AI4E_OK;
 }
@@ -843,7 +942,7 @@ int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count,
     }
     ctx = e->open_ctx;
     e->open_ctx = nullptr;
-    ctx->count = count; ctx->src_h = h; ctx->src_w = w;
+    ctx->count = count; ctx->src_h = h; ctx->src_w = w; ctx->kind = 0;
     ctx->t_first = Clock::now();
     ctx->first_ticket = e->next_ticket;
     ctx->ext_src = pinned ? h_images : nullptr;

@@ -257,6 +257,14 @@ AI4E_API int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int
  * has been waited for; pageable memory is copied to the staging slot before returning. */
 AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count, int h, int w,
                                       int c, uint64_t* out_first_ticket);
+/* Same for one baseline JPEG (K0): headers and the entropy decode run on the calling thread,
+ * the record joins the open micro-batch (a batch holds images of one size and sampling) and the
+ * GPU reconstructs the pixels in front of the preprocessing kernel.  The engine's model must
+ * take 3 channels; unsupported streams (progressive, CMYK, ...) -> AI4E_ERR_UNSUPPORTED and
+ * nothing is queued.  This is `Image.open(BytesIO(request.data)).convert("RGB")` + the rest of
+ * the callback at APIs/1.0/base-py/ai4e_service.py:203. */
+AI4E_API int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag,
+                                     uint64_t* out_ticket);
 AI4E_API int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                      float* logits_or_null);
 AI4E_API int ai4e_engine_flush(ai4e_engine* e);

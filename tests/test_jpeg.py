@@ -123,3 +123,48 @@ def test_gpu_reconstruct_batch_of_one_geometry():
     out = ops.jpeg_reconstruct(torch.from_numpy(np.stack(recs)).cuda(), info0).cpu().numpy()
     for got, want in zip(out, wants):
         assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_engine_submit_jpeg_equals_submit_of_decoded_pixels():
+    """the engine classifies JPEG bytes exactly as it classifies Pillow's decode of them: mixed
+    sizes and samplings (each closes the open micro-batch), the resize path for non-224 images,
+    many threads submitting at once, and a bad stream that must fail without queueing anything."""
+    import threading
+    from tests import util
+    from ai4e_b200 import Ai4eError
+    from ai4e_b200.engine import Engine
+    PIL = pytest.importorskip("PIL.Image")
+    g, imgs = util.load_golden("resnet50")
+    cases = []
+    for i, img in enumerate(imgs[:6]):  # 224 x 224, 4:2:0, differing quality
+        buf = io.BytesIO()
+        PIL.fromarray(img).save(buf, format="JPEG", quality=80 + 3 * i, subsampling=2)
+        cases.append(buf.getvalue())
+    for i, (hw, sub) in enumerate((((224, 224), 1), ((200, 256), 2), ((200, 256), 2))):  # other sampling / size
+        buf = io.BytesIO()
+        PIL.fromarray(imgs[i]).resize((hw[1], hw[0])).save(buf, format="JPEG", quality=88, subsampling=sub)
+        cases.append(buf.getvalue())
+    decoded = [np.asarray(PIL.open(io.BytesIO(d)).convert("RGB")) for d in cases]
+    with Engine(util.program_for("resnet50", 3, 224, False), device=0, max_batch=8, max_wait_us=3000) as e:
+        want = [e.classify(d, want_logits=True) for d in decoded]
+        got = [None] * len(cases)
+
+        def work(k):
+            got[k] = e.classify_jpeg(cases[k], want_logits=True)
+
+        threads = [threading.Thread(target=work, args=(k,)) for k in range(len(cases))]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        for k, ((wi, wp, wl), (gi, gp, gl)) in enumerate(zip(want, got)):
+            assert np.array_equal(gi, wi), k
+            assert np.array_equal(gl, wl), (k, np.abs(gl - wl).max())  # same pixels -> same bits
+        before = e.stats()["images"]
+        buf = io.BytesIO()
+        PIL.fromarray(imgs[0]).save(buf, format="JPEG", progressive=True)
+        with pytest.raises(Ai4eError, match="progressive"):
+            e.submit_jpeg(buf.getvalue())
+        e.flush()
+        assert e.stats()["images"] == before and e.stats()["healthy"]
