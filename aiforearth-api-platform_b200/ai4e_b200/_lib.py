@@ -93,6 +93,9 @@ SIGNATURES = {
     "ai4e_pool_create": (_i, [C.POINTER(C.c_int), _i, C.POINTER(ModelDesc), _vp, _u64, _i, _i, C.POINTER(_vp)]),
     "ai4e_pool_destroy": (_i, [_vp]),
     "ai4e_pool_submit": (_i, [_vp, _vp, _i, _i, _i, _i, _u64, _u64p]),
+    "ai4e_pool_submit_jpeg": (_i, [_vp, _vp, _u64, _u64, _u64p]),
+    "ai4e_engine_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
+    "ai4e_engine_wait_many": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ai4e_pool_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),
     "ai4e_pool_flush": (_i, [_vp]),
     "ai4e_pool_size": (_i, [_vp]),

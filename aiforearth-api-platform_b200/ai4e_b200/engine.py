@@ -91,6 +91,29 @@ class Engine(_Base):
                                              a.strides[0], tag, C.byref(t)))
         return t.value
 
+    def submit_tile(self, tile_u8_hwc: np.ndarray, chip: int = 256) -> np.ndarray:
+        """every chip x chip chip of a [H, W, C] uint8 tile (row-major over the chip grid), submitted
+        in one C call with the tile's row stride -> uint64 tickets [gh * gw]."""
+        a = np.asarray(tile_u8_hwc)
+        if a.dtype != np.uint8 or a.ndim != 3 or a.strides[2] != 1 or a.strides[1] != a.shape[2]:
+            raise ValueError("expected a uint8 [H, W, C] tile with dense pixels")
+        gh, gw = a.shape[0] // chip, a.shape[1] // chip
+        tickets = np.empty(max(gh * gw, 1), np.uint64)
+        n = C.c_int32()
+        L.check(self._lib.ai4e_engine_submit_tile(self._h, a.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1], a.shape[2],
+                                                  a.strides[0], chip, tickets.ctypes.data_as(C.c_void_p), tickets.size,
+                                                  C.byref(n)))
+        return tickets[:n.value]
+
+    def wait_many(self, tickets: np.ndarray):
+        """-> (idx [n, 5] int32, prob [n, 5] float32) for the tickets, in order."""
+        t = np.ascontiguousarray(tickets, np.uint64)
+        idx = np.empty((t.size, L.TOPK), np.int32)
+        prob = np.empty((t.size, L.TOPK), np.float32)
+        L.check(self._lib.ai4e_engine_wait_many(self._h, t.ctypes.data_as(C.c_void_p), t.size,
+                                                idx.ctypes.data_as(C.c_void_p), prob.ctypes.data_as(C.c_void_p)))
+        return idx, prob
+
     def submit_jpeg(self, data: bytes, tag: int = 0) -> int:
         """one baseline JPEG (bytes) -> ticket.  The Huffman decode runs on this thread with the GIL
         released; the GPU reconstructs the pixels (bit-identical to Pillow) in front of the model."""

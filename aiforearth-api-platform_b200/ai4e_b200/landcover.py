@@ -24,6 +24,12 @@ def classify_tile(engine, tile_u8_hwc: np.ndarray, chip: int = 256):
     if a.dtype != np.uint8 or a.ndim != 3:
         raise ValueError("expected a uint8 [H, W, bands] tile")
     gh, gw = a.shape[0] // chip, a.shape[1] // chip
+    if hasattr(engine, "submit_tile"):  # one C call for the whole chip grid, one for the results
+        tickets = engine.submit_tile(a, chip)
+        engine.flush()
+        idx, prob = engine.wait_many(tickets)
+        idx, prob = idx.reshape(gh, gw, 5), prob.reshape(gh, gw, 5)
+        return idx[:, :, 0].copy(), idx, prob
     tickets = [(rc, engine.submit(v)) for rc, v in chip_views(a, chip)]
     engine.flush()
     idx = np.empty((gh, gw, 5), np.int32)

@@ -1090,6 +1090,65 @@ int ai4e_pool_destroy(ai4e_pool* p) {
 
 // ticket = replica index in the top byte | replica-local ticket.  Routing: the healthy replica
 // with the shortest queue, round-robin among equals (the reference: Istio ROUND_ROBIN).
+// A tile cut into chip x chip chips (row-major over the chip grid), every chip submitted from C:
+// the strided copies into the pinned slots and the ticket bookkeeping without a Python round trip
+// per chip (SURVEY 8(f) row 3 for the land-cover case: tile -> chips -> classify).
+int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
+                            int chip, uint64_t* out_tickets, int capacity, int* out_count) {
+  AI4E_REQUIRE(e && h_tile && out_tickets && out_count, "submit_tile: null pointer");
+  AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
+  if (row_stride <= 0) row_stride = tile_w * c;
+  const int gh = tile_h / chip, gw = tile_w / chip;
+  AI4E_REQUIRE(capacity >= gh * gw, "submit_tile: %d tickets needed, room for %d", gh * gw, capacity);
+  // The cost of a submit is the strided copy of the chip into its pinned slot (256 KB for a
+  // 256 x 256 x 4 chip: one thread moves ~300 tiles/s of 64 chips and the GPU waits), so the chips are
+  // dealt to a few threads; ai4e_engine_submit is thread-safe and a batch launches only when all of
+  // its copies have landed.
+  const int total = gh * gw;
+  const int n_threads = std::max(1, std::min({8, total / 4, (int)std::thread::hardware_concurrency()}));
+  std::vector<int> rcs(n_threads, AI4E_OK);
+  std::vector<std::string> msgs(n_threads);
+  auto work = [&](int t) {
+    for (int i = t; i < total; i += n_threads) {
+      const int r = i / gw, q = i - r * gw;
+      const uint8_t* src = h_tile + (size_t)r * chip * row_stride + (size_t)q * chip * c;
+      const int rc = ai4e_engine_submit(e, src, chip, chip, c, row_stride, 0, &out_tickets[i]);
+      if (rc) { rcs[t] = rc; msgs[t] = ai4e_last_error(); return; }  // the message is thread-local: carry it over
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < n_threads; ++t) pool.emplace_back(work, t);
+  work(0);
+  for (auto& th : pool) th.join();
+  *out_count = total;
+  for (int t = 0; t < n_threads; ++t)
+    if (rcs[t]) { set_last_error("%s", msgs[t].c_str()); *out_count = 0; return rcs[t]; }
+  return AI4E_OK;
+}
+
+// results of `n` tickets in order: idx [n][5], prob [n][5]
+int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5) {
+  AI4E_REQUIRE(e && tickets && top_idx5 && top_prob5 && n >= 0, "wait_many: bad arguments");
+  for (int i = 0; i < n; ++i) {
+    int rc = ai4e_engine_wait(e, tickets[i], top_idx5 + (size_t)i * AI4E_TOPK, top_prob5 + (size_t)i * AI4E_TOPK, nullptr);
+    if (rc) return rc;
+  }
+  return AI4E_OK;
+}
+
+static int pool_pick(ai4e_pool* p);
+
+int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
+  AI4E_REQUIRE(p && out_ticket, "pool_submit_jpeg: null pointer");
+  const int best = pool_pick(p);
+  if (best < 0) { set_last_error("pool_submit_jpeg: no healthy replica"); return AI4E_ERR_STATE; }
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit_jpeg(p->engines[best], jpeg, len, tag, &t);
+  if (rc) return rc;
+  *out_ticket = ((uint64_t)best << 56) | (t & ((1ull << 56) - 1));
+  return AI4E_OK;
+}
+
 int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
                      uint64_t* out_ticket) {
   AI4E_REQUIRE(p && out_ticket, "pool_submit: null pointer");
@@ -1114,6 +1173,26 @@ int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, in
   if (rc) return rc;
   *out_ticket = ((uint64_t)best << 56) | (t & ((1ull << 56) - 1));
   return AI4E_OK;
+}
+
+// healthy replica with the shortest queue, round-robin among equals (-1: none)
+static int pool_pick(ai4e_pool* p) {
+  const size_t n = p->engines.size();
+  const uint64_t start = p->rr.fetch_add(1);
+  int best = -1;
+  uint64_t best_depth = ~0ull;
+  for (size_t k = 0; k < n; ++k) {
+    const size_t i = (start + k) % n;
+    ai4e_engine* e = p->engines[i];
+    if (!e->healthy.load()) continue;
+    uint64_t depth;
+    {
+      std::lock_guard<std::mutex> lk(e->mu);
+      depth = e->next_ticket - e->done_upto;
+    }
+    if (depth < best_depth) { best_depth = depth; best = (int)i; }
+  }
+  return best;
 }
 
 int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {

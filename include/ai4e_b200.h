@@ -265,6 +265,17 @@ AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, i
  * the callback at APIs/1.0/base-py/ai4e_service.py:203. */
 AI4E_API int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag,
                                      uint64_t* out_ticket);
+/* A tile cut into chip x chip chips (row-major over the chip grid; the remainder at the right /
+ * bottom is ignored), each submitted as by ai4e_engine_submit with the tile's row stride, in one
+ * call: tile -> chips -> classify of the land-cover case (BASELINE.json configs[3]; the reference
+ * chains such stages through AddPipelineTask, Common/task_management/distributed_api_task.py:67-100,
+ * one HTTP hop per stage).  out_tickets: one per chip, `capacity` >= (tile_h/chip)*(tile_w/chip). */
+AI4E_API int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c,
+                                     int row_stride, int chip, uint64_t* out_tickets, int capacity,
+                                     int* out_count);
+/* ai4e_engine_wait for n tickets: top_idx5 / top_prob5 are [n][5]. */
+AI4E_API int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_t* top_idx5,
+                                   float* top_prob5);
 AI4E_API int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                      float* logits_or_null);
 AI4E_API int ai4e_engine_flush(ai4e_engine* e);
@@ -292,6 +303,8 @@ AI4E_API int ai4e_pool_create(const int* devices, int n_devices, const ai4e_mode
 AI4E_API int ai4e_pool_destroy(ai4e_pool* p);
 AI4E_API int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride,
                      uint64_t tag, uint64_t* out_ticket);
+AI4E_API int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag,
+                                   uint64_t* out_ticket);
 AI4E_API int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                    float* logits_or_null);
 AI4E_API int ai4e_pool_flush(ai4e_pool* p);

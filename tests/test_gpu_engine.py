@@ -188,6 +188,18 @@ def test_landcover_tile_pipeline():
         assert cls.shape == (2, 3) and idx.shape == (2, 3, 5)
         assert np.array_equal(idx.reshape(6, 5), g["top5_idx"][:6])
         assert np.allclose(prob.reshape(6, 5), g["top5_prob"][:6], atol=2e-4, rtol=3e-2)
+        # the one-call tile submit (C loop over the chip grid) and the per-chip Python submits agree
+        from ai4e_b200.landcover import chip_views
+        tickets = [e.submit(v) for _, v in chip_views(tile, 256)]
+        e.flush()
+        per_chip = [e.wait(t) for t in tickets]
+        assert np.array_equal(np.stack([p[0] for p in per_chip]), idx.reshape(6, 5))
+        assert np.array_equal(np.stack([p[1] for p in per_chip]), prob.reshape(6, 5))
+        # a view into a larger tile (row stride > width * channels) and a ragged remainder
+        big = np.zeros((600, 900, 4), np.uint8)
+        big[10:522, 20:788] = tile
+        cls2, idx2, _ = classify_tile(e, big[10:10 + 512 + 100, 20:20 + 768 + 50])
+        assert cls2.shape == (2, 3) and np.array_equal(idx2, idx)
 
 
 def test_async_endpoint_drives_the_engine():
