@@ -226,6 +226,16 @@ class Pool(_Base):
                                            a.strides[0], tag, C.byref(t)))
         return t.value
 
+    def submit_jpeg(self, data: bytes, tag: int = 0) -> int:
+        """one baseline JPEG -> ticket, routed to the least-loaded replica (see Engine.submit_jpeg)."""
+        buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+        t = C.c_uint64()
+        L.check(self._lib.ai4e_pool_submit_jpeg(self._h, buf, len(data), tag, C.byref(t)))
+        return t.value
+
+    def classify_jpeg(self, data: bytes, want_logits: bool = False):
+        return self.wait(self.submit_jpeg(data), want_logits)
+
     def wait(self, ticket: int, want_logits: bool = False):
         idx, prob = self._results(1)
         logits = np.empty((self.num_classes,), np.float32) if want_logits else None
