@@ -365,6 +365,15 @@ __device__ __forceinline__ void tmem_wait_ld_pin(uint32_t (&v)[32]) {
       :
       : "memory");
 }
+// K1's arithmetic, shared with the JPEG kernel that writes normalised pixels directly:
+__device__ __forceinline__ uint16_t norm_to_bf16(float v, float mean, float stdv) {
+  // three separately rounded IEEE operations, exactly as the oracle
+  float x = __fdiv_rn(v, 255.0f);
+  x = __fsub_rn(x, mean);
+  x = __fdiv_rn(x, stdv);
+  return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
+
 // relu on two packed bf16 values
 __device__ __forceinline__ uint32_t relu_bf16x2(uint32_t a) {
   uint32_t d;

@@ -176,14 +176,25 @@ void free_ctx(BatchCtx& c) {
 // preprocess + every layer, enqueued on `stream`.  Caller holds e->launch_mu.
 int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batch, int src_h, int src_w,
                     int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream,
-                    cudaEvent_t* marks = nullptr) {
+                    cudaEvent_t* marks = nullptr, const BatchCtx* jpeg = nullptr) {
   const ai4e_model_desc& m = eng->desc;
   int mark = 0;
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   const bool resize = src_h != m.in_h || src_w != m.in_w;
-  int rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, 0, resize ? m.in_h : 0,
-                             resize ? m.in_w : 0, m.in_h, m.in_w, m.mean, m.std, AI4E_LAYOUT_NHWC,
-                             m.in_c_pad, e->bufs[0], stream);
+  int rc = AI4E_OK;
+  if (jpeg && !resize && m.in_c == 3 && m.in_c_pad == 4) {
+    // K0 fused into K1: the JPEG colour kernel writes the normalised bf16 NHWC4 pixels itself
+    const float ms[6] = {m.mean[0], m.mean[1], m.mean[2], m.std[0], m.std[1], m.std[2]};
+    rc = jpeg_reconstruct(jpeg->d_rec, batch, &jpeg->jinfo, jpeg->d_planes, (uint8_t*)e->bufs[0], stream, ms);
+  } else {
+    if (jpeg) {  // other sizes: pixels first, then K1's resize + centre crop
+      rc = jpeg_reconstruct(jpeg->d_rec, batch, &jpeg->jinfo, jpeg->d_planes, const_cast<uint8_t*>(d_images), stream);
+      if (rc) return rc;
+    }
+    rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, 0, resize ? m.in_h : 0,
+                           resize ? m.in_w : 0, m.in_h, m.in_w, m.mean, m.std, AI4E_LAYOUT_NHWC,
+                           m.in_c_pad, e->bufs[0], stream);
+  }
   if (rc < 0) return rc;
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   for (LayerRt& L : e->layers) {
@@ -264,8 +275,6 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
       c.d_planes_bytes = need_planes;
     }
     AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_rec, c.h_in, rec_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
-    int rcj = jpeg_reconstruct(c.d_rec, c.count, &c.jinfo, c.d_planes, c.d_in, c.stream);
-    if (rcj) return rcj;
   } else {
     AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
   }
@@ -275,7 +284,8 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
     int rc = lane_begin(e, c.stream, &ln);
     if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_start, c.stream));
-    rc = forward_enqueue(e, ln, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream);
+    rc = forward_enqueue(e, ln, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream, nullptr,
+                         c.kind != 0 ? &c : nullptr);
     if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_fwd, c.stream));
     rc = lane_done(ln, c.stream);

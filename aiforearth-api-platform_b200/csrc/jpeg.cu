@@ -442,9 +442,14 @@ __device__ __forceinline__ int jpeg_sample(const uint8_t* __restrict__ pl, const
   return (3 * cur + (3 * r0[cx - 1] + r1[cx - 1]) + 8) >> 4;
 }
 
-// one thread = one pixel: upsample chroma, YCbCr -> RGB (jdcolor.c, SCALEBITS 16), write HWC
+struct JpegNorm { float mean[3], stdv[3]; };
+
+// one thread = one pixel: upsample chroma, YCbCr -> RGB (jdcolor.c, SCALEBITS 16); writes uint8 HWC,
+// or (kNormalize) K1's output directly: (v/255 - mean)/std as bf16 NHWC with a zero 4th channel
+template <bool kNormalize>
 __global__ void __launch_bounds__(256)
-jpeg_color_kernel(const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb, const JpegGeom g, int batch) {
+jpeg_color_kernel(const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb, const JpegGeom g, int batch,
+                  const JpegNorm nm) {
   const long long hw = (long long)g.width * g.height;
   const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (idx >= hw * batch) return;
@@ -462,8 +467,14 @@ jpeg_color_kernel(const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb,
     gg = yy + ((-22554 * cb + 32768 + -46802 * cr) >> 16);           // FIX(0.34414), FIX(0.71414)
     r = min(max(r, 0), 255); gg = min(max(gg, 0), 255); b = min(max(b, 0), 255);
   }
-  uint8_t* o = rgb + idx * 3;
-  o[0] = (uint8_t)r; o[1] = (uint8_t)gg; o[2] = (uint8_t)b;
+  if constexpr (kNormalize) {
+    const uint32_t c0 = norm_to_bf16((float)r, nm.mean[0], nm.stdv[0]), c1 = norm_to_bf16((float)gg, nm.mean[1], nm.stdv[1]);
+    const uint32_t c2 = norm_to_bf16((float)b, nm.mean[2], nm.stdv[2]);
+    reinterpret_cast<uint2*>(rgb)[idx] = make_uint2(c0 | (c1 << 16), c2);
+  } else {
+    uint8_t* o = rgb + idx * 3;
+    o[0] = (uint8_t)r; o[1] = (uint8_t)gg; o[2] = (uint8_t)b;
+  }
 }
 
 static void make_geom(const ai4e_jpeg_info& in, JpegGeom* g) {
@@ -483,8 +494,10 @@ static void make_geom(const ai4e_jpeg_info& in, JpegGeom* g) {
   g->plane_bytes = in.plane_bytes;
 }
 
+// `norm_mean_std` == nullptr: d_out is uint8 [batch][H][W][3]; else 6 floats (mean[3], std[3]) and d_out
+// is what K1 would have produced from those pixels: bf16 [batch][H][W][4], 4th channel zero
 int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* info, uint8_t* d_scratch, uint8_t* d_rgb,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, const float* norm_mean_std) {
   AI4E_REQUIRE(d_records && info && d_scratch && d_rgb && batch > 0, "jpeg_reconstruct: bad arguments");
   AI4E_REQUIRE((info->components == 1 || info->components == 3) && info->width > 0 && info->height > 0 &&
                info->record_int16 > 0 && info->plane_bytes > 0, "jpeg_reconstruct: geometry not filled in (call ai4e_jpeg_entropy_decode)");
@@ -494,7 +507,13 @@ int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* 
   jpeg_idct_kernel<<<(unsigned)((blocks + 127) / 128), 128, 0, stream>>>(d_records, d_scratch, g, batch);
   AI4E_CUDA_TRY(cudaGetLastError());
   const long long px = (long long)batch * info->width * info->height;
-  jpeg_color_kernel<<<(unsigned)((px + 255) / 256), 256, 0, stream>>>(d_scratch, d_rgb, g, batch);
+  JpegNorm nm{};
+  if (norm_mean_std) {
+    for (int i = 0; i < 3; ++i) { nm.mean[i] = norm_mean_std[i]; nm.stdv[i] = norm_mean_std[3 + i]; }
+    jpeg_color_kernel<true><<<(unsigned)((px + 255) / 256), 256, 0, stream>>>(d_scratch, d_rgb, g, batch, nm);
+  } else {
+    jpeg_color_kernel<false><<<(unsigned)((px + 255) / 256), 256, 0, stream>>>(d_scratch, d_rgb, g, batch, nm);
+  }
   AI4E_CUDA_TRY(cudaGetLastError());
   return AI4E_OK;
 }

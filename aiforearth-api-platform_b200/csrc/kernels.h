@@ -19,7 +19,7 @@ int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int
 // ---- K0 baseline JPEG (jpeg.cu): host headers + entropy decode, device IDCT / upsampling / colour
 int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_t capacity_int16, ai4e_jpeg_info* out);
 int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry, uint8_t* d_scratch,
-                     uint8_t* d_rgb_hwc, cudaStream_t stream);
+                     uint8_t* d_out, cudaStream_t stream, const float* norm_mean_std = nullptr);
 
 // ---- direct convolution on CUDA cores (conv_direct.cu)
 int launch_conv_direct(const void* in, int N, int H, int W, int Cin, const void* weight,

@@ -39,13 +39,6 @@ constexpr int kPixPerThread = 16;
 constexpr int kLutThreads = 256;
 constexpr int kChunkPix = kPixPerThread * kLutThreads;  // 4096
 
-__device__ __forceinline__ uint16_t norm_to_bf16(float v, float mean, float stdv) {
-  // three separately rounded IEEE operations, exactly as the oracle
-  float x = __fdiv_rn(v, 255.0f);
-  x = __fsub_rn(x, mean);
-  x = __fdiv_rn(x, stdv);
-  return __bfloat16_as_ushort(__float2bfloat16_rn(x));
-}
 
 // Shared-memory budget of the streaming kernel: the look-up table is replicated per lane
 // (entry (c, v) for lane l lives in word (c * 256 + v) * 32 + l, i.e. always in bank l), so the
