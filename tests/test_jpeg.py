@@ -168,3 +168,24 @@ def test_engine_submit_jpeg_equals_submit_of_decoded_pixels():
             e.submit_jpeg(buf.getvalue())
         e.flush()
         assert e.stats()["images"] == before and e.stats()["healthy"]
+
+
+@pytest.mark.gpu
+def test_pool_submit_jpeg_routes_like_submit():
+    from tests import util
+    from ai4e_b200.engine import Pool
+    PIL = pytest.importorskip("PIL.Image")
+    g, imgs = util.load_golden("resnet18")
+    jpegs = []
+    for img in imgs[:8]:
+        buf = io.BytesIO()
+        PIL.fromarray(img).save(buf, format="JPEG", quality=93, subsampling=2)
+        jpegs.append(buf.getvalue())
+    decoded = [np.asarray(PIL.open(io.BytesIO(d)).convert("RGB")) for d in jpegs]
+    with Pool(util.program_for("resnet18"), devices=[0, 0], max_batch=4, max_wait_us=300) as p:
+        want = [p.classify(d, want_logits=True) for d in decoded]
+        tickets = [p.submit_jpeg(d) for d in jpegs * 2]
+        got = [p.wait(t, want_logits=True) for t in tickets]
+        for k, (gi, gp, gl) in enumerate(got):
+            assert np.array_equal(gi, want[k % 8][0]) and np.array_equal(gl, want[k % 8][2])
+        assert all(s["images"] > 0 for s in p.stats())
