@@ -669,9 +669,10 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
 
   }  // lanes
 
-  // ---- staging: images up to 1.5x the model input area (covers a 256 -> 224 resize+crop)
+  // ---- staging: images up to 2x the model input's bytes: covers a 256 -> 224 resize+crop (1.31x)
+  // and the int16 coefficient record of a 4:4:4 JPEG of the input size (2x + tables)
   const size_t in_bytes = (size_t)desc->in_h * desc->in_w * desc->in_c;
-  size_t slot = in_bytes + in_bytes / 2;
+  size_t slot = 2 * in_bytes + 4096;
   if (const char* s = getenv("AI4E_B200_MAX_SRC_BYTES")) slot = std::max(in_bytes, (size_t)strtoull(s, nullptr, 10));
   e->slot_bytes = (slot + 255) & ~(size_t)255;
   int rc = alloc_ctx(e, e->sync_ctx);

@@ -141,7 +141,7 @@ def test_engine_submit_jpeg_equals_submit_of_decoded_pixels():
         buf = io.BytesIO()
         PIL.fromarray(img).save(buf, format="JPEG", quality=80 + 3 * i, subsampling=2)
         cases.append(buf.getvalue())
-    for i, (hw, sub) in enumerate((((224, 224), 1), ((200, 256), 2), ((200, 256), 2))):  # other sampling / size
+    for i, (hw, sub) in enumerate((((224, 224), 1), ((200, 256), 2), ((200, 256), 2), ((224, 224), 0))):  # other sampling / size
         buf = io.BytesIO()
         PIL.fromarray(imgs[i]).resize((hw[1], hw[0])).save(buf, format="JPEG", quality=88, subsampling=sub)
         cases.append(buf.getvalue())
