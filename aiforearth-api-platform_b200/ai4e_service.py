@@ -199,6 +199,34 @@ class APIService():
     def health_check(self):
         return 'Health check OK'
 
+    # ------------------------------------------------------------------ autoscaling signals
+    def attach_engine(self, engine, route=True):
+        """the B200 engine (or pool) whose queue depth and latency `metrics()` should report; also
+        serves `metrics()` as JSON at `{prefix}/metrics` (call at start-up, before the first request;
+        the reference has no such route, so it only exists once this is called)."""
+        self._engine = engine
+        if route and not getattr(self, '_metrics_routed', False):
+            self.app.add_url_rule(self.api_prefix + '/metrics', view_func=lambda: json.dumps(self.metrics()),
+                                  methods=['GET'], endpoint='ai4e_metrics')
+            self._metrics_routed = True
+
+    def metrics(self):
+        """In-flight requests per endpoint under the name the platform's HPA consumes,
+        `CURRENT_REQUESTS/{cluster}{prefix}{path}` (ProcessManager/RequestReporter/
+        CurrentProcessingUpsert.cs:102-104, APIs/Charts/templates/appinsights-metric.yaml:7), plus,
+        when an engine is attached, what the reference cannot see: queue depth, batch sizes and
+        task latency of the replica(s)."""
+        with self._counts_guard:
+            counts = dict(self.func_request_counts)
+        out = {'CURRENT_REQUESTS/%s%s%s' % (service_cluster, self.api_prefix, path): n for path, n in counts.items()}
+        engine = getattr(self, '_engine', None)
+        if engine is not None:
+            stats = engine.stats()
+            for i, st in enumerate(stats if isinstance(stats, list) else [stats]):
+                for key in ('queue_depth', 'images', 'batches', 'lat_ms_p50', 'lat_ms_p99', 'healthy'):
+                    out['ENGINE/%s/replica%d/%s' % (service_cluster, i, key)] = st[key]
+        return out
+
     def api_func(self, is_async, api_path, methods, request_processing_function, maximum_concurrent_requests,
                  content_types=None, content_max_length=None, trace_name=None, *args, **kwargs):
         def register(func):

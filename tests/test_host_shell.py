@@ -249,3 +249,35 @@ def test_worker_pool_runs_many_tasks_concurrently():
             break
         time.sleep(0.01)
     assert svc.func_request_counts["/c"] == 0
+
+
+def test_metrics_endpoint_uses_the_platform_metric_names(monkeypatch):
+    """in-flight requests under the name the HPA consumes
+    (CURRENT_REQUESTS/{cluster}{prefix}{path}), counted while a request is being served, plus the
+    attached engine's queue depth and latency."""
+    import json
+    monkeypatch.setenv("API_PREFIX", "/v1/org")
+    from ai4e_service import APIService
+    app = _flask()("m")
+    svc = APIService(app, type("L", (), {"tracer": None, "log_exception": lambda *a, **k: None})())
+    seen = {}
+
+    @svc.api_sync_func(api_path="/classify", methods=["POST"], maximum_concurrent_requests=4)
+    def classify(*a, **k):
+        seen.update(svc.metrics())  # taken while this request is in flight
+        return "ok"
+
+    class FakeEngine:
+        def stats(self):
+            return {"queue_depth": 7, "images": 100, "batches": 3, "lat_ms_p50": 1.5, "lat_ms_p99": 2.5, "healthy": 1}
+
+    svc.attach_engine(FakeEngine())  # also adds the /metrics route: before the first request
+    c = app.test_client()
+    assert c.post("/v1/org/classify", data=b"x").get_data(as_text=True) == "ok"
+    import ai4e_service
+    name = "CURRENT_REQUESTS/%s/v1/org/classify" % ai4e_service.service_cluster
+    assert seen[name] == 1
+    m = json.loads(c.get("/v1/org/metrics").get_data(as_text=True))
+    assert m[name] == 0
+    assert m["ENGINE/%s/replica0/queue_depth" % ai4e_service.service_cluster] == 7
+    assert m["ENGINE/%s/replica0/lat_ms_p99" % ai4e_service.service_cluster] == 2.5
