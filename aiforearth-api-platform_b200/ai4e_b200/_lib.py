@@ -70,6 +70,7 @@ SIGNATURES = {
     "ai4e_last_error": (C.c_char_p, []),
     "ai4e_device_count": (_i, [C.POINTER(C.c_int)]),
     "ai4e_preprocess": (_i, [_vp, _i, _i, _i, _i, _i64, _i, _i, _i, _i, _i, _fp, _fp, _i, _i, _vp, _vp]),
+    "ai4e_preprocess_tile": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _fp, _fp, _i, _i, _vp, _vp]),
     "ai4e_conv_layer": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp, _i, _vp]),
     "ai4e_jpeg_entropy_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(JpegInfo)]),
     "ai4e_jpeg_reconstruct": (_i, [_vp, _i, C.POINTER(JpegInfo), _vp, _vp, _vp]),
@@ -97,6 +98,16 @@ SIGNATURES = {
     "ai4e_engine_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
     "ai4e_engine_wait_many": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ai4e_pool_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),
+    "ai4e_engine_submit_many": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
+    "ai4e_engine_poll": (_i, [_vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]),
+    "ai4e_engine_wait_for": (_i, [_vp, _u64, _i64, _vp, _vp, _vp]),
+    "ai4e_engine_debug_inject_fault": (_i, [_vp, _i]),
+    "ai4e_pool_submit_many": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
+    "ai4e_pool_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
+    "ai4e_pool_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
+    "ai4e_pool_wait_many": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "ai4e_pool_poll": (_i, [_vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]),
+    "ai4e_pool_wait_for": (_i, [_vp, _u64, _i64, _vp, _vp, _vp]),
     "ai4e_pool_flush": (_i, [_vp]),
     "ai4e_pool_size": (_i, [_vp]),
     "ai4e_pool_engine": (_i, [_vp, _i, C.POINTER(_vp)]),

@@ -10,27 +10,274 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import threading
 
 import numpy as np
 
 from . import _lib as L
 from .models import Program
 
+_REAPER_GUARD = threading.Lock()
+
 
 def _u8_hwc(image) -> np.ndarray:
     a = np.asarray(image)
     if a.dtype != np.uint8 or a.ndim != 3:
         raise ValueError(f"expected a uint8 HWC image, got dtype {a.dtype} shape {a.shape}")
-    if a.strides[2] != 1 or a.strides[1] != a.shape[2]:
+    # dense pixels and rows that go FORWARD in memory by at least a row; anything else (a flipped or
+    # transposed view) is copied - the C side reads rows at +row_stride
+    if a.strides[2] != 1 or a.strides[1] != a.shape[2] or a.strides[0] < a.shape[1] * a.shape[2]:
         a = np.ascontiguousarray(a)
     return a
 
 
+def _vp(a: np.ndarray):
+    return C.c_void_p(a.ctypes.data)
+
+
+class Pending:
+    """Result of `classify_later`: resolved by the engine's reaper thread, never by a thread blocked
+    per task.  `APIService` understands it: a task function that returns a Pending keeps its request
+    counted as in flight until the result (and the `then` callback) is through, and an error in
+    either marks the task failed exactly like an exception raised by the function itself."""
+
+    __slots__ = ("ticket", "idx", "prob", "error", "_then", "_done", "_watchers", "_lock")
+
+    def __init__(self, then=None):
+        self.ticket = None
+        self.idx = self.prob = self.error = None
+        self._then = then
+        self._done = threading.Event()
+        self._watchers = []
+        self._lock = threading.Lock()
+
+    def done(self) -> bool:
+        return self._done.is_set()
+
+    def result(self, timeout=None):
+        if not self._done.wait(timeout):
+            raise TimeoutError("classify_later: no result yet")
+        if self.error is not None:
+            raise self.error
+        return self.idx, self.prob
+
+    def add_done_callback(self, fn):
+        """fn(pending) once the result and `then` are through (at once if they already are)."""
+        with self._lock:
+            if not self._done.is_set():
+                self._watchers.append(fn)
+                return
+        fn(self)
+
+    def _resolve(self, idx, prob, error):
+        self.idx, self.prob, self.error = idx, prob, error
+        if error is None and self._then is not None:
+            try:
+                self._then(idx, prob)
+            except BaseException as e:  # noqa: BLE001 - reported through the Pending, like a task function's exception
+                self.error = e
+        with self._lock:
+            self._done.set()
+            watchers, self._watchers = self._watchers, []
+        for fn in watchers:
+            try:
+                fn(self)
+            except BaseException:  # noqa: BLE001 - a watcher must not kill the reaper
+                pass
+
+
 class _Base:
+    """what Engine and Pool share: both C handles answer the same calls under two prefixes."""
     _h = None
+    _prefix = "ai4e_engine_"
+
+    def _fn(self, name):
+        return getattr(self._lib, self._prefix + name)
 
     def _results(self, n=1):
         return (np.empty((n, L.TOPK), np.int32), np.empty((n, L.TOPK), np.float32))
+
+    # ---- many images per call, completions through one queue
+    def submit_many(self, images, tags=None, notify: bool = False) -> np.ndarray:
+        """`images`: a uint8 [N,H,W,C] array or a sequence of equal-sized uint8 HWC arrays -> uint64
+        tickets [N], in ONE C call.  `tags` (uint64 [N]) come back from `poll`; with `notify` every
+        ticket is announced there when its batch has finished."""
+        if isinstance(images, np.ndarray) and images.ndim == 4:
+            a = images
+            if a.dtype != np.uint8:
+                raise ValueError("expected uint8 images")
+            if a.strides[3] != 1 or a.strides[2] != a.shape[3] or a.strides[1] < a.shape[2] * a.shape[3] or a.strides[0] <= 0:
+                a = np.ascontiguousarray(a)
+            n, h, w, c = a.shape
+            ptrs = a.ctypes.data + np.arange(n, dtype=np.uint64) * np.uint64(a.strides[0])
+            row_stride, keep = a.strides[1], a
+        else:
+            keep = [_u8_hwc(im) for im in images]
+            n = len(keep)
+            if n == 0:
+                return np.empty(0, np.uint64)
+            h, w, c = keep[0].shape
+            row_stride = keep[0].strides[0]
+            for im in keep:
+                if im.shape != (h, w, c):
+                    raise ValueError("submit_many: all images of one call must have the same size")
+                if im.strides[0] != row_stride:
+                    keep = [np.ascontiguousarray(x) for x in keep]
+                    row_stride = w * c
+                    break
+            ptrs = np.fromiter((im.__array_interface__["data"][0] for im in keep), np.uint64, n)
+        tickets = np.empty(n, np.uint64)
+        t = None if tags is None else np.ascontiguousarray(tags, np.uint64)
+        if t is not None and t.size != n:
+            raise ValueError("submit_many: one tag per image")
+        L.check(self._fn("submit_many")(self._h, _vp(ptrs), n, h, w, c, row_stride, _vp(t) if t is not None else None,
+                                        int(bool(notify)), _vp(tickets)))
+        del keep
+        return tickets
+
+    def poll(self, capacity: int = 256, timeout_s: float | None = 0.1):
+        """announced completions, oldest first -> (tickets u64 [n], tags u64 [n], status i32 [n],
+        idx i32 [n,5], prob f32 [n,5]); n may be 0 after `timeout_s` (None = wait for ever)."""
+        tk, tg = np.empty(capacity, np.uint64), np.empty(capacity, np.uint64)
+        st = np.empty(capacity, np.int32)
+        idx, prob = self._results(capacity)
+        n = C.c_int()
+        us = -1 if timeout_s is None else int(timeout_s * 1e6)
+        L.check(self._fn("poll")(self._h, capacity, us, _vp(tk), _vp(tg), _vp(st), _vp(idx), _vp(prob), C.byref(n)))
+        n = n.value
+        return tk[:n], tg[:n], st[:n], idx[:n], prob[:n]
+
+    # ---- deferred classification: no thread blocked per task
+    def classify_later(self, image, then=None) -> Pending:
+        """submit one image and return at once; `then(idx, prob)` runs on the reaper thread when the
+        micro-batch has finished.  A task function returns the Pending to `APIService`."""
+        p = Pending(then)
+        self._ensure_reaper()
+        with self._pend_lock:
+            self._pend_seq += 1
+            tag = self._pend_seq
+            self._pending[tag] = p
+        try:
+            p.ticket = int(self.submit_many([image], tags=np.array([tag], np.uint64), notify=True)[0])
+        except BaseException:
+            with self._pend_lock:
+                self._pending.pop(tag, None)
+            raise
+        return p
+
+    def classify_many_later(self, images, then=None):
+        """`classify_later` for N images in one C call; `then(i, idx, prob)` per image."""
+        imgs = images if isinstance(images, np.ndarray) else list(images)
+        n = len(imgs)
+        self._ensure_reaper()
+        pend = [Pending((lambda idx, prob, i=i: then(i, idx, prob)) if then else None) for i in range(n)]
+        with self._pend_lock:
+            tags = np.arange(self._pend_seq + 1, self._pend_seq + 1 + n, dtype=np.uint64)
+            self._pend_seq += n
+            for t, p in zip(tags.tolist(), pend):
+                self._pending[t] = p
+        try:
+            tickets = self.submit_many(imgs, tags=tags, notify=True)
+        except BaseException:
+            with self._pend_lock:
+                for t in tags.tolist():
+                    self._pending.pop(t, None)
+            raise
+        for p, t in zip(pend, tickets.tolist()):
+            p.ticket = t
+        return pend
+
+    def _ensure_reaper(self):
+        if getattr(self, "_reaper", None) is not None:
+            return
+        with _REAPER_GUARD:
+            if getattr(self, "_reaper", None) is not None:
+                return
+            self._pend_lock = threading.Lock()
+            self._pending, self._pend_seq = {}, 0
+            self._reaper_stop = False
+            self._reaper = threading.Thread(target=self._reap, daemon=True, name="ai4e-reaper")
+            self._reaper.start()
+
+    def _reap(self):
+        while not self._reaper_stop:
+            try:
+                tk, tg, st, idx, prob = self.poll(512, 0.05)
+            except Exception:  # noqa: BLE001 - the handle went away under us: stop
+                return
+            if not len(tk):
+                continue
+            with self._pend_lock:
+                ps = [self._pending.pop(t, None) for t in tg.tolist()]
+            for i, p in enumerate(ps):
+                if p is None:
+                    continue
+                if st[i] == L.OK:
+                    p._resolve(idx[i].copy(), prob[i].copy(), None)
+                else:
+                    p._resolve(None, None, L.Ai4eError(int(st[i]), "the micro-batch of this task failed on the GPU"))
+
+    def _stop_reaper(self):
+        r = getattr(self, "_reaper", None)
+        if r is not None:
+            self._reaper_stop = True
+            r.join(timeout=1.0)
+            self._reaper = None
+            with self._pend_lock:
+                left, self._pending = list(self._pending.values()), {}
+            for p in left:
+                p._resolve(None, None, L.Ai4eError(L.ERR_STATE, "engine closed before the task finished"))
+
+    def wait_many(self, tickets: np.ndarray):
+        """-> (idx [n, 5] int32, prob [n, 5] float32) for the tickets, in order."""
+        t = np.ascontiguousarray(tickets, np.uint64)
+        idx, prob = self._results(t.size)
+        L.check(self._fn("wait_many")(self._h, _vp(t), t.size, _vp(idx), _vp(prob)))
+        return idx, prob
+
+    def wait(self, ticket: int, want_logits: bool = False, timeout_s: float | None = None):
+        """blocks until the ticket's micro-batch has finished.  `timeout_s` None = the library's
+        default limit (AI4E_B200_WAIT_TIMEOUT_MS, 60 s); raises Ai4eError(ERR_TIMEOUT) when it passes."""
+        idx, prob = self._results(1)
+        logits = np.empty((self.num_classes,), np.float32) if want_logits else None
+        lp = _vp(logits) if want_logits else None
+        if timeout_s is None:
+            L.check(self._fn("wait")(self._h, ticket, _vp(idx), _vp(prob), lp))
+        else:
+            L.check(self._fn("wait_for")(self._h, ticket, int(timeout_s * 1e6), _vp(idx), _vp(prob), lp))
+        return (idx[0], prob[0], logits) if want_logits else (idx[0], prob[0])
+
+    def classify(self, image, want_logits: bool = False):
+        """submit + wait for one image: the call a user `func` makes."""
+        return self.wait(self.submit(image), want_logits)
+
+    def submit_tile(self, tile_u8_hwc: np.ndarray, chip: int = 256) -> np.ndarray:
+        """every chip x chip chip of a [H, W, C] uint8 tile (row-major over the chip grid) in one C
+        call -> uint64 tickets [gh * gw].  The tile goes to the GPU once and the preprocessing kernel
+        reads the chips in place; a Pool deals contiguous chip ranges to its replicas.  A page-locked
+        tile must stay unchanged until its tickets are done."""
+        a = np.asarray(tile_u8_hwc)
+        if a.dtype != np.uint8 or a.ndim != 3 or a.strides[2] != 1 or a.strides[1] != a.shape[2] or a.strides[0] < a.shape[1] * a.shape[2]:
+            raise ValueError("expected a uint8 [H, W, C] tile with dense pixels and forward rows")
+        gh, gw = a.shape[0] // chip, a.shape[1] // chip
+        tickets = np.empty(max(gh * gw, 1), np.uint64)
+        n = C.c_int32()
+        L.check(self._fn("submit_tile")(self._h, _vp(a), a.shape[0], a.shape[1], a.shape[2], a.strides[0], chip,
+                                        _vp(tickets), tickets.size, C.byref(n)))
+        return tickets[:n.value]
+
+    def submit_batch(self, images_u8: np.ndarray):
+        """dense [B,H,W,C] uint8 host array -> tickets (consecutive; a range for an Engine, an array
+        for a Pool).  Page-locked arrays are read in place by the H2D copy: keep them unchanged until
+        the last ticket has been waited for."""
+        a = images_u8
+        if a.dtype != np.uint8 or a.ndim != 4 or not a.flags.c_contiguous:
+            raise ValueError("expected a C-contiguous uint8 [B,H,W,C] array")
+        t = C.c_uint64()
+        L.check(self._fn("submit_batch")(self._h, _vp(a), a.shape[0], a.shape[1], a.shape[2], a.shape[3], C.byref(t)))
+        if self._prefix == "ai4e_engine_":
+            return range(t.value, t.value + a.shape[0])
+        return np.uint64(t.value) + np.arange(a.shape[0], dtype=np.uint64)
 
 
 class Engine(_Base):
@@ -91,29 +338,6 @@ class Engine(_Base):
                                              a.strides[0], tag, C.byref(t)))
         return t.value
 
-    def submit_tile(self, tile_u8_hwc: np.ndarray, chip: int = 256) -> np.ndarray:
-        """every chip x chip chip of a [H, W, C] uint8 tile (row-major over the chip grid), submitted
-        in one C call with the tile's row stride -> uint64 tickets [gh * gw]."""
-        a = np.asarray(tile_u8_hwc)
-        if a.dtype != np.uint8 or a.ndim != 3 or a.strides[2] != 1 or a.strides[1] != a.shape[2]:
-            raise ValueError("expected a uint8 [H, W, C] tile with dense pixels")
-        gh, gw = a.shape[0] // chip, a.shape[1] // chip
-        tickets = np.empty(max(gh * gw, 1), np.uint64)
-        n = C.c_int32()
-        L.check(self._lib.ai4e_engine_submit_tile(self._h, a.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1], a.shape[2],
-                                                  a.strides[0], chip, tickets.ctypes.data_as(C.c_void_p), tickets.size,
-                                                  C.byref(n)))
-        return tickets[:n.value]
-
-    def wait_many(self, tickets: np.ndarray):
-        """-> (idx [n, 5] int32, prob [n, 5] float32) for the tickets, in order."""
-        t = np.ascontiguousarray(tickets, np.uint64)
-        idx = np.empty((t.size, L.TOPK), np.int32)
-        prob = np.empty((t.size, L.TOPK), np.float32)
-        L.check(self._lib.ai4e_engine_wait_many(self._h, t.ctypes.data_as(C.c_void_p), t.size,
-                                                idx.ctypes.data_as(C.c_void_p), prob.ctypes.data_as(C.c_void_p)))
-        return idx, prob
-
     def submit_jpeg(self, data: bytes, tag: int = 0) -> int:
         """one baseline JPEG (bytes) -> ticket.  The Huffman decode runs on this thread with the GIL
         released; the GPU reconstructs the pixels (bit-identical to Pillow) in front of the model."""
@@ -126,17 +350,6 @@ class Engine(_Base):
         """blocking: submit_jpeg + wait."""
         return self.wait(self.submit_jpeg(data), want_logits)
 
-    def submit_batch(self, images_u8: np.ndarray) -> range:
-        """dense [B,H,W,C] uint8 host array -> tickets (a range).  Page-locked arrays are read in
-        place by the H2D copy: keep them unchanged until the last ticket has been waited for."""
-        a = images_u8
-        if a.dtype != np.uint8 or a.ndim != 4 or not a.flags.c_contiguous:
-            raise ValueError("expected a C-contiguous uint8 [B,H,W,C] array")
-        t = C.c_uint64()
-        L.check(self._lib.ai4e_engine_submit_batch(self._h, a.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1],
-                                                   a.shape[2], a.shape[3], C.byref(t)))
-        return range(t.value, t.value + a.shape[0])
-
     def profile_layers(self, d_images, batch: int, h: int, w: int, reps: int = 5) -> np.ndarray:
         """mean device ms of [preprocess, layer 0, layer 1, ...] on a device-resident batch."""
         n = len(self.program.layers) + 1
@@ -144,18 +357,6 @@ class Engine(_Base):
         L.check(self._lib.ai4e_engine_profile(self._h, C.c_void_p(d_images.data_ptr()), batch, h, w, reps,
                                               out.ctypes.data_as(C.POINTER(C.c_float)), n))
         return out
-
-    def wait(self, ticket: int, want_logits: bool = False):
-        idx, prob = self._results(1)
-        logits = np.empty((self.num_classes,), np.float32) if want_logits else None
-        L.check(self._lib.ai4e_engine_wait(self._h, ticket, idx.ctypes.data_as(C.c_void_p),
-                                           prob.ctypes.data_as(C.c_void_p),
-                                           logits.ctypes.data_as(C.c_void_p) if want_logits else None))
-        return (idx[0], prob[0], logits) if want_logits else (idx[0], prob[0])
-
-    def classify(self, image, want_logits: bool = False):
-        """submit + wait for one image: the call a user `func` makes."""
-        return self.wait(self.submit(image), want_logits)
 
     def flush(self):
         L.check(self._lib.ai4e_engine_flush(self._h))
@@ -176,7 +377,12 @@ class Engine(_Base):
         L.check(self._lib.ai4e_engine_read_activation(self._h, slot, out.ctypes.data_as(C.c_void_p), out.nbytes))
         return out
 
+    def inject_fault(self, n_batches: int = 1):
+        """fault drill: the next `n_batches` micro-batches fail like a sticky CUDA error (tests)."""
+        L.check(self._lib.ai4e_engine_debug_inject_fault(self._h, n_batches))
+
     def close(self):
+        self._stop_reaper()
         if self._h is not None and self._owned:
             self._lib.ai4e_engine_destroy(self._h)
         self._h = None
@@ -196,6 +402,7 @@ class Engine(_Base):
 
 class Pool(_Base):
     """N independent replicas (one per GPU) fed from one dispatcher; no collective anywhere."""
+    _prefix = "ai4e_pool_"
 
     def __init__(self, program: Program, devices=None, max_batch: int | None = None, max_wait_us: int | None = None):
         self._lib = L.load()
@@ -236,17 +443,6 @@ class Pool(_Base):
     def classify_jpeg(self, data: bytes, want_logits: bool = False):
         return self.wait(self.submit_jpeg(data), want_logits)
 
-    def wait(self, ticket: int, want_logits: bool = False):
-        idx, prob = self._results(1)
-        logits = np.empty((self.num_classes,), np.float32) if want_logits else None
-        L.check(self._lib.ai4e_pool_wait(self._h, ticket, idx.ctypes.data_as(C.c_void_p),
-                                         prob.ctypes.data_as(C.c_void_p),
-                                         logits.ctypes.data_as(C.c_void_p) if want_logits else None))
-        return (idx[0], prob[0], logits) if want_logits else (idx[0], prob[0])
-
-    def classify(self, image, want_logits: bool = False):
-        return self.wait(self.submit(image), want_logits)
-
     def flush(self):
         L.check(self._lib.ai4e_pool_flush(self._h))
 
@@ -262,6 +458,7 @@ class Pool(_Base):
         return [e.stats() for e in self.engines()]
 
     def close(self):
+        self._stop_reaper()
         if self._h is not None:
             self._lib.ai4e_pool_destroy(self._h)
         self._h = None

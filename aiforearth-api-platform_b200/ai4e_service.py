@@ -36,7 +36,10 @@ Contract kept (reference line numbers):
 Built differently underneath:
   * async tasks run on reusable worker threads instead of one new `threading.Thread` per task
     (:180-183); many workers blocked in `engine.classify` are what fills the engine's
-    micro-batches;
+    micro-batches.  A task function may instead `return engine.classify_later(image, then=...)`:
+    the worker is released at once, the engine's single reaper thread runs `then` (which calls
+    CompleteTask) when the micro-batch has finished, and the shell keeps the request counted and
+    maps a failure to FailTask until then - no thread is blocked per task;
   * in-flight counters are guarded by a lock (:148-156 is unsynchronised);
   * `kwargs['request']` is a snapshot that stays readable on the worker thread (the reference
     passes the context-bound proxy, :181);
@@ -128,15 +131,23 @@ class _TaskWorkers:
     def __init__(self, cap):
         self._cap, self._jobs = cap, queue.SimpleQueue()
         self._guard = threading.Lock()
-        self._idle = self._alive = 0
+        self._idle = self._alive = self._pending = 0
 
     def run(self, fn, args, kwargs):
+        # a job starts at once whenever a thread may still be created: an idle worker counts only if
+        # no queued job has already claimed it (two requests arriving back to back must not share one)
         with self._guard:
-            grow = self._idle == 0 and self._alive < self._cap
+            self._pending += 1
+            grow = self._idle < self._pending and self._alive < self._cap
             self._alive += grow
         self._jobs.put((fn, args, kwargs))
         if grow:
             threading.Thread(target=self._loop, daemon=True, name='ai4e-task').start()
+
+    def queued(self):
+        """jobs accepted but not yet picked up by a worker (only non-zero at the thread cap)."""
+        with self._guard:
+            return max(0, self._pending - self._idle)
 
     def _loop(self):
         while True:
@@ -145,6 +156,7 @@ class _TaskWorkers:
             fn, args, kwargs = self._jobs.get()
             with self._guard:
                 self._idle -= 1
+                self._pending -= 1
             try:
                 fn(*args, **kwargs)
             except BaseException:  # noqa: BLE001 - already logged and the task failed by the wrapper
@@ -348,8 +360,16 @@ class APIService():
     def _execute_func_with_counter(self, is_async=True, *args, **kwargs):
         func, api_path = kwargs['func'], kwargs['api_path']
         self.increment_requests(api_path)
+        deferred = False
         try:
-            return func(*args, **kwargs)
+            result = func(*args, **kwargs)
+            if is_async and hasattr(result, 'add_done_callback') and hasattr(result, 'error'):
+                # the function handed its image to the engine with `classify_later` and returned the
+                # Pending: the task is still in flight.  Its worker thread is free now; the request
+                # stays counted, and a failure is reported, when the engine's reaper resolves it.
+                deferred = True
+                result.add_done_callback(lambda pending: self._finish_deferred(pending, kwargs))
+            return result
         except HTTPException as http_error:  # the function chose its own HTTP answer
             self._log_and_fail_exeception(is_async, **kwargs)
             return http_error
@@ -358,4 +378,19 @@ class APIService():
             if not is_async:  # on a worker thread there is no response left to turn into a 500
                 abort(500)
         finally:
-            self.decrement_requests(api_path)
+            if not deferred:
+                self.decrement_requests(api_path)
+
+    def _finish_deferred(self, pending, kwargs):
+        """runs on the engine's reaper thread when a deferred task's result (and its `then`) is through."""
+        try:
+            if pending.error is not None:
+                task_id = kwargs.get('taskId')
+                try:
+                    self.log.log_exception(type(pending.error), task_id)
+                except Exception:  # noqa: BLE001 - a logger must not keep the task from being failed
+                    pass
+                if task_id:
+                    self.api_task_manager.FailTask(task_id, TASK_FAILED_STATUS)
+        finally:
+            self.decrement_requests(kwargs['api_path'])

@@ -39,6 +39,28 @@ int ai4e_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int c
   return rc < 0 ? rc : AI4E_OK;
 }
 
+int ai4e_preprocess_tile(const uint8_t* d_tile, int tile_h, int tile_w, int channels, int tile_row_stride, int chip,
+                         int first_chip, int n_chips, int resize_h, int resize_w, int out_h, int out_w,
+                         const float* h_mean, const float* h_std, int layout, int out_channels, void* d_dst_bf16,
+                         void* stream) {
+  AI4E_REQUIRE(d_tile && chip > 0 && tile_h >= chip && tile_w >= chip, "preprocess_tile: tile %d x %d smaller than a %d chip",
+               tile_h, tile_w, chip);
+  AI4E_REQUIRE(channels == 3 || channels == 4, "preprocess_tile: channels must be 3 or 4");
+  if (tile_row_stride <= 0) tile_row_stride = tile_w * channels;
+  AI4E_REQUIRE(tile_row_stride >= tile_w * channels, "preprocess_tile: row stride too small");
+  const int gh = tile_h / chip, gw = tile_w / chip;
+  AI4E_REQUIRE(first_chip >= 0 && n_chips >= 1 && first_chip + n_chips <= gh * gw,
+               "preprocess_tile: chips [%d, %d) outside the %d x %d grid", first_chip, first_chip + n_chips, gh, gw);
+  ChipGrid g;
+  g.grid_w = gw; g.first = first_chip;
+  g.row_bytes = tile_row_stride;
+  g.x_stride = (long long)chip * channels;
+  g.y_stride = (long long)chip * tile_row_stride;
+  const int rc = launch_preprocess(d_tile, n_chips, chip, chip, channels, 0, tile_row_stride, resize_h, resize_w, out_h, out_w,
+                                   h_mean, h_std, layout, out_channels, d_dst_bf16, (cudaStream_t)stream, &g);
+  return rc < 0 ? rc : AI4E_OK;
+}
+
 int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
                     const void* d_weight_krsc, const float* d_bias, int cout, int kh, int kw,
                     int stride, int pad, const void* d_residual_or_null, int relu,

@@ -6,6 +6,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -472,5 +473,21 @@ int tmap_encode_im2col_nhwc(CUtensorMap* out, const void* gaddr, int n, int h, i
 int tmap_encode_im2col(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c, const int lower[2],
                        const int upper[2], const int stride_wh[2], int channels_per_pixel,
                        int pixels_per_column, CUtensorMapSwizzle swizzle);
+
+
+// cudaFuncSetAttribute is per DEVICE: a process that drives several GPUs (ai4e_pool_*) must raise a
+// kernel's dynamic shared-memory limit once on each of them.  `done` holds one bit per device;
+// racing threads at worst repeat the (idempotent) call.
+template <typename Kernel>
+inline int ensure_dyn_smem(Kernel kernel, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  AI4E_CUDA_TRY(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(done.load(std::memory_order_acquire) & bit)) {
+    AI4E_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done.fetch_or(bit, std::memory_order_release);
+  }
+  return AI4E_OK;
+}
 
 }  // namespace ai4e

@@ -448,14 +448,8 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
 
 template <int N1>
 static int fused_launch_n1(const FusedPlan& plan, const FusedParams& prm, int grid, cudaStream_t stream) {
-  static unsigned long long attr_done = 0;  // bit per device
-  int dev = 0;
-  AI4E_CUDA_TRY(cudaGetDevice(&dev));
-  if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(bottleneck_tail_kernel<N1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       FusedCfg<N1>::kSmem));
-    attr_done |= 1ull << dev;
-  }
+  static std::atomic<unsigned long long> attr_done{0};  // bit per device
+  if (int rc = ensure_dyn_smem(bottleneck_tail_kernel<N1>, FusedCfg<N1>::kSmem, attr_done)) return rc;
   AI4E_CUDA_TRY(launch_pdl(bottleneck_tail_kernel<N1>, dim3(grid), dim3(kIgemmThreads), (size_t)FusedCfg<N1>::kSmem, stream,
                            plan.tmap_a, plan.tmap_w2, plan.tmap_w3, plan.tmap_out, plan.tmap_res, prm));
   return AI4E_OK;

@@ -792,14 +792,9 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
 template <int BN, int kMode, bool kPair = false>
 static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const IgemmParams& prm, int grid,
                            cudaStream_t stream) {
-  static unsigned long long attr_done = 0;  // bit per device
-  int dev = 0;
-  AI4E_CUDA_TRY(cudaGetDevice(&dev));
-  if (!(attr_done >> dev & 1ull)) {
-    AI4E_CUDA_TRY(cudaFuncSetAttribute(conv_igemm_kernel<BN, kMode, kPair>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       IgemmCfg<BN, kMode, kPair>::kSmemLimit));
-    attr_done |= 1ull << dev;
-  }
+  static std::atomic<unsigned long long> attr_done{0};  // bit per device
+  if (int rc = ensure_dyn_smem(conv_igemm_kernel<BN, kMode, kPair>, IgemmCfg<BN, kMode, kPair>::kSmemLimit, attr_done))
+    return rc;
   AI4E_CUDA_TRY(launch_pdl_cluster(conv_igemm_kernel<BN, kMode, kPair>, dim3(grid), dim3(kIgemmThreads),
                                    (size_t)IgemmCfg<BN, kMode, kPair>::smem_bytes(prm.residual != nullptr), stream,
                                    kPair ? 2 : 1, plan.tmap_a, tb, plan.tmap_out, plan.tmap_res, prm));

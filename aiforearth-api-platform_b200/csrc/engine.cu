@@ -32,6 +32,8 @@ using Clock = std::chrono::steady_clock;
 namespace {
 
 constexpr int kNumCtx = 4;
+constexpr int kNumTileBufs = 3;
+constexpr int kKindTile = -1;  // BatchCtx::kind of a batch whose images are chips of a device-resident tile
 constexpr uint64_t kResultRing = 1ull << 16;
 constexpr uint64_t kLogitRing = 1ull << 12;
 constexpr int kLatRing = 4096;
@@ -51,6 +53,29 @@ struct LayerRt {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, wait_ev = nullptr;
 };
 
+// A tile (or the band of chip rows one replica needs of it) resident in device memory: it crosses
+// PCIe once and K1 reads the chips in place through the chip-grid strides (K6).
+struct TileBuf {
+  uint8_t* d = nullptr;
+  size_t bytes = 0;
+  cudaEvent_t ev_ready = nullptr;  // the H2D copy of the band has finished
+  int users = 0;                   // batches that still read it (guarded by ai4e_engine::mu)
+  bool busy = false;               // being filled by a submitter
+};
+
+// One finished ticket that asked to be announced (submit_many with notify): what ai4e_*_poll returns.
+struct DoneRec {
+  uint64_t ticket, tag;
+  int32_t status;
+  int32_t idx[AI4E_TOPK];
+  float prob[AI4E_TOPK];
+};
+struct CompletionQueue {
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<DoneRec> q;
+};
+
 struct BatchCtx {
   uint8_t* h_in = nullptr;  // pinned, max_batch * slot_bytes
   uint8_t* d_in = nullptr;
@@ -68,9 +93,12 @@ struct BatchCtx {
   // JPEG batches: h_in holds entropy-decoded records of one geometry instead of pixels
   int kind = 0;                      // 0 = raw pixels; else a key of the JPEG geometry (see jpeg_kind)
   ai4e_jpeg_info jinfo{};
-  int16_t* d_rec = nullptr;          // device copy of the records, grown on demand
+  int16_t* d_rec = nullptr;          // device copy of the records (3-channel models only)
   uint8_t* d_planes = nullptr;       // component planes between the IDCT and the colour kernel
-  size_t d_rec_bytes = 0, d_planes_bytes = 0;
+  // tile batches (kind == kKindTile): chips [tile_first, tile_first + count) of the band in `tile`
+  TileBuf* tile = nullptr;
+  int tile_first = 0, tile_grid_w = 0, tile_chip = 0;
+  long long tile_row_bytes = 0;
 };
 
 }  // namespace
@@ -118,12 +146,26 @@ struct ai4e_engine {
   uint64_t next_ticket = 0, done_upto = 0;
   bool stopping = false, flush_req = false, batcher_done = false, completer_done = false;
   std::atomic<int> healthy{1};
+  std::atomic<int> inject_faults{0};          // debug hook: fail this many upcoming batches like a CUDA fault
+  std::atomic<uint64_t> n_submitted{0}, n_completed{0};  // queue depth without taking `mu` (pool routing)
   std::thread batcher, completer;
+  int wait_timeout_ms = 60000;                // ai4e_engine_wait gives up after this (AI4E_B200_WAIT_TIMEOUT_MS)
+
+  // device-resident tiles (K6)
+  TileBuf tiles[kNumTileBufs];
+  cudaStream_t copy_stream = nullptr;
+
+  // announced completions (ai4e_engine_poll); a pool points all its replicas at one shared queue
+  CompletionQueue own_cq;
+  CompletionQueue* cq = &own_cq;
+  uint64_t ticket_prefix = 0;                 // replica index << 56 inside a pool
 
   // results
   std::vector<int32_t> r_idx;
   std::vector<float> r_prob, r_logits;
   std::vector<int8_t> r_status;
+  std::vector<uint8_t> r_notify;
+  std::vector<uint64_t> r_tag;
   std::vector<Clock::time_point> r_submit;
   std::vector<float> lat_ms;
   uint64_t lat_n = 0;
@@ -132,11 +174,30 @@ struct ai4e_engine {
 
 namespace {
 
+// two JPEGs may share a launch only if their records have the same layout, component by component
+// (equal totals can hide different per-component sampling)
+bool jpeg_same_geometry(const ai4e_jpeg_info& a, const ai4e_jpeg_info& b) {
+  if (a.width != b.width || a.height != b.height || a.components != b.components || a.hmax != b.hmax ||
+      a.vmax != b.vmax || a.record_int16 != b.record_int16 || a.plane_bytes != b.plane_bytes)
+    return false;
+  for (int c = 0; c < 3; ++c)
+    if (a.h[c] != b.h[c] || a.v[c] != b.v[c] || a.blocks_w[c] != b.blocks_w[c] || a.blocks_h[c] != b.blocks_h[c] ||
+        a.comp_w[c] != b.comp_w[c] || a.comp_h[c] != b.comp_h[c] || a.coef_off[c] != b.coef_off[c])
+      return false;
+  return true;
+}
+
 int alloc_ctx(ai4e_engine* e, BatchCtx& c) {
   const size_t B = e->max_batch;
   const int K = e->desc.num_classes;
   AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_in, B * e->slot_bytes, cudaHostAllocDefault));
   AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_in, B * e->slot_bytes));
+  if (e->desc.in_c == 3) {
+    // JPEG batches: records and component planes are bounded by the staging slot (checked at submit),
+    // so they are sized once here - no cudaMalloc / cudaFree (device-wide syncs) on the batcher thread
+    AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_rec, B * e->slot_bytes));
+    AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_planes, B * e->slot_bytes));
+  }
   AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_idx, B * AI4E_TOPK * sizeof(int32_t), cudaHostAllocDefault));
   AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_prob, B * AI4E_TOPK * sizeof(float), cudaHostAllocDefault));
   AI4E_CUDA_TRY(cudaHostAlloc((void**)&c.h_logits, B * K * sizeof(float), cudaHostAllocDefault));
@@ -155,7 +216,7 @@ void free_ctx(BatchCtx& c) {
   if (c.d_in) cudaFree(c.d_in);
   if (c.d_rec) cudaFree(c.d_rec);
   if (c.d_planes) cudaFree(c.d_planes);
-  c.d_rec = nullptr; c.d_planes = nullptr; c.d_rec_bytes = c.d_planes_bytes = 0;
+  c.d_rec = nullptr; c.d_planes = nullptr;
   if (c.h_idx) cudaFreeHost(c.h_idx);
   if (c.h_prob) cudaFreeHost(c.h_prob);
   if (c.h_logits) cudaFreeHost(c.h_logits);
@@ -176,7 +237,7 @@ void free_ctx(BatchCtx& c) {
 // preprocess + every layer, enqueued on `stream`.  Caller holds e->launch_mu.
 int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batch, int src_h, int src_w,
                     int32_t* d_idx, float* d_prob, float* d_logits, cudaStream_t stream,
-                    cudaEvent_t* marks = nullptr, const BatchCtx* jpeg = nullptr) {
+                    cudaEvent_t* marks = nullptr, const BatchCtx* jpeg = nullptr, const ChipGrid* chips = nullptr) {
   const ai4e_model_desc& m = eng->desc;
   int mark = 0;
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
@@ -191,9 +252,9 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
       rc = jpeg_reconstruct(jpeg->d_rec, batch, &jpeg->jinfo, jpeg->d_planes, const_cast<uint8_t*>(d_images), stream);
       if (rc) return rc;
     }
-    rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, 0, resize ? m.in_h : 0,
+    rc = launch_preprocess(d_images, batch, src_h, src_w, m.in_c, 0, chips ? (int)chips->row_bytes : 0, resize ? m.in_h : 0,
                            resize ? m.in_w : 0, m.in_h, m.in_w, m.mean, m.std, AI4E_LAYOUT_NHWC,
-                           m.in_c_pad, e->bufs[0], stream);
+                           m.in_c_pad, e->bufs[0], stream, chips);
   }
   if (rc < 0) return rc;
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
@@ -257,24 +318,23 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
   const int K = e->desc.num_classes;
   const size_t img_bytes = (size_t)c.src_h * c.src_w * e->desc.in_c;
   const uint8_t* h_src = c.ext_src ? c.ext_src : c.h_in;  // ext_src: caller's page-locked buffer
-  if (c.kind != 0) {
+  ChipGrid grid{};
+  if (c.kind == kKindTile) {
+    grid.grid_w = c.tile_grid_w; grid.first = c.tile_first;
+    grid.row_bytes = c.tile_row_bytes;
+    grid.x_stride = (long long)c.tile_chip * e->desc.in_c;
+    grid.y_stride = (long long)c.tile_chip * c.tile_row_bytes;
+  }
+  if (c.kind > 0) {
     // K0: the slots hold entropy-decoded JPEG records (one geometry per batch): copy them, then
     // dequantise + IDCT + upsample + colour-convert straight into the pixel slots K1 reads
     const size_t rec_bytes = (size_t)c.jinfo.record_int16 * sizeof(int16_t);
-    const size_t need_rec = rec_bytes * e->max_batch, need_planes = (size_t)c.jinfo.plane_bytes * e->max_batch;
-    if (c.d_rec_bytes < need_rec) {
-      if (c.d_rec) AI4E_CUDA_TRY(cudaFree(c.d_rec));
-      c.d_rec = nullptr; c.d_rec_bytes = 0;
-      AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_rec, need_rec));
-      c.d_rec_bytes = need_rec;
-    }
-    if (c.d_planes_bytes < need_planes) {
-      if (c.d_planes) AI4E_CUDA_TRY(cudaFree(c.d_planes));
-      c.d_planes = nullptr; c.d_planes_bytes = 0;
-      AI4E_CUDA_TRY(cudaMalloc((void**)&c.d_planes, need_planes));
-      c.d_planes_bytes = need_planes;
-    }
+    AI4E_REQUIRE(c.d_rec && rec_bytes <= e->slot_bytes && (size_t)c.jinfo.plane_bytes <= e->slot_bytes,
+                 "jpeg batch exceeds the staging slot");
     AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_rec, c.h_in, rec_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
+  } else if (c.kind == kKindTile) {
+    // K6: the band is already on its way (one H2D on the copy stream); nothing is copied per chip
+    AI4E_CUDA_TRY(cudaStreamWaitEvent(c.stream, c.tile->ev_ready, 0));
   } else {
     AI4E_CUDA_TRY(cudaMemcpyAsync(c.d_in, h_src, img_bytes * c.count, cudaMemcpyHostToDevice, c.stream));
   }
@@ -284,8 +344,8 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
     int rc = lane_begin(e, c.stream, &ln);
     if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_start, c.stream));
-    rc = forward_enqueue(e, ln, c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob, c.d_logits, c.stream, nullptr,
-                         c.kind != 0 ? &c : nullptr);
+    rc = forward_enqueue(e, ln, c.kind == kKindTile ? c.tile->d : c.d_in, c.count, c.src_h, c.src_w, c.d_idx, c.d_prob,
+                         c.d_logits, c.stream, nullptr, c.kind > 0 ? &c : nullptr, c.kind == kKindTile ? &grid : nullptr);
     if (rc) return rc;
     AI4E_CUDA_TRY(cudaEventRecord(c.ev_fwd, c.stream));
     rc = lane_done(ln, c.stream);
@@ -355,8 +415,24 @@ void batcher_main(ai4e_engine* e) {
     BatchCtx* c = e->closed_q.front();
     e->closed_q.pop_front();
     lk.unlock();
-    while (c->copied.load(std::memory_order_acquire) < c->count) std::this_thread::yield();
-    c->launch_rc = e->healthy.load() ? launch_batch(e, *c, true) : AI4E_ERR_STATE;
+    // every submitter of this batch has reserved its slot; wait for the copies to land - bounded, so a
+    // submitter that never finishes (a killed thread) fails this batch instead of hanging the queue
+    const auto copy_deadline = Clock::now() + std::chrono::seconds(10);
+    bool copies_ok = true;
+    while (c->copied.load(std::memory_order_acquire) < c->count) {
+      if (Clock::now() > copy_deadline) { copies_ok = false; break; }
+      std::this_thread::yield();
+    }
+    if (!copies_ok) {
+      set_last_error("batch of %d: only %d image copies landed within 10 s", c->count, c->copied.load());
+      c->launch_rc = AI4E_ERR_TIMEOUT;
+    } else if (!e->healthy.load()) {
+      c->launch_rc = AI4E_ERR_STATE;
+    } else if (e->inject_faults.load() > 0 && e->inject_faults.fetch_sub(1) > 0) {
+      c->launch_rc = AI4E_ERR_CUDA;  // ai4e_engine_debug_inject_fault: behave as if the launch hit a sticky CUDA error
+    } else {
+      c->launch_rc = launch_batch(e, *c, true);
+    }
     lk.lock();
     e->inflight_q.push_back(c);
     e->cv_inflight.notify_one();
@@ -382,14 +458,27 @@ void completer_main(ai4e_engine* e) {
         rc = AI4E_ERR_CUDA;
       }
     }
-    if (rc != AI4E_OK) e->healthy.store(0);
+    // a CUDA fault is sticky (the context is gone): the replica stops taking work.  Anything else
+    // (bad geometry, a copy that never landed, no memory) fails this batch's tickets only.
+    if (rc == AI4E_ERR_CUDA) e->healthy.store(0);
     const auto now = Clock::now();
+    std::vector<DoneRec> announce;
     lk.lock();
     const int K = e->desc.num_classes;
     for (int i = 0; i < c->count; ++i) {
       const uint64_t t = c->first_ticket + i;
       const uint64_t r = t % kResultRing;
       e->r_status[r] = (int8_t)rc;
+      if (e->r_notify[r]) {
+        DoneRec d{};
+        d.ticket = e->ticket_prefix | t; d.tag = e->r_tag[r]; d.status = rc;
+        if (rc == AI4E_OK) {
+          memcpy(d.idx, c->h_idx + (size_t)i * AI4E_TOPK, sizeof(d.idx));
+          memcpy(d.prob, c->h_prob + (size_t)i * AI4E_TOPK, sizeof(d.prob));
+        }
+        announce.push_back(d);
+        e->r_notify[r] = 0;
+      }
       if (rc == AI4E_OK) {
         memcpy(&e->r_idx[r * AI4E_TOPK], c->h_idx + (size_t)i * AI4E_TOPK, AI4E_TOPK * sizeof(int32_t));
         memcpy(&e->r_prob[r * AI4E_TOPK], c->h_prob + (size_t)i * AI4E_TOPK, AI4E_TOPK * sizeof(float));
@@ -400,12 +489,24 @@ void completer_main(ai4e_engine* e) {
     }
     if (rc == AI4E_OK) account_batch(e, *c);
     e->done_upto = c->first_ticket + c->count;
+    e->n_completed.fetch_add((uint64_t)c->count);
+    if (c->tile) { c->tile->users -= 1; c->tile = nullptr; }
     c->count = 0;
+    c->kind = 0;
     c->ext_src = nullptr;
     c->copied.store(0);
     e->free_q.push_back(c);
     e->cv_free.notify_all();
     e->cv_done.notify_all();
+    if (!announce.empty()) {
+      lk.unlock();
+      {
+        std::lock_guard<std::mutex> ql(e->cq->mu);
+        for (const DoneRec& d : announce) e->cq->q.push_back(d);
+      }
+      e->cq->cv.notify_all();
+      lk.lock();
+    }
   }
   e->completer_done = true;
   e->cv_done.notify_all();
@@ -687,8 +788,13 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   e->r_prob.assign(kResultRing * AI4E_TOPK, 0.f);
   e->r_logits.assign(kLogitRing * K, 0.f);
   e->r_status.assign(kResultRing, 0);
+  e->r_notify.assign(kResultRing, 0);
+  e->r_tag.assign(kResultRing, 0);
   e->r_submit.assign(kResultRing, Clock::now());
   e->lat_ms.assign(kLatRing, 0.f);
+  if (const char* v = getenv("AI4E_B200_WAIT_TIMEOUT_MS")) e->wait_timeout_ms = std::max(1, atoi(v));
+  TRY_OR_FAIL(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  for (TileBuf& tb : e->tiles) TRY_OR_FAIL(cudaEventCreateWithFlags(&tb.ev_ready, cudaEventDisableTiming));
   e->batcher = std::thread(batcher_main, e);
   e->completer = std::thread(completer_main, e);
   *out = e;
@@ -739,6 +845,11 @@ int ai4e_engine_destroy(ai4e_engine* e) {
     }
     if (ln.side_stream) cudaStreamDestroy(ln.side_stream);
   }
+  for (TileBuf& tb : e->tiles) {
+    if (tb.d) cudaFree(tb.d);
+    if (tb.ev_ready) cudaEventDestroy(tb.ev_ready);
+  }
+  if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
   if (e->d_blob) cudaFree(e->d_blob);
   if (e->d_stem_w) cudaFree(e->d_stem_w);
   delete e;
@@ -796,71 +907,126 @@ int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images, int batc
   return lane_done(ln, s);
 }
 
+// Reserves up to `want` consecutive slots of the open batch for images of one size and kind (0 = raw
+// pixels, > 0 = a JPEG geometry key) and hands out their tickets; closes the batch when it is full.
+// The caller copies its payload into the slots and then adds the count to ctx->copied.
+static int reserve_slots(ai4e_engine* e, const char* who, int h, int w, int kind, const ai4e_jpeg_info* jinfo, int want,
+                         const uint64_t* tags, uint64_t tag, int notify, BatchCtx** out_ctx, int* out_slot0, int* out_got,
+                         uint64_t* out_tickets) {
+  std::unique_lock<std::mutex> lk(e->mu);
+  BatchCtx* ctx = nullptr;
+  for (;;) {
+    if (e->stopping) { set_last_error("%s: engine is shutting down", who); return AI4E_ERR_STATE; }
+    if (!e->healthy.load()) { set_last_error("%s: engine on device %d is unhealthy", who, e->device); return AI4E_ERR_STATE; }
+    if (!e->open_ctx) {
+      if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
+      e->open_ctx = e->free_q.front();
+      e->free_q.pop_front();
+      e->open_ctx->count = 0;
+      e->open_ctx->copied.store(0);
+    }
+    ctx = e->open_ctx;
+    // a batch holds one image size and kind; JPEG batches additionally one record layout
+    const bool other = ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w || ctx->kind != kind ||
+                                          (kind > 0 && !jpeg_same_geometry(ctx->jinfo, *jinfo)));
+    if (other) {
+      e->closed_q.push_back(ctx);
+      e->open_ctx = nullptr;
+      e->cv_work.notify_one();
+      continue;
+    }
+    break;
+  }
+  const auto now = Clock::now();
+  if (ctx->count == 0) {
+    ctx->src_h = h; ctx->src_w = w;
+    ctx->kind = kind;
+    if (jinfo) ctx->jinfo = *jinfo;
+    ctx->tile = nullptr;
+    ctx->t_first = now;
+    ctx->first_ticket = e->next_ticket;
+  }
+  const int got = std::min(want, e->max_batch - ctx->count);
+  *out_ctx = ctx; *out_slot0 = ctx->count; *out_got = got;
+  for (int i = 0; i < got; ++i) {
+    const uint64_t t = e->next_ticket++;
+    const uint64_t r = t % kResultRing;
+    out_tickets[i] = t;
+    e->r_submit[r] = now;
+    e->r_status[r] = 1;  // pending
+    e->r_notify[r] = notify ? 1 : 0;
+    e->r_tag[r] = tags ? tags[i] : tag;
+  }
+  ctx->count += got;
+  e->n_submitted.fetch_add((uint64_t)got);
+  if (ctx->count == e->max_batch) {
+    e->closed_q.push_back(ctx);
+    e->open_ctx = nullptr;
+  }
+  e->cv_work.notify_one();
+  return AI4E_OK;
+}
+
+static inline void copy_image(uint8_t* dst, const uint8_t* src, int h, int w, int c, int row_stride) {
+  if (row_stride == w * c) {
+    memcpy(dst, src, (size_t)h * w * c);
+  } else {
+    for (int y = 0; y < h; ++y) memcpy(dst + (size_t)y * w * c, src + (size_t)y * row_stride, (size_t)w * c);
+  }
+}
+
+int ai4e_engine_submit_many(ai4e_engine* e, const uint8_t* const* h_images, int n, int h, int w, int c, int row_stride,
+                            const uint64_t* tags_or_null, int notify, uint64_t* out_tickets) {
+  AI4E_REQUIRE(e && h_images && out_tickets, "submit_many: null pointer");
+  AI4E_REQUIRE(n >= 0, "submit_many: negative count");
+  AI4E_REQUIRE(c == e->desc.in_c, "submit_many: images have %d channels, model takes %d", c, e->desc.in_c);
+  AI4E_REQUIRE(h > 0 && w > 0, "submit_many: empty image");
+  AI4E_REQUIRE(row_stride >= 0, "submit_many: negative row stride (pass a copy of a flipped view)");
+  if (row_stride == 0) row_stride = w * c;
+  AI4E_REQUIRE(row_stride >= w * c, "submit_many: row stride too small");
+  const size_t img_bytes = (size_t)h * w * c;
+  AI4E_REQUIRE(img_bytes <= e->slot_bytes, "submit_many: image of %zu bytes exceeds the staging slot (%zu)", img_bytes,
+               e->slot_bytes);
+  for (int i = 0; i < n; ++i) AI4E_REQUIRE(h_images[i], "submit_many: image %d is null", i);
+  int done = 0;
+  while (done < n) {
+    BatchCtx* ctx = nullptr;
+    int slot0 = 0, got = 0;
+    int rc = reserve_slots(e, "submit", h, w, 0, nullptr, n - done, tags_or_null ? tags_or_null + done : nullptr, 0, notify,
+                           &ctx, &slot0, &got, out_tickets + done);
+    if (rc) return rc;  // tickets handed out so far stay valid
+    for (int i = 0; i < got; ++i)
+      copy_image(ctx->h_in + (size_t)(slot0 + i) * img_bytes, h_images[done + i], h, w, c, row_stride);
+    ctx->copied.fetch_add(got, std::memory_order_release);
+    done += got;
+  }
+  return AI4E_OK;
+}
+
 int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
                        uint64_t* out_ticket) {
-  (void)tag;
   AI4E_REQUIRE(e && h_hwc && out_ticket, "submit: null pointer");
   AI4E_REQUIRE(c == e->desc.in_c, "submit: image has %d channels, model takes %d", c, e->desc.in_c);
   AI4E_REQUIRE(h > 0 && w > 0, "submit: empty image");
-  if (row_stride <= 0) row_stride = w * c;
+  AI4E_REQUIRE(row_stride >= 0, "submit: negative row stride (pass a copy of a flipped view)");
+  if (row_stride == 0) row_stride = w * c;
   AI4E_REQUIRE(row_stride >= w * c, "submit: row stride too small");
   const size_t img_bytes = (size_t)h * w * c;
   AI4E_REQUIRE(img_bytes <= e->slot_bytes, "submit: image of %zu bytes exceeds the staging slot (%zu)", img_bytes,
                e->slot_bytes);
   BatchCtx* ctx = nullptr;
-  int slot = 0;
-  {
-    std::unique_lock<std::mutex> lk(e->mu);
-    for (;;) {
-      if (e->stopping) { set_last_error("submit: engine is shutting down"); return AI4E_ERR_STATE; }
-      if (!e->healthy.load()) { set_last_error("submit: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
-      if (!e->open_ctx) {
-        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
-        e->open_ctx = e->free_q.front();
-        e->free_q.pop_front();
-        e->open_ctx->count = 0;
-        e->open_ctx->copied.store(0);
-      }
-      ctx = e->open_ctx;
-      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w || ctx->kind != 0)) {  // a batch holds one image size and kind
-        e->closed_q.push_back(ctx);
-        e->open_ctx = nullptr;
-        e->cv_work.notify_one();
-        continue;
-      }
-      break;
-    }
-    if (ctx->count == 0) {
-      ctx->src_h = h; ctx->src_w = w;
-      ctx->kind = 0;
-      ctx->t_first = Clock::now();
-      ctx->first_ticket = e->next_ticket;
-    }
-    slot = ctx->count++;
-    *out_ticket = e->next_ticket++;
-    e->r_submit[*out_ticket % kResultRing] = Clock::now();
-    e->r_status[*out_ticket % kResultRing] = 1;  // pending
-    if (ctx->count == e->max_batch) {
-      e->closed_q.push_back(ctx);
-      e->open_ctx = nullptr;
-    }
-    e->cv_work.notify_one();
-  }
-  uint8_t* dst = ctx->h_in + (size_t)slot * img_bytes;
-  if (row_stride == w * c) {
-    memcpy(dst, h_hwc, img_bytes);
-  } else {
-    for (int y = 0; y < h; ++y) memcpy(dst + (size_t)y * w * c, h_hwc + (size_t)y * row_stride, (size_t)w * c);
-  }
+  int slot = 0, got = 0;
+  int rc = reserve_slots(e, "submit", h, w, 0, nullptr, 1, nullptr, tag, 0, &ctx, &slot, &got, out_ticket);
+  if (rc) return rc;
+  copy_image(ctx->h_in + (size_t)slot * img_bytes, h_hwc, h, w, c, row_stride);
   ctx->copied.fetch_add(1, std::memory_order_release);
   return AI4E_OK;
 }
 
-// geometry key of a JPEG batch: images whose records have the same layout share a launch
+// geometry key of a JPEG batch (reserve_slots compares the complete record layout on top of it)
 static int jpeg_kind(const ai4e_jpeg_info& j) { return 1 + j.components * 64 + j.hmax * 16 + j.vmax * 4 + (j.h[0] * 2 + j.v[0]) % 4; }
 
 int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
-  (void)tag;
   AI4E_REQUIRE(e && jpeg && out_ticket, "submit_jpeg: null pointer");
   AI4E_REQUIRE(e->desc.in_c == 3, "submit_jpeg: the model takes %d channels, a JPEG decodes to 3", e->desc.in_c);
   // entropy decode on the caller's thread, into a thread-local record: nothing is reserved if it fails
@@ -870,54 +1036,17 @@ int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, u
   if (rc) return rc;
   const size_t rec_bytes = (size_t)info.record_int16 * sizeof(int16_t);
   const size_t rgb_bytes = (size_t)info.width * info.height * 3;
-  AI4E_REQUIRE(rec_bytes <= e->slot_bytes && rgb_bytes <= e->slot_bytes,
+  AI4E_REQUIRE(rec_bytes <= e->slot_bytes && rgb_bytes <= e->slot_bytes && (size_t)info.plane_bytes <= e->slot_bytes,
                "submit_jpeg: a %d x %d image needs %zu bytes of staging, the slot holds %zu (AI4E_B200_MAX_SRC_BYTES)",
                info.width, info.height, std::max(rec_bytes, rgb_bytes), e->slot_bytes);
   if (rec.size() < (size_t)info.record_int16) rec.resize((size_t)info.record_int16);
   rc = jpeg_host_decode(jpeg, len, rec.data(), rec.size(), &info);
   if (rc) return rc;
-  const int kind = jpeg_kind(info), h = info.height, w = info.width;
   BatchCtx* ctx = nullptr;
-  int slot = 0;
-  {
-    std::unique_lock<std::mutex> lk(e->mu);
-    for (;;) {
-      if (e->stopping) { set_last_error("submit_jpeg: engine is shutting down"); return AI4E_ERR_STATE; }
-      if (!e->healthy.load()) { set_last_error("submit_jpeg: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
-      if (!e->open_ctx) {
-        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
-        e->open_ctx = e->free_q.front();
-        e->free_q.pop_front();
-        e->open_ctx->count = 0;
-        e->open_ctx->copied.store(0);
-      }
-      ctx = e->open_ctx;
-      if (ctx->count > 0 && (ctx->src_h != h || ctx->src_w != w || ctx->kind != kind ||
-                             ctx->jinfo.record_int16 != info.record_int16)) {
-        e->closed_q.push_back(ctx);
-        e->open_ctx = nullptr;
-        e->cv_work.notify_one();
-        continue;
-      }
-      break;
-    }
-    if (ctx->count == 0) {
-      ctx->src_h = h; ctx->src_w = w;
-      ctx->kind = kind;
-      ctx->jinfo = info;
-      ctx->t_first = Clock::now();
-      ctx->first_ticket = e->next_ticket;
-    }
-    slot = ctx->count++;
-    *out_ticket = e->next_ticket++;
-    e->r_submit[*out_ticket % kResultRing] = Clock::now();
-    e->r_status[*out_ticket % kResultRing] = 1;  // pending
-    if (ctx->count == e->max_batch) {
-      e->closed_q.push_back(ctx);
-      e->open_ctx = nullptr;
-    }
-    e->cv_work.notify_one();
-  }
+  int slot = 0, got = 0;
+  rc = reserve_slots(e, "submit_jpeg", info.height, info.width, jpeg_kind(info), &info, 1, nullptr, tag, 0, &ctx, &slot, &got,
+                     out_ticket);
+  if (rc) return rc;
   memcpy(ctx->h_in + (size_t)slot * rec_bytes, rec.data(), rec_bytes);
   ctx->copied.fetch_add(1, std::memory_order_release);
   return AI4E_OK;
@@ -954,6 +1083,7 @@ int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count,
     ctx = e->open_ctx;
     e->open_ctx = nullptr;
     ctx->count = count; ctx->src_h = h; ctx->src_w = w; ctx->kind = 0;
+    ctx->tile = nullptr;
     ctx->t_first = Clock::now();
     ctx->first_ticket = e->next_ticket;
     ctx->ext_src = pinned ? h_images : nullptr;
@@ -963,8 +1093,11 @@ int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count,
       const uint64_t r = (e->next_ticket + i) % kResultRing;
       e->r_submit[r] = ctx->t_first;
       e->r_status[r] = 1;
+      e->r_notify[r] = 0;
+      e->r_tag[r] = 0;
     }
     e->next_ticket += count;
+    e->n_submitted.fetch_add((uint64_t)count);
     e->closed_q.push_back(ctx);
     e->cv_work.notify_one();
   }
@@ -1011,11 +1144,20 @@ int ai4e_engine_profile(ai4e_engine* e, const uint8_t* d_images, int batch, int 
   return AI4E_OK;
 }
 
-int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {
+// timeout_us < 0: wait for ever; 0: only report what is there
+int ai4e_engine_wait_for(ai4e_engine* e, uint64_t ticket, int64_t timeout_us, int32_t* top_idx5, float* top_prob5,
+                         float* logits_or_null) {
   AI4E_REQUIRE(e && top_idx5 && top_prob5, "wait: null pointer");
   std::unique_lock<std::mutex> lk(e->mu);
   AI4E_REQUIRE(ticket < e->next_ticket, "wait: unknown ticket %llu", (unsigned long long)ticket);
-  e->cv_done.wait(lk, [&] { return e->done_upto > ticket || e->completer_done; });
+  auto ready = [&] { return e->done_upto > ticket || e->completer_done; };
+  if (timeout_us < 0) {
+    e->cv_done.wait(lk, ready);
+  } else if (!e->cv_done.wait_for(lk, std::chrono::microseconds(timeout_us), ready)) {
+    set_last_error("wait: ticket %llu not finished after %lld us (%llu tickets in the queue ahead of it)",
+                   (unsigned long long)ticket, (long long)timeout_us, (unsigned long long)(ticket - e->done_upto));
+    return AI4E_ERR_TIMEOUT;
+  }
   if (e->done_upto <= ticket) { set_last_error("wait: engine shut down before ticket completed"); return AI4E_ERR_STATE; }
   AI4E_REQUIRE(e->next_ticket - ticket <= kResultRing, "wait: result of ticket %llu has been overwritten",
                (unsigned long long)ticket);
@@ -1033,6 +1175,46 @@ int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* 
   return AI4E_OK;
 }
 
+int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {
+  AI4E_REQUIRE(e, "wait: null engine");
+  return ai4e_engine_wait_for(e, ticket, (int64_t)e->wait_timeout_ms * 1000, top_idx5, top_prob5, logits_or_null);
+}
+
+// Drains up to `capacity` announced completions from `cq`, blocking up to timeout_us for the first one.
+static int poll_queue(CompletionQueue* cq, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
+                      int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n) {
+  std::unique_lock<std::mutex> lk(cq->mu);
+  if (cq->q.empty() && timeout_us != 0) {
+    if (timeout_us < 0) cq->cv.wait(lk, [&] { return !cq->q.empty(); });
+    else cq->cv.wait_for(lk, std::chrono::microseconds(timeout_us), [&] { return !cq->q.empty(); });
+  }
+  int n = 0;
+  while (n < capacity && !cq->q.empty()) {
+    const DoneRec& d = cq->q.front();
+    if (tickets) tickets[n] = d.ticket;
+    if (tags) tags[n] = d.tag;
+    if (status) status[n] = d.status;
+    if (top_idx5) memcpy(top_idx5 + (size_t)n * AI4E_TOPK, d.idx, sizeof(d.idx));
+    if (top_prob5) memcpy(top_prob5 + (size_t)n * AI4E_TOPK, d.prob, sizeof(d.prob));
+    cq->q.pop_front();
+    ++n;
+  }
+  *out_n = n;
+  return AI4E_OK;
+}
+
+int ai4e_engine_poll(ai4e_engine* e, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags, int32_t* status,
+                     int32_t* top_idx5, float* top_prob5, int* out_n) {
+  AI4E_REQUIRE(e && out_n && capacity >= 0, "poll: bad arguments");
+  return poll_queue(e->cq, capacity, timeout_us, tickets, tags, status, top_idx5, top_prob5, out_n);
+}
+
+int ai4e_engine_debug_inject_fault(ai4e_engine* e, int n_batches) {
+  AI4E_REQUIRE(e && n_batches >= 0, "inject_fault: bad arguments");
+  e->inject_faults.store(n_batches);
+  return AI4E_OK;
+}
+
 int ai4e_engine_flush(ai4e_engine* e) {
   AI4E_REQUIRE(e, "flush: null engine");
   std::unique_lock<std::mutex> lk(e->mu);
@@ -1047,7 +1229,7 @@ int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out) {
   AI4E_REQUIRE(e && out, "stats: null pointer");
   std::lock_guard<std::mutex> lk(e->mu);
   *out = e->st;
-  out->queue_depth = e->next_ticket - e->done_upto;
+  out->queue_depth = e->next_ticket - e->done_upto;  // == n_submitted - n_completed
   out->healthy = e->healthy.load();
   out->launches_per_forward = e->launches;
   const uint64_t n = std::min<uint64_t>(e->lat_n, kLatRing);
@@ -1072,68 +1254,123 @@ int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t b
   return AI4E_OK;
 }
 
-// ---------------------------------------------------------------------------------------- pool
-struct ai4e_pool {
-  std::vector<ai4e_engine*> engines;
-  std::atomic<uint64_t> rr{0};
-};
+// ---------------------------------------------------------------------------------------- tiles (K6)
+// Chips [first_chip, first_chip + n_chips) of a tile cut into chip x chip squares (row-major over the
+// chip grid).  The band of chip rows that holds them crosses PCIe ONCE (one 2-D copy on the copy
+// stream into a device tile buffer); the batches made from it carry only (first chip, count) and K1
+// reads every chip in place through the chip-grid strides - no per-chip host copy, no gather kernel.
+static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
+                             int chip, int first_chip, int n_chips, uint64_t* out_tickets) {
+  AI4E_REQUIRE(e && h_tile && out_tickets, "submit_tile: null pointer");
+  AI4E_REQUIRE(c == e->desc.in_c, "submit_tile: tile has %d channels, model takes %d", c, e->desc.in_c);
+  AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
+  AI4E_REQUIRE(row_stride >= 0, "submit_tile: negative row stride");
+  if (row_stride == 0) row_stride = tile_w * c;
+  AI4E_REQUIRE(row_stride >= tile_w * c, "submit_tile: row stride too small");
+  const int gh = tile_h / chip, gw = tile_w / chip;
+  AI4E_REQUIRE(first_chip >= 0 && n_chips >= 1 && first_chip + n_chips <= gh * gw, "submit_tile: chips [%d, %d) outside the %d x %d grid",
+               first_chip, first_chip + n_chips, gh, gw);
+  const int r0 = first_chip / gw, r1 = (first_chip + n_chips - 1) / gw;
+  const size_t band_rows = (size_t)(r1 - r0 + 1) * chip;
+  const size_t row_bytes = ((size_t)gw * chip * c + 15) & ~(size_t)15;  // device rows: only the columns chips cover, 16-byte aligned
+  const size_t band_bytes = band_rows * row_bytes;
+  AI4E_CUDA_TRY(cudaSetDevice(e->device));
 
-int ai4e_pool_create(const int* devices, int n_devices, const ai4e_model_desc* desc, const void* h_weights_blob,
-                     uint64_t blob_bytes, int max_batch, int max_wait_us, ai4e_pool** out) {
-  AI4E_REQUIRE(devices && n_devices >= 1 && n_devices <= 64 && out, "pool_create: bad arguments");
-  ai4e_pool* p = new ai4e_pool();
-  for (int i = 0; i < n_devices; ++i) {
-    ai4e_engine* e = nullptr;
-    int rc = ai4e_engine_create(devices[i], desc, h_weights_blob, blob_bytes, max_batch, max_wait_us, &e);
-    if (rc) { ai4e_pool_destroy(p); return rc; }
-    p->engines.push_back(e);
+  // ---- a free tile buffer
+  TileBuf* tb = nullptr;
+  {
+    std::unique_lock<std::mutex> lk(e->mu);
+    for (;;) {
+      if (e->stopping) { set_last_error("submit_tile: engine is shutting down"); return AI4E_ERR_STATE; }
+      if (!e->healthy.load()) { set_last_error("submit_tile: engine on device %d is unhealthy", e->device); return AI4E_ERR_STATE; }
+      for (TileBuf& t : e->tiles)
+        if (!t.busy && t.users == 0) { tb = &t; break; }
+      if (tb) break;
+      e->cv_free.wait(lk);
+    }
+    tb->busy = true;
   }
-  *out = p;
-  return AI4E_OK;
+  auto release = [&](int rc) {
+    std::lock_guard<std::mutex> lk(e->mu);
+    tb->busy = false;
+    e->cv_free.notify_all();
+    return rc;
+  };
+  if (tb->bytes < band_bytes) {  // first tile of this size on this buffer
+    if (tb->d) cudaFree(tb->d);
+    tb->d = nullptr; tb->bytes = 0;
+    cudaError_t ce = cudaMalloc((void**)&tb->d, band_bytes);
+    if (ce != cudaSuccess) { set_last_error("submit_tile: %zu bytes of tile buffer: %s", band_bytes, cudaGetErrorString(ce)); cudaGetLastError(); return release(AI4E_ERR_NOMEM); }
+    tb->bytes = band_bytes;
+  }
+  // page-locked source: asynchronous, keep the tile unchanged until its tickets are done; pageable
+  // source: the runtime stages it and the tile is free on return
+  cudaError_t ce = cudaMemcpy2DAsync(tb->d, row_bytes, h_tile + (size_t)r0 * chip * row_stride, (size_t)row_stride,
+                                     (size_t)gw * chip * c, band_rows, cudaMemcpyHostToDevice, e->copy_stream);
+  if (ce == cudaSuccess) ce = cudaEventRecord(tb->ev_ready, e->copy_stream);
+  if (ce != cudaSuccess) { set_last_error("submit_tile: H2D copy failed: %s", cudaGetErrorString(ce)); return release(AI4E_ERR_CUDA); }
+
+  // ---- batches over the band
+  int done = 0;
+  while (done < n_chips) {
+    const int count = std::min(n_chips - done, e->max_batch);
+    std::unique_lock<std::mutex> lk(e->mu);
+    for (;;) {
+      if (e->stopping || !e->healthy.load()) {
+        tb->busy = false;
+        e->cv_free.notify_all();
+        set_last_error("submit_tile: engine stopped or unhealthy");
+        return AI4E_ERR_STATE;
+      }
+      if (e->open_ctx && e->open_ctx->count > 0) {  // never mixed with single submits
+        e->closed_q.push_back(e->open_ctx);
+        e->open_ctx = nullptr;
+        e->cv_work.notify_one();
+      }
+      if (!e->open_ctx) {
+        if (e->free_q.empty()) { e->cv_free.wait(lk); continue; }
+        e->open_ctx = e->free_q.front();
+        e->free_q.pop_front();
+      }
+      break;
+    }
+    BatchCtx* ctx = e->open_ctx;
+    e->open_ctx = nullptr;
+    ctx->count = count; ctx->src_h = chip; ctx->src_w = chip; ctx->kind = kKindTile;
+    ctx->tile = tb; ctx->tile_first = first_chip - r0 * gw + done; ctx->tile_grid_w = gw; ctx->tile_chip = chip;
+    ctx->tile_row_bytes = (long long)row_bytes;
+    ctx->ext_src = nullptr;
+    ctx->t_first = Clock::now();
+    ctx->first_ticket = e->next_ticket;
+    ctx->copied.store(count);
+    tb->users += 1;
+    for (int i = 0; i < count; ++i) {
+      const uint64_t t = e->next_ticket++;
+      const uint64_t r = t % kResultRing;
+      out_tickets[done + i] = t;
+      e->r_submit[r] = ctx->t_first;
+      e->r_status[r] = 1;
+      e->r_notify[r] = 0;
+      e->r_tag[r] = 0;
+    }
+    e->n_submitted.fetch_add((uint64_t)count);
+    e->closed_q.push_back(ctx);
+    e->cv_work.notify_one();
+    done += count;
+  }
+  return release(AI4E_OK);
 }
 
-int ai4e_pool_destroy(ai4e_pool* p) {
-  if (!p) return AI4E_OK;
-  for (ai4e_engine* e : p->engines) ai4e_engine_destroy(e);
-  delete p;
-  return AI4E_OK;
-}
-
-// ticket = replica index in the top byte | replica-local ticket.  Routing: the healthy replica
-// with the shortest queue, round-robin among equals (the reference: Istio ROUND_ROBIN).
-// A tile cut into chip x chip chips (row-major over the chip grid), every chip submitted from C:
-// the strided copies into the pinned slots and the ticket bookkeeping without a Python round trip
-// per chip (SURVEY 8(f) row 3 for the land-cover case: tile -> chips -> classify).
 int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
                             int chip, uint64_t* out_tickets, int capacity, int* out_count) {
   AI4E_REQUIRE(e && h_tile && out_tickets && out_count, "submit_tile: null pointer");
   AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
-  if (row_stride <= 0) row_stride = tile_w * c;
-  const int gh = tile_h / chip, gw = tile_w / chip;
-  AI4E_REQUIRE(capacity >= gh * gw, "submit_tile: %d tickets needed, room for %d", gh * gw, capacity);
-  // The cost of a submit is the strided copy of the chip into its pinned slot (256 KB for a
-  // 256 x 256 x 4 chip: one thread moves ~300 tiles/s of 64 chips and the GPU waits), so the chips are
-  // dealt to a few threads; ai4e_engine_submit is thread-safe and a batch launches only when all of
-  // its copies have landed.
-  const int total = gh * gw;
-  const int n_threads = std::max(1, std::min({8, total / 4, (int)std::thread::hardware_concurrency()}));
-  std::vector<int> rcs(n_threads, AI4E_OK);
-  std::vector<std::string> msgs(n_threads);
-  auto work = [&](int t) {
-    for (int i = t; i < total; i += n_threads) {
-      const int r = i / gw, q = i - r * gw;
-      const uint8_t* src = h_tile + (size_t)r * chip * row_stride + (size_t)q * chip * c;
-      const int rc = ai4e_engine_submit(e, src, chip, chip, c, row_stride, 0, &out_tickets[i]);
-      if (rc) { rcs[t] = rc; msgs[t] = ai4e_last_error(); return; }  // the message is thread-local: carry it over
-    }
-  };
-  std::vector<std::thread> pool;
-  for (int t = 1; t < n_threads; ++t) pool.emplace_back(work, t);
-  work(0);
-  for (auto& th : pool) th.join();
+  const int total = (tile_h / chip) * (tile_w / chip);
+  AI4E_REQUIRE(capacity >= total, "submit_tile: %d tickets needed, room for %d", total, capacity);
+  *out_count = 0;
+  int rc = submit_tile_range(e, h_tile, tile_h, tile_w, c, row_stride, chip, 0, total, out_tickets);
+  if (rc) return rc;
   *out_count = total;
-  for (int t = 0; t < n_threads; ++t)
-    if (rcs[t]) { set_last_error("%s", msgs[t].c_str()); *out_count = 0; return rcs[t]; }
   return AI4E_OK;
 }
 
@@ -1147,46 +1384,42 @@ int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_
   return AI4E_OK;
 }
 
-static int pool_pick(ai4e_pool* p);
+// ---------------------------------------------------------------------------------------- pool
+// ticket = replica index in the top byte | replica-local ticket.  Routing: the healthy replica
+// with the shortest queue, round-robin among equals (the reference: Istio ROUND_ROBIN).
+struct ai4e_pool {
+  std::vector<ai4e_engine*> engines;
+  std::atomic<uint64_t> rr{0};
+  CompletionQueue cq;  // shared by the replicas: one reaper thread serves all GPUs
+};
 
-int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
-  AI4E_REQUIRE(p && out_ticket, "pool_submit_jpeg: null pointer");
-  const int best = pool_pick(p);
-  if (best < 0) { set_last_error("pool_submit_jpeg: no healthy replica"); return AI4E_ERR_STATE; }
-  uint64_t t = 0;
-  int rc = ai4e_engine_submit_jpeg(p->engines[best], jpeg, len, tag, &t);
-  if (rc) return rc;
-  *out_ticket = ((uint64_t)best << 56) | (t & ((1ull << 56) - 1));
-  return AI4E_OK;
-}
+static constexpr uint64_t kLocalMask = (1ull << 56) - 1;
 
-int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
-                     uint64_t* out_ticket) {
-  AI4E_REQUIRE(p && out_ticket, "pool_submit: null pointer");
-  const size_t n = p->engines.size();
-  const uint64_t start = p->rr.fetch_add(1);
-  int best = -1;
-  uint64_t best_depth = ~0ull;
-  for (size_t k = 0; k < n; ++k) {
-    const size_t i = (start + k) % n;
-    ai4e_engine* e = p->engines[i];
-    if (!e->healthy.load()) continue;
-    uint64_t depth;
-    {
-      std::lock_guard<std::mutex> lk(e->mu);
-      depth = e->next_ticket - e->done_upto;
-    }
-    if (depth < best_depth) { best_depth = depth; best = (int)i; }
+int ai4e_pool_create(const int* devices, int n_devices, const ai4e_model_desc* desc, const void* h_weights_blob,
+                     uint64_t blob_bytes, int max_batch, int max_wait_us, ai4e_pool** out) {
+  AI4E_REQUIRE(devices && n_devices >= 1 && n_devices <= 64 && out, "pool_create: bad arguments");
+  ai4e_pool* p = new ai4e_pool();
+  for (int i = 0; i < n_devices; ++i) {
+    ai4e_engine* e = nullptr;
+    int rc = ai4e_engine_create(devices[i], desc, h_weights_blob, blob_bytes, max_batch, max_wait_us, &e);
+    if (rc) { ai4e_pool_destroy(p); return rc; }
+    e->cq = &p->cq;
+    e->ticket_prefix = (uint64_t)i << 56;
+    p->engines.push_back(e);
   }
-  if (best < 0) { set_last_error("pool_submit: no healthy replica"); return AI4E_ERR_STATE; }
-  uint64_t t = 0;
-  int rc = ai4e_engine_submit(p->engines[best], h_hwc, h, w, c, row_stride, tag, &t);
-  if (rc) return rc;
-  *out_ticket = ((uint64_t)best << 56) | (t & ((1ull << 56) - 1));
+  *out = p;
   return AI4E_OK;
 }
 
-// healthy replica with the shortest queue, round-robin among equals (-1: none)
+int ai4e_pool_destroy(ai4e_pool* p) {
+  if (!p) return AI4E_OK;
+  for (ai4e_engine* e : p->engines) ai4e_engine_destroy(e);
+  delete p;
+  return AI4E_OK;
+}
+
+// healthy replica with the shortest queue, round-robin among equals (-1: none).  Reads two atomics
+// per replica: no engine lock is taken on the routing path.
 static int pool_pick(ai4e_pool* p) {
   const size_t n = p->engines.size();
   const uint64_t start = p->rr.fetch_add(1);
@@ -1196,21 +1429,133 @@ static int pool_pick(ai4e_pool* p) {
     const size_t i = (start + k) % n;
     ai4e_engine* e = p->engines[i];
     if (!e->healthy.load()) continue;
-    uint64_t depth;
-    {
-      std::lock_guard<std::mutex> lk(e->mu);
-      depth = e->next_ticket - e->done_upto;
-    }
+    const uint64_t done = e->n_completed.load(), sub = e->n_submitted.load();
+    const uint64_t depth = sub > done ? sub - done : 0;
     if (depth < best_depth) { best_depth = depth; best = (int)i; }
   }
   return best;
+}
+
+#define POOL_PICK_OR_FAIL(who)                                                       \
+  const int best = pool_pick(p);                                                     \
+  if (best < 0) { set_last_error(who ": no healthy replica"); return AI4E_ERR_STATE; }
+
+int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, int c, int row_stride, uint64_t tag,
+                     uint64_t* out_ticket) {
+  AI4E_REQUIRE(p && out_ticket, "pool_submit: null pointer");
+  POOL_PICK_OR_FAIL("pool_submit");
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit(p->engines[best], h_hwc, h, w, c, row_stride, tag, &t);
+  if (rc) return rc;
+  *out_ticket = ((uint64_t)best << 56) | (t & kLocalMask);
+  return AI4E_OK;
+}
+
+int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
+  AI4E_REQUIRE(p && out_ticket, "pool_submit_jpeg: null pointer");
+  POOL_PICK_OR_FAIL("pool_submit_jpeg");
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit_jpeg(p->engines[best], jpeg, len, tag, &t);
+  if (rc) return rc;
+  *out_ticket = ((uint64_t)best << 56) | (t & kLocalMask);
+  return AI4E_OK;
+}
+
+// n images in one call: dealt to the replicas in runs (n / replicas, at most a micro-batch), each run
+// to the replica with the shortest queue at that moment.
+int ai4e_pool_submit_many(ai4e_pool* p, const uint8_t* const* h_images, int n, int h, int w, int c, int row_stride,
+                          const uint64_t* tags_or_null, int notify, uint64_t* out_tickets) {
+  AI4E_REQUIRE(p && h_images && out_tickets && n >= 0, "pool_submit_many: bad arguments");
+  const int ne = (int)p->engines.size();
+  const int run = std::max(1, std::min(p->engines[0]->max_batch, (n + ne - 1) / ne));
+  for (int i = 0; i < n; i += run) {
+    const int k = std::min(run, n - i);
+    POOL_PICK_OR_FAIL("pool_submit_many");
+    int rc = ai4e_engine_submit_many(p->engines[best], h_images + i, k, h, w, c, row_stride,
+                                     tags_or_null ? tags_or_null + i : nullptr, notify, out_tickets + i);
+    if (rc) return rc;
+    for (int j = 0; j < k; ++j) out_tickets[i + j] = ((uint64_t)best << 56) | (out_tickets[i + j] & kLocalMask);
+  }
+  return AI4E_OK;
+}
+
+int ai4e_pool_submit_batch(ai4e_pool* p, const uint8_t* h_images, int count, int h, int w, int c,
+                           uint64_t* out_first_ticket) {
+  AI4E_REQUIRE(p && out_first_ticket, "pool_submit_batch: null pointer");
+  POOL_PICK_OR_FAIL("pool_submit_batch");
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit_batch(p->engines[best], h_images, count, h, w, c, &t);
+  if (rc) return rc;
+  *out_first_ticket = ((uint64_t)best << 56) | (t & kLocalMask);  // the batch's tickets are consecutive
+  return AI4E_OK;
+}
+
+// The chips of a tile in contiguous ranges, one range per healthy replica (256 chips on 8 GPUs: 32
+// each); every replica receives only the band of chip rows it needs.
+int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride, int chip,
+                          uint64_t* out_tickets, int capacity, int* out_count) {
+  AI4E_REQUIRE(p && h_tile && out_tickets && out_count, "pool_submit_tile: null pointer");
+  AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "pool_submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
+  const int total = (tile_h / chip) * (tile_w / chip);
+  AI4E_REQUIRE(capacity >= total, "pool_submit_tile: %d tickets needed, room for %d", total, capacity);
+  *out_count = 0;
+  std::vector<int> alive;
+  const uint64_t start = p->rr.fetch_add(1);
+  for (size_t k = 0; k < p->engines.size(); ++k) {
+    const size_t i = (start + k) % p->engines.size();
+    if (p->engines[i]->healthy.load()) alive.push_back((int)i);
+  }
+  if (alive.empty()) { set_last_error("pool_submit_tile: no healthy replica"); return AI4E_ERR_STATE; }
+  const int parts = (int)std::min<size_t>(alive.size(), (size_t)total);
+  const int per = (total + parts - 1) / parts;
+  std::vector<int> rcs(parts, AI4E_OK);
+  std::vector<std::string> msgs(parts);
+  auto work = [&](int k) {  // one submitter per replica: the H2D copies of the bands run side by side
+    const int first = k * per, n = std::min(per, total - first);
+    if (n <= 0) return;
+    const int i = alive[k];
+    const int rc = submit_tile_range(p->engines[i], h_tile, tile_h, tile_w, c, row_stride, chip, first, n, out_tickets + first);
+    if (rc) { rcs[k] = rc; msgs[k] = ai4e_last_error(); return; }
+    for (int j = 0; j < n; ++j) out_tickets[first + j] = ((uint64_t)i << 56) | (out_tickets[first + j] & kLocalMask);
+  };
+  std::vector<std::thread> th;
+  for (int k = 1; k < parts; ++k) th.emplace_back(work, k);
+  work(0);
+  for (auto& t : th) t.join();
+  for (int k = 0; k < parts; ++k)
+    if (rcs[k]) { set_last_error("%s", msgs[k].c_str()); return rcs[k]; }
+  *out_count = total;
+  return AI4E_OK;
+}
+
+int ai4e_pool_wait_for(ai4e_pool* p, uint64_t ticket, int64_t timeout_us, int32_t* top_idx5, float* top_prob5,
+                       float* logits_or_null) {
+  AI4E_REQUIRE(p, "pool_wait: null pool");
+  const size_t i = ticket >> 56;
+  AI4E_REQUIRE(i < p->engines.size(), "pool_wait: bad ticket");
+  return ai4e_engine_wait_for(p->engines[i], ticket & kLocalMask, timeout_us, top_idx5, top_prob5, logits_or_null);
 }
 
 int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5, float* logits_or_null) {
   AI4E_REQUIRE(p, "pool_wait: null pool");
   const size_t i = ticket >> 56;
   AI4E_REQUIRE(i < p->engines.size(), "pool_wait: bad ticket");
-  return ai4e_engine_wait(p->engines[i], ticket & ((1ull << 56) - 1), top_idx5, top_prob5, logits_or_null);
+  return ai4e_engine_wait(p->engines[i], ticket & kLocalMask, top_idx5, top_prob5, logits_or_null);
+}
+
+int ai4e_pool_wait_many(ai4e_pool* p, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5) {
+  AI4E_REQUIRE(p && tickets && top_idx5 && top_prob5 && n >= 0, "pool_wait_many: bad arguments");
+  for (int i = 0; i < n; ++i) {
+    int rc = ai4e_pool_wait(p, tickets[i], top_idx5 + (size_t)i * AI4E_TOPK, top_prob5 + (size_t)i * AI4E_TOPK, nullptr);
+    if (rc) return rc;
+  }
+  return AI4E_OK;
+}
+
+int ai4e_pool_poll(ai4e_pool* p, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags, int32_t* status,
+                   int32_t* top_idx5, float* top_prob5, int* out_n) {
+  AI4E_REQUIRE(p && out_n && capacity >= 0, "pool_poll: bad arguments");
+  return poll_queue(&p->cq, capacity, timeout_us, tickets, tags, status, top_idx5, top_prob5, out_n);
 }
 
 int ai4e_pool_flush(ai4e_pool* p) {

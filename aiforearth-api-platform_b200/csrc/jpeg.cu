@@ -49,6 +49,8 @@ bool build_table(HuffTable& t, const uint8_t* counts, const uint8_t* syms, int n
   for (int len = 1; len <= 16; ++len) {
     t.valptr[len] = k;
     t.mincode[len] = code;
+    // over-subscribed code lengths would index past the look-up table below: refuse them first
+    if (code + counts[len - 1] > (1 << len)) return false;
     for (int i = 0; i < counts[len - 1]; ++i, ++k, ++code) {
       if (len <= kLookBits) {
         const int first = code << (kLookBits - len);
@@ -56,7 +58,6 @@ bool build_table(HuffTable& t, const uint8_t* counts, const uint8_t* syms, int n
       }
     }
     t.maxcode[len] = counts[len - 1] ? code - 1 : -1;
-    if (code > (1 << len)) return false;  // over-subscribed
     code <<= 1;
   }
   t.maxcode[17] = 0x7fffffff;
@@ -231,16 +232,19 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
       out->restart_interval = rd16(seg);
     } else if (m == 0xDA) {
       AI4E_REQUIRE(have_frame, "jpeg: SOS before SOF");
-      AI4E_REQUIRE(n >= 1 + 2 * seg[0] + 3, "jpeg: bad scan header");
+      AI4E_REQUIRE(n >= 1 && n >= 1 + 2 * seg[0] + 3, "jpeg: bad scan header");
       if (seg[0] != out->components) {
         set_last_error("jpeg: multi-scan files are not supported");
         return AI4E_ERR_UNSUPPORTED;
       }
+      bool named[3] = {false, false, false};
       for (int i = 0; i < seg[0]; ++i) {
         int c = -1;
         for (int j = 0; j < out->components; ++j)
           if (cid[j] == seg[1 + 2 * i]) c = j;
         AI4E_REQUIRE(c >= 0, "jpeg: scan names an unknown component");
+        AI4E_REQUIRE(!named[c], "jpeg: scan names component %d twice", c);
+        named[c] = true;
         td[c] = seg[2 + 2 * i] >> 4;
         ta[c] = seg[2 + 2 * i] & 15;
         AI4E_REQUIRE(td[c] < 4 && ta[c] < 4 && dc[td[c]].present && ac[ta[c]].present, "jpeg: scan uses an undefined Huffman table");

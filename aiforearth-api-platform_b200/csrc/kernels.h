@@ -10,11 +10,20 @@ namespace ai4e {
 
 int sm_count();
 
+// K6: the images of a batch are chips of one larger tile.  Image i sits at
+//   d_src + ((first + i) / grid_w) * y_stride + ((first + i) % grid_w) * x_stride        (bytes)
+// and its rows are `row_bytes` apart (the tile's row pitch): the gather is address arithmetic inside
+// K1, no copy.  grid_w == 0 (or a null pointer) means "images src_image_stride apart".
+struct ChipGrid {
+  int grid_w = 0, first = 0;
+  long long x_stride = 0, y_stride = 0, row_bytes = 0;
+};
+
 // ---- K1 preprocess (preprocess.cu); returns 1 if the streaming LUT kernel ran, 0 generic
 int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
                       long long src_image_stride, int src_row_stride, int resize_h, int resize_w,
                       int out_h, int out_w, const float* mean, const float* stdv, int layout,
-                      int out_channels, void* d_dst, cudaStream_t stream);
+                      int out_channels, void* d_dst, cudaStream_t stream, const ChipGrid* chips = nullptr);
 
 // ---- K0 baseline JPEG (jpeg.cu): host headers + entropy decode, device IDCT / upsampling / colour
 int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_t capacity_int16, ai4e_jpeg_info* out);

@@ -17,6 +17,7 @@
 //     one thread per output pixel, same fp32 operation order as the oracle, no FMA
 //     contraction.
 #include "common.cuh"
+#include "kernels.h"
 #include <cstdlib>
 
 namespace ai4e {
@@ -33,7 +34,20 @@ struct PreprocParams {
   int layout;        // 0 = NCHW, 1 = NHWC
   int out_channels;  // NHWC: padded channel count (>= channels); NCHW: == channels
   float mean[4], stdv[4];
+  // K6 chip grid (grid_w > 0): image i starts at ((first + i) / grid_w) * y_stride + ((first + i) % grid_w) * x_stride
+  int grid_w, grid_first;
+  long long grid_x_stride, grid_y_stride;
+  int rows_per_chunk;  // streaming kernel with strided rows: a chunk is this many whole rows (0 = dense images)
 };
+
+__device__ __forceinline__ const uint8_t* image_base(const PreprocParams& p, int img) {
+  if (p.grid_w > 0) {
+    const int g = p.grid_first + img;
+    const int gy = g / p.grid_w, gx = g - gy * p.grid_w;
+    return p.src + (long long)gy * p.grid_y_stride + (long long)gx * p.grid_x_stride;
+  }
+  return p.src + (long long)img * p.src_image_stride;
+}
 
 constexpr int kPixPerThread = 16;
 constexpr int kLutThreads = 256;
@@ -81,10 +95,19 @@ preprocess_lut_kernel(const PreprocParams p, int chunks_per_image, int total_chu
     const int px0 = cj * kChunkPix;
     const int npx = min(kChunkPix, hw - px0);
     const uint32_t bytes = (uint32_t)npx * C;
-    const uint8_t* g = p.src + (long long)img * p.src_image_stride + (long long)px0 * C;
+    const uint8_t* base = image_base(p, img);
     const uint32_t bar = smem_u32(&bars[stage]);
     mbar_expect_tx(bar, bytes);
-    bulk_load_1d(smem_u32(stage_buf + stage * Cfg::kStageBytes), g, bytes, bar);
+    if (p.rows_per_chunk == 0) {
+      bulk_load_1d(smem_u32(stage_buf + stage * Cfg::kStageBytes), base + (long long)px0 * C, bytes, bar);
+    } else {
+      // strided rows (a chip inside a tile): the chunk is whole rows, one bulk copy per row, one barrier
+      const int row0 = px0 / p.src_w, rows = npx / p.src_w;
+      const uint32_t rb = (uint32_t)p.src_w * C;
+      for (int r = 0; r < rows; ++r)
+        bulk_load_1d(smem_u32(stage_buf + stage * Cfg::kStageBytes + r * rb),
+                     base + (long long)(row0 + r) * p.src_row_stride, rb, bar);
+    }
   };
   if (tid == 0) {  // the source is the caller's buffer, not a predecessor kernel's output
     for (int s = 0; s < kStages; ++s) {
@@ -201,7 +224,7 @@ preprocess_generic_kernel(const PreprocParams p) {
     const int x = (int)(idx % p.out_w);
     const int y = (int)((idx / p.out_w) % p.out_h);
     const int n = (int)(idx / ((long long)p.out_w * p.out_h));
-    const uint8_t* img = p.src + (long long)n * p.src_image_stride;
+    const uint8_t* img = image_base(p, n);
     const int C = p.channels;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
     if (p.resize_h > 0) {
@@ -236,23 +259,26 @@ preprocess_generic_kernel(const PreprocParams p) {
   }
 }
 
-static int g_sm_count = 0;
-int sm_count() {
-  if (g_sm_count == 0) {
+static std::atomic<int> g_sm_count{0};
+int sm_count() {  // of the first device asked about; a box holds one kind of GPU
+  int n = g_sm_count.load(std::memory_order_relaxed);
+  if (n == 0) {
     int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&g_sm_count, cudaDevAttrMultiProcessorCount, dev);
-    if (g_sm_count <= 0) g_sm_count = 148;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+    g_sm_count.store(n, std::memory_order_relaxed);
   }
-  return g_sm_count;
+  return n;
 }
 
 // returns 1 if the streaming (LUT) kernel was used, 0 for the generic kernel, <0 on error
 int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int channels,
                       long long src_image_stride, int src_row_stride, int resize_h, int resize_w,
                       int out_h, int out_w, const float* mean, const float* stdv, int layout,
-                      int out_channels, void* d_dst, cudaStream_t stream) {
+                      int out_channels, void* d_dst, cudaStream_t stream, const ChipGrid* chips) {
   AI4E_REQUIRE(d_src && d_dst && mean && stdv, "preprocess: null pointer");
+  if (chips && chips->grid_w <= 0) chips = nullptr;
   AI4E_REQUIRE(batch > 0 && src_h > 0 && src_w > 0, "preprocess: empty input (%d x %d x %d)", batch,
                src_h, src_w);
   AI4E_REQUIRE(channels == 3 || channels == 4, "preprocess: channels must be 3 or 4, got %d",
@@ -288,26 +314,39 @@ int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int
   p.crop_top = centre(full_h, out_h); p.crop_left = centre(full_w, out_w);
   p.out_h = out_h; p.out_w = out_w; p.layout = layout; p.out_channels = out_channels;
   for (int c = 0; c < 4; ++c) { p.mean[c] = c < channels ? mean[c] : 0.f; p.stdv[c] = c < channels ? stdv[c] : 1.f; }
+  if (chips) {
+    AI4E_REQUIRE(chips->first >= 0 && chips->x_stride >= (long long)src_w * channels &&
+                 chips->y_stride >= (long long)src_row_stride * src_h,
+                 "preprocess: chip grid strides smaller than a chip");
+    p.grid_w = chips->grid_w; p.grid_first = chips->first;
+    p.grid_x_stride = chips->x_stride; p.grid_y_stride = chips->y_stride;
+  }
 
   const long long hw = (long long)out_h * out_w;
-  const bool dense = !resize && out_h == src_h && out_w == src_w &&
-                     src_row_stride == src_w * channels;
-  const bool fast = dense && (hw % kPixPerThread == 0) && (src_image_stride % 16 == 0) &&
+  const bool same_size = !resize && out_h == src_h && out_w == src_w;
+  const bool dense = same_size && src_row_stride == src_w * channels;
+  // strided rows stream too when a 4096-pixel chunk is whole rows and every row is a 16-byte multiple
+  // at a 16-byte aligned address (256 x 256 x 4 chips of a 4096-wide tile: 16 rows of 1 KB per chunk)
+  const bool strided_ok = same_size && !dense && (kChunkPix % src_w == 0) && ((src_w * channels) % 16 == 0) &&
+                          (src_row_stride % 16 == 0);
+  const bool bases_ok = chips ? (chips->x_stride % 16 == 0 && chips->y_stride % 16 == 0) : (src_image_stride % 16 == 0);
+  const bool fast = (dense || strided_ok) && (hw % kPixPerThread == 0) && bases_ok &&
                     ((reinterpret_cast<uintptr_t>(d_src) & 15) == 0) &&
                     ((reinterpret_cast<uintptr_t>(d_dst) & 15) == 0) &&
                     (layout == 0 || out_channels == 4);
+  p.rows_per_chunk = (fast && !dense) ? kChunkPix / src_w : 0;
   if (fast) {
     const int chunks_per_image = (int)((hw + kChunkPix - 1) / kChunkPix);
     const long long total_chunks = (long long)chunks_per_image * batch;
     AI4E_REQUIRE(total_chunks < (1ll << 31), "preprocess: batch too large");
     const int grid = (int)std::min<long long>(total_chunks, (long long)sm_count());  // one CTA per SM (shared memory)
     if (channels == 3) {
-      static bool attr3 = false;
-      if (!attr3) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LutCfg<3>::kSmem)); attr3 = true; }
+      static std::atomic<unsigned long long> attr3{0};
+      if (int rc = ensure_dyn_smem(preprocess_lut_kernel<3>, LutCfg<3>::kSmem, attr3)) return rc;
       preprocess_lut_kernel<3><<<grid, kLutThreads, LutCfg<3>::kSmem, stream>>>(p, chunks_per_image, (int)total_chunks);
     } else {
-      static bool attr4 = false;
-      if (!attr4) { AI4E_CUDA_TRY(cudaFuncSetAttribute(preprocess_lut_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, LutCfg<4>::kSmem)); attr4 = true; }
+      static std::atomic<unsigned long long> attr4{0};
+      if (int rc = ensure_dyn_smem(preprocess_lut_kernel<4>, LutCfg<4>::kSmem, attr4)) return rc;
       preprocess_lut_kernel<4><<<grid, kLutThreads, LutCfg<4>::kSmem, stream>>>(p, chunks_per_image, (int)total_chunks);
     }
     AI4E_CUDA_TRY(cudaGetLastError());

@@ -89,6 +89,19 @@ AI4E_API int ai4e_preprocess(const uint8_t* d_src, int batch, int src_h, int src
                     int out_h, int out_w, const float* h_mean, const float* h_std, int layout,
                     int out_channels, void* d_dst_bf16, void* stream);
 
+/* K6 fused into K1: the images are chips of ONE larger tile already resident in device memory
+ * (land-cover case, BASELINE.json configs[3]: a 4096 x 4096 x 4 tile -> 256 chips of 256 x 256).
+ * Chips are numbered row-major over the (tile_h / chip) x (tile_w / chip) grid; chips
+ * [first_chip, first_chip + n_chips) are preprocessed exactly as ai4e_preprocess would preprocess
+ * their copies (same resize / crop / layout arguments, src size = chip x chip), but the gather is
+ * address arithmetic inside the kernel: no chip is ever copied.  The reference has no such stage; a
+ * PyTorch container slices the tile on the host before the model call at ai4e_service.py:203.
+ * Bit-exact against oracle/preprocess_oracle.py (chips_from_tile + preprocess). */
+AI4E_API int ai4e_preprocess_tile(const uint8_t* d_tile, int tile_h, int tile_w, int channels, int tile_row_stride,
+                         int chip, int first_chip, int n_chips, int resize_h, int resize_w, int out_h, int out_w,
+                         const float* h_mean, const float* h_std, int layout, int out_channels,
+                         void* d_dst_bf16, void* stream);
+
 /* K2/K4.  One convolution layer with folded BatchNorm, optional residual add and ReLU fused:
  *   out = act(conv(in, w) + bias [+ residual]).  Stands in for Conv2d + BatchNorm2d (+ add)
  * (+ ReLU) of torchvision's ResNet blocks.  `algo` is one of AI4E_CONV_*.  The tcgen05 path
@@ -250,6 +263,20 @@ AI4E_API int ai4e_engine_forward_device(ai4e_engine* e, const uint8_t* d_images,
  * per-task thread + per-image forward of ai4e_service.py:180-183,203. */
 AI4E_API int ai4e_engine_submit(ai4e_engine* e, const uint8_t* h_hwc, int h, int w, int c, int row_stride,
                        uint64_t tag, uint64_t* out_ticket);
+/* `n` images of one size in ONE call (one lock acquisition per micro-batch instead of per image, one
+ * trip through the caller's FFI).  h_images[i] points at image i (rows `row_stride` bytes apart,
+ * 0 = dense); tags_or_null[i] is an opaque caller value (a task index) handed back by
+ * ai4e_engine_poll.  With notify != 0 every ticket is ANNOUNCED when its batch finishes: one
+ * reaper thread drains ai4e_engine_poll instead of one blocked thread per task in `wait` - the
+ * thread-per-task model of ai4e_service.py:180-183 turned into a queue.  row_stride must not be
+ * negative (copy a flipped view first). */
+AI4E_API int ai4e_engine_submit_many(ai4e_engine* e, const uint8_t* const* h_images, int n, int h, int w, int c,
+                            int row_stride, const uint64_t* tags_or_null, int notify, uint64_t* out_tickets);
+/* Up to `capacity` announced completions, oldest first; blocks up to timeout_us for the first one
+ * (< 0: for ever, 0: never).  Any output array may be NULL.  status[i] is AI4E_OK or the error that
+ * failed the ticket's batch; top_idx5 / top_prob5 are [capacity][5].  *out_n may be 0 (timeout). */
+AI4E_API int ai4e_engine_poll(ai4e_engine* e, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
+                     int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n);
 /* A caller-made batch (e.g. the 256 chips of a land-cover tile, or a dispatcher that already
  * holds a full micro-batch): `count` dense images become one batch of their own, tickets
  * first..first+count-1.  If h_images is page-locked (cudaHostAlloc / cudaHostRegister /
@@ -266,18 +293,26 @@ AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, i
 AI4E_API int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag,
                                      uint64_t* out_ticket);
 /* A tile cut into chip x chip chips (row-major over the chip grid; the remainder at the right /
- * bottom is ignored), each submitted as by ai4e_engine_submit with the tile's row stride, in one
- * call: tile -> chips -> classify of the land-cover case (BASELINE.json configs[3]; the reference
- * chains such stages through AddPipelineTask, Common/task_management/distributed_api_task.py:67-100,
- * one HTTP hop per stage).  out_tickets: one per chip, `capacity` >= (tile_h/chip)*(tile_w/chip). */
+ * bottom is ignored), in one call: tile -> chips -> classify of the land-cover case (BASELINE.json
+ * configs[3]; the reference chains such stages through AddPipelineTask,
+ * Common/task_management/distributed_api_task.py:67-100, one HTTP hop per stage).  The tile crosses
+ * PCIe once (one 2-D H2D copy into a device tile buffer) and K1 reads the chips in place
+ * (ai4e_preprocess_tile): no per-chip copy on the host or the device.  A page-locked tile is copied
+ * asynchronously - keep it unchanged until the last ticket is done; a pageable one is free on
+ * return.  out_tickets: one per chip, `capacity` >= (tile_h/chip)*(tile_w/chip). */
 AI4E_API int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c,
                                      int row_stride, int chip, uint64_t* out_tickets, int capacity,
                                      int* out_count);
 /* ai4e_engine_wait for n tickets: top_idx5 / top_prob5 are [n][5]. */
 AI4E_API int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_t* top_idx5,
                                    float* top_prob5);
+/* Blocks until the ticket's batch has finished, at most AI4E_B200_WAIT_TIMEOUT_MS (default 60 s):
+ * then AI4E_ERR_TIMEOUT, and the ticket may be waited for again. */
 AI4E_API int ai4e_engine_wait(ai4e_engine* e, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                      float* logits_or_null);
+/* Same with an explicit limit: timeout_us < 0 waits for ever, 0 only reports a finished ticket. */
+AI4E_API int ai4e_engine_wait_for(ai4e_engine* e, uint64_t ticket, int64_t timeout_us, int32_t* top_idx5,
+                         float* top_prob5, float* logits_or_null);
 AI4E_API int ai4e_engine_flush(ai4e_engine* e);
 AI4E_API int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out);
 
@@ -287,6 +322,12 @@ AI4E_API int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out);
  * from it.  No reference counterpart (the reference has no profile). */
 AI4E_API int ai4e_engine_profile(ai4e_engine* e, const uint8_t* d_images, int batch, int src_h, int src_w,
                                  int reps, float* h_ms_out, int n_out);
+
+/* Fault drill: the next `n_batches` micro-batches fail as if their launch had hit a sticky CUDA
+ * error - their tickets fail with AI4E_ERR_CUDA, the replica turns unhealthy and a pool routes
+ * around it (SURVEY 5's failure model; the shell turns the error into
+ * FailTask(taskId, 'Task failed - try again'), ai4e_service.py:185-195).  No reference counterpart. */
+AI4E_API int ai4e_engine_debug_inject_fault(ai4e_engine* e, int n_batches);
 
 /* Debug/parity: copy activation slot `buf` of the last forward to the host (bf16 NHWC). */
 AI4E_API int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t bytes);
@@ -305,8 +346,24 @@ AI4E_API int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, 
                      uint64_t tag, uint64_t* out_ticket);
 AI4E_API int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag,
                                    uint64_t* out_ticket);
+/* The ai4e_engine_* calls of the same name behind the dispatcher.  submit_many deals the images to
+ * the replicas in runs, submit_batch gives the whole batch to one replica (tickets consecutive),
+ * submit_tile deals contiguous chip ranges, one per healthy replica (256 chips on 8 GPUs: 32 each)
+ * and sends each replica only the band of chip rows it needs; poll drains ONE queue that all
+ * replicas announce into. */
+AI4E_API int ai4e_pool_submit_many(ai4e_pool* p, const uint8_t* const* h_images, int n, int h, int w, int c,
+                          int row_stride, const uint64_t* tags_or_null, int notify, uint64_t* out_tickets);
+AI4E_API int ai4e_pool_submit_batch(ai4e_pool* p, const uint8_t* h_images, int count, int h, int w, int c,
+                           uint64_t* out_first_ticket);
+AI4E_API int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
+                          int chip, uint64_t* out_tickets, int capacity, int* out_count);
+AI4E_API int ai4e_pool_wait_many(ai4e_pool* p, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5);
+AI4E_API int ai4e_pool_poll(ai4e_pool* p, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
+                   int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n);
 AI4E_API int ai4e_pool_wait(ai4e_pool* p, uint64_t ticket, int32_t* top_idx5, float* top_prob5,
                    float* logits_or_null);
+AI4E_API int ai4e_pool_wait_for(ai4e_pool* p, uint64_t ticket, int64_t timeout_us, int32_t* top_idx5,
+                       float* top_prob5, float* logits_or_null);
 AI4E_API int ai4e_pool_flush(ai4e_pool* p);
 AI4E_API int ai4e_pool_size(ai4e_pool* p);
 AI4E_API int ai4e_pool_engine(ai4e_pool* p, int i, ai4e_engine** out);

@@ -251,6 +251,80 @@ def test_worker_pool_runs_many_tasks_concurrently():
     assert svc.func_request_counts["/c"] == 0
 
 
+def test_back_to_back_tasks_do_not_share_one_idle_worker():
+    """Two async requests that arrive while one worker is idle must both start at once (the reference
+    starts a thread per task, ai4e_service.py:180-183): the second may not wait for the first."""
+    from ai4e_service import _TaskWorkers
+    w = _TaskWorkers(16)
+    warm = threading.Event()
+    w.run(warm.set, (), {})
+    assert warm.wait(5)
+    time.sleep(0.05)  # the worker is idle again
+    started, gate = [], threading.Event()
+
+    def job(name):
+        started.append((name, time.perf_counter()))
+        gate.wait(5)
+
+    t0 = time.perf_counter()
+    w.run(job, ("a",), {})
+    w.run(job, ("b",), {})
+    for _ in range(200):
+        if len(started) == 2:
+            break
+        time.sleep(0.005)
+    gate.set()
+    assert len(started) == 2 and max(t for _, t in started) - t0 < 0.5
+
+
+class _FakePending:
+    """the surface of ai4e_b200.engine.Pending that the shell relies on."""
+
+    def __init__(self):
+        self.error, self._cbs, self.done = None, [], False
+
+    def add_done_callback(self, fn):
+        self._cbs.append(fn)
+
+    def resolve(self, error=None):
+        self.error = error
+        for fn in self._cbs:
+            fn(self)
+
+
+def test_deferred_task_keeps_the_request_counted_and_fails_like_an_exception():
+    """A task function that returns a Pending (engine.classify_later) frees its worker at once; the
+    request stays in flight until the Pending resolves, and an error there becomes
+    FailTask(taskId, 'Task failed - try again') like any exception (reference :185-195)."""
+    from ai4e_service import APIService
+    app = _flask()("d")
+    svc = APIService(app, type("L", (), {"tracer": None, "log_exception": lambda *a, **k: None})())
+    tm = RecordingTaskManager()
+    svc.api_task_manager = tm
+    pendings = {}
+
+    @svc.api_async_func(api_path="/c", methods=["POST"], maximum_concurrent_requests=8)
+    def c_(*args, **kwargs):
+        p = pendings[kwargs["taskId"]] = _FakePending()
+        return p
+
+    cl = app.test_client()
+    for tid in ("ok", "bad"):
+        assert cl.post("/c", headers={"taskId": tid}).get_data(as_text=True) == "TaskId: " + tid
+    for _ in range(200):
+        if len(pendings) == 2:
+            break
+        time.sleep(0.005)
+    time.sleep(0.05)
+    assert svc.func_request_counts["/c"] == 2          # the functions returned, the tasks have not finished
+    pendings["ok"].resolve()
+    assert svc.func_request_counts["/c"] == 1
+    pendings["bad"].resolve(RuntimeError("GPU batch failed"))
+    assert svc.func_request_counts["/c"] == 0
+    fails = [c for c in tm.calls if c[0] == "FailTask"]
+    assert fails == [["FailTask", "bad", "Task failed - try again"]]
+
+
 def test_metrics_endpoint_uses_the_platform_metric_names(monkeypatch):
     """in-flight requests under the name the HPA consumes
     (CURRENT_REQUESTS/{cluster}{prefix}{path}), counted while a request is being served, plus the

@@ -90,6 +90,54 @@ def test_host_decoder_rejects_what_it_does_not_support():
         ops.jpeg_entropy_decode(good[:200])  # truncated inside the tables / scan
 
 
+def _dht_stream(counts, nsyms=None, tc_th=0x00):
+    """SOI + one DHT segment with the given 16 code-length counts (+ EOI)."""
+    counts = list(counts) + [0] * (16 - len(counts))
+    n = sum(counts) if nsyms is None else nsyms
+    seg = bytes([tc_th]) + bytes(counts) + bytes(range(256))[:n]
+    return b"\xff\xd8" + b"\xff\xc4" + (len(seg) + 2).to_bytes(2, "big") + seg + b"\xff\xd9"
+
+
+@pytest.mark.parametrize("length", range(1, 17))
+def test_host_decoder_refuses_oversubscribed_huffman_tables(length):
+    """A DHT whose counts claim more codes of one length than that length has must be refused
+    BEFORE the look-up table is filled: such a table used to write past it (a crafted request could
+    crash the serving process)."""
+    from ai4e_b200 import ops, Ai4eError
+    counts = [0] * 16
+    counts[length - 1] = min(255, (1 << length) + 1)
+    if counts[length - 1] <= (1 << length):  # 255 codes fit lengths >= 8: over-subscribe with the shorter ones
+        counts[0] = 2
+        counts[1] = 1
+    with pytest.raises(Ai4eError, match="Huffman"):
+        ops.jpeg_entropy_decode(_dht_stream(counts))
+
+
+def test_host_decoder_survives_malformed_segments():
+    from ai4e_b200 import ops, Ai4eError
+    with pytest.raises(Ai4eError):                       # counts[0] = 255: the reproducer of the overflow
+        ops.jpeg_entropy_decode(_dht_stream([255]))
+    with pytest.raises(Ai4eError):                       # 256 symbols declared, segment too short for them
+        ops.jpeg_entropy_decode(_dht_stream([0, 0, 0, 0, 0, 0, 0, 255, 1], nsyms=10))
+    with pytest.raises(Ai4eError):                       # a full, valid 256-symbol table alone: no frame header
+        ops.jpeg_entropy_decode(_dht_stream([0, 0, 0, 0, 0, 0, 0, 255, 2][:9]))
+    good = open(FIXTURES[0], "rb").read()
+    sos = good.index(b"\xff\xda")
+    with pytest.raises(Ai4eError):                       # SOS as the last four bytes: header length 2, no payload
+        ops.jpeg_entropy_decode(good[:sos] + b"\xff\xda\x00\x02")
+    # a scan that names the first component twice leaves the others without tables
+    hdr = bytearray(good[sos:sos + 14])
+    assert hdr[4] == 3
+    hdr[7] = hdr[5]
+    with pytest.raises(Ai4eError, match="twice"):
+        ops.jpeg_entropy_decode(good[:sos] + bytes(hdr) + good[sos + 14:])
+    for cut in range(2, min(len(good), 700), 7):         # truncation anywhere in the headers never crashes
+        try:
+            ops.jpeg_entropy_decode(good[:cut])
+        except Ai4eError:
+            pass
+
+
 # ------------------------------------------------------------------ GPU: bit-exact reconstruction
 @pytest.mark.gpu
 @pytest.mark.parametrize("path", FIXTURES, ids=_name)
