@@ -46,6 +46,31 @@ def preprocess(src_u8: torch.Tensor, mean, std, layout: str = "nchw", out_channe
     return out
 
 
+def preprocess_tile(tile_u8: torch.Tensor, chip: int, mean, std, first_chip: int = 0, n_chips: int | None = None,
+                    layout: str = "nchw", out_channels: int | None = None, resize: tuple[int, int] | None = None,
+                    crop: tuple[int, int] | None = None, stream=None) -> torch.Tensor:
+    """K6 fused into K1: uint8 [H,W,C] cuda tile -> the preprocessed chips [first_chip, first_chip + n_chips)
+    of its chip x chip grid (row-major), read in place - no chip is copied."""
+    lib = L.load()
+    assert tile_u8.is_cuda and tile_u8.dtype == torch.uint8 and tile_u8.dim() == 3
+    th, tw, c = tile_u8.shape
+    assert tile_u8.stride(2) == 1 and tile_u8.stride(1) == c, "pixels must be dense HWC"
+    total = (th // chip) * (tw // chip)
+    n = total - first_chip if n_chips is None else n_chips
+    rh, rw = resize if resize else (0, 0)
+    full_h, full_w = (rh, rw) if resize else (chip, chip)
+    oh, ow = crop if crop else (full_h, full_w)
+    if layout == "nchw":
+        oc, lay = c, L.LAYOUT_NCHW
+        out = torch.empty((n, c, oh, ow), dtype=torch.bfloat16, device=tile_u8.device)
+    else:
+        oc, lay = out_channels or 4, L.LAYOUT_NHWC
+        out = torch.empty((n, oh, ow, oc), dtype=torch.bfloat16, device=tile_u8.device)
+    L.check(lib.ai4e_preprocess_tile(_ptr(tile_u8), th, tw, c, tile_u8.stride(0), chip, first_chip, n, rh, rw, oh, ow,
+                                     _farr(mean, c), _farr(std, c), lay, oc, _ptr(out), _stream_ptr(stream)))
+    return out
+
+
 def conv_layer(x_nhwc: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tensor, stride: int, pad: int,
                residual: torch.Tensor | None = None, relu: bool = True, algo: int = L.CONV_AUTO,
                stream=None) -> torch.Tensor:

@@ -344,8 +344,24 @@ class APIService():
         with self._span(trace_name, kwargs):
             self._create_and_execute_thread(*args, **kwargs)
 
+    @staticmethod
+    def _detached_request():
+        """the request as the task function may read it on another thread.  The real request object
+        behind the context-bound proxy stays valid once its body is cached, and keeps the complete
+        API (headers, args, json, files); only a foreign request type falls back to a copy."""
+        live = request
+        unwrap = getattr(live, '_get_current_object', None)
+        if unwrap is None:
+            return RequestSnapshot(live)
+        obj = unwrap()
+        try:
+            obj.get_data(cache=True)  # the server may close the input stream once the view has answered
+        except Exception:  # noqa: BLE001 - not a Werkzeug request after all
+            return RequestSnapshot(live)
+        return obj
+
     def _create_and_execute_thread(self, *args, **kwargs):
-        kwargs['request'] = RequestSnapshot(request)
+        kwargs['request'] = self._detached_request()
         self._workers.run(self._execute_func_with_counter, args, kwargs)
 
     def _log_and_fail_exeception(self, is_async, **kwargs):

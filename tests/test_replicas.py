@@ -42,7 +42,7 @@ def _spawn(script: str, world: int, extra_env=None, timeout=240):
 
 WORKER = r"""
 import json, os, time
-from ai4e_b200.replicas import ReplicaGroup, shard_range
+from tools.replica_group import ReplicaGroup, shard_range
 g = ReplicaGroup("gloo")
 assert g.world == 2 and g.backend == "gloo"
 # rank 1 is late to the barrier; nobody may pass before it arrives
@@ -72,7 +72,7 @@ def test_replica_group_world2_gloo():
 
 
 def test_replica_group_world1_needs_no_process_group():
-    from ai4e_b200.replicas import ReplicaGroup, shard_range, merge_shards
+    from tools.replica_group import ReplicaGroup, shard_range, merge_shards
     env = {k: os.environ.pop(k, None) for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE")}
     try:
         g = ReplicaGroup()

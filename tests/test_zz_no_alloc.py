@@ -36,6 +36,10 @@ def test_head_noalloc_matches_head_twice_in_a_row():
     got1 = ops.head_noalloc(x1, w1, b1)
     torch.cuda.synchronize()
     _same(got1, want1)
+    # on its own feet too: the logits against plain fp32 torch (mean over the 7x7 positions, then FC)
+    ref = x1.float().mean(dim=(1, 2)) @ w1.float().t() + b1
+    assert torch.allclose(got1[0], ref, atol=2e-4, rtol=1e-4), (got1[0] - ref).abs().max()
+    assert torch.equal(got1[1][:, 0].long(), got1[0].argmax(dim=1))
     # ... the second, smaller and different, must not see anything of the first
     x2, w2, b2 = _case(5, 8, 512, 1000, seed=12)
     want2 = ops.head(x2, w2, b2)

@@ -1,0 +1,109 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[4], the latency half: open-loop Poisson arrivals at a fraction of the measured
+peak (50 % and 80 %), per-TASK latency p50 / p99 through submit -> result.
+
+    python tools/openloop_bench.py --gpus 1 --peak 75000 --load 0.5 0.8 [--max-batch 64] [--seconds 5]
+
+Arrival times are drawn up front (exponential gaps at rate load x peak).  A feeder thread submits every
+arrival that is due (one `submit_many` per wake-up, tag = arrival number); a reaper drains `poll`.
+Latency of a task = time its result was announced - its SCHEDULED arrival time, so time spent waiting
+for the feeder or for the micro-batch to close is counted.  One Pool over N GPUs, one process.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "aiforearth-api-platform_b200")]
+
+import numpy as np  # noqa: E402
+
+
+def run(pool, images, rate, seconds, seed=0):
+    rng = np.random.default_rng(seed)
+    n = int(rate * seconds)
+    arrivals = np.cumsum(rng.exponential(1.0 / rate, n))
+    done_at = np.zeros(n)
+    status = np.zeros(n, np.int32)
+    n_done = [0]
+    stop = [False]
+
+    def reaper():
+        while n_done[0] < n and not stop[0]:
+            tk, tg, st, idx, prob = pool.poll(4096, 0.05)
+            if len(tk):
+                now = time.perf_counter()
+                done_at[tg.astype(np.int64)] = now
+                status[tg.astype(np.int64)] = st
+                n_done[0] += len(tk)
+
+    rp = threading.Thread(target=reaper, daemon=True)
+    rp.start()
+    nimg = len(images)
+    t0 = time.perf_counter()
+    sent = 0
+    late_max = 0.0
+    while sent < n:
+        now = time.perf_counter() - t0
+        due = int(np.searchsorted(arrivals, now, side="right"))
+        if due <= sent:
+            gap = arrivals[sent] - now
+            if gap > 2e-4:
+                time.sleep(gap * 0.5)
+            continue
+        late_max = max(late_max, now - arrivals[sent])
+        k = min(due - sent, 512)
+        views = [images[j % nimg] for j in range(sent, sent + k)]  # views, not copies: only pointers travel
+        pool.submit_many(views, tags=np.arange(sent, sent + k, dtype=np.uint64), notify=True)
+        sent += k
+    deadline = time.time() + 30
+    while n_done[0] < n and time.time() < deadline:
+        time.sleep(0.005)
+    stop[0] = True
+    rp.join(timeout=2)
+    ok = done_at > 0
+    lat = (done_at[ok] - t0 - arrivals[ok]) * 1e3
+    lat.sort()
+    q = lambda f: float(lat[int((len(lat) - 1) * f)]) if len(lat) else None  # noqa: E731
+    span = (done_at[ok].max() - t0) if ok.any() else float("nan")
+    return {"offered_per_s": rate, "tasks": n, "completed": int(ok.sum()), "failed": int((status != 0).sum()),
+            "achieved_per_s": float(ok.sum() / span), "p50_ms": q(0.50), "p90_ms": q(0.90), "p99_ms": q(0.99),
+            "max_ms": q(1.0), "feeder_max_lateness_ms": late_max * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--peak", type=float, required=True, help="closed-loop images/s of this configuration (all GPUs)")
+    ap.add_argument("--load", type=float, nargs="+", default=[0.5, 0.8])
+    ap.add_argument("--max-batch", type=int, default=64)
+    ap.add_argument("--max-wait-us", type=int, default=2000)
+    ap.add_argument("--seconds", type=float, default=5.0)
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    from ai4e_b200.engine import Pool
+    from ai4e_b200.models import build_resnet_program, synthetic_state_dict
+    prog = build_resnet_program("resnet50", synthetic_state_dict("resnet50", seed=0), 224, 224)
+    images = np.random.default_rng(1234).integers(0, 256, (1024, 224, 224, 3), dtype=np.uint8)
+    rows = []
+    with Pool(prog, devices=list(range(a.gpus)), max_batch=a.max_batch, max_wait_us=a.max_wait_us) as pool:
+        run(pool, images, a.peak * 0.2, 1.0, seed=9)  # warm-up
+        for load in a.load:
+            r = run(pool, images, a.peak * load, a.seconds, seed=int(load * 100))
+            r.update({"gpus": a.gpus, "load": load, "peak_per_s": a.peak, "max_batch": a.max_batch, "max_wait_us": a.max_wait_us,
+                      "arrivals": "Poisson, open loop", "latency_of": "scheduled arrival -> result announced (Pool.submit_many / poll)"})
+            st = pool.stats()
+            r["batch_hist"] = np.sum([s["batch_hist"] for s in st], axis=0).tolist()
+            rows.append(r)
+            print(json.dumps(r), flush=True)
+    if a.out:
+        with open(a.out, "a") as fh:
+            for r in rows:
+                fh.write(json.dumps(r) + "\n")
+
+
+if __name__ == "__main__":
+    main()
