@@ -5,7 +5,8 @@ functions, so the hot path can be driven and benchmarked "in-process without net
 Contract restated from the reference (citations relative to /root/reference):
   * task JSON fields TaskId, Timestamp, Status, BackendStatus, Endpoint, Body, PublishToGrid
     (ProcessManager/Classes/APITask.cs:12-18);
-  * upsert: an empty body is a 400 (CacheManager/CacheConnectorUpsert.cs:57-74); an empty
+  * upsert: an empty body is a 400 (CacheManager/CacheConnectorUpsert.cs:57-74), a body that does not
+    deserialise a 500 (:76-82), an array body means its first element (:60-63); an empty
     TaskId gets a new GUID (:92-100); Timestamp is overwritten with UTC now (:102); the stored
     JSON has Body stripped (:119-127); the task id is added to the sorted set
     "{EndpointPath}_{BackendStatus}" scored by epoch seconds (:130-133) and removed from the
@@ -43,10 +44,12 @@ class LocalTaskStore:
             return 400, ""
         try:
             task = json.loads(body_text)
-        except ValueError:
-            return 400, ""
+            if isinstance(task, list):  # upstream takes the first element of an array body (:60-63)
+                task = task[0]
+        except (ValueError, IndexError):
+            return 500, ""  # upstream: the deserialiser throws and the function answers 500 (:76-82)
         if not isinstance(task, dict) or not task.get("Endpoint") or not task.get("BackendStatus"):
-            return 400, ""
+            return 500, ""  # upstream: Uri(null) / BackendStatus.Equals on null throw inside the try (:130-142, :204-210)
         task_body = task.get("Body")
         if not task.get("TaskId"):
             task["TaskId"] = str(uuid.uuid4())
@@ -54,8 +57,9 @@ class LocalTaskStore:
         task["Body"] = None
         task.setdefault("Status", None)
         task.setdefault("PublishToGrid", False)
-        serialized = json.dumps(task)
         path = urlparse(task["Endpoint"]).path
+        task["EndpointPath"] = path  # a public getter of APITask, so the serialiser emits it (Classes/APITask.cs:20-27)
+        serialized = json.dumps(task)
         status = task["BackendStatus"]
         tid = task["TaskId"]
         now = int(time.time())
