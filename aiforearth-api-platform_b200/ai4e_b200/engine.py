@@ -41,33 +41,68 @@ class Pending:
     counted as in flight until the result (and the `then` callback) is through, and an error in
     either marks the task failed exactly like an exception raised by the function itself."""
 
-    __slots__ = ("ticket", "idx", "prob", "error", "_then", "_done", "_watchers", "_lock")
+    __slots__ = ("ticket", "idx", "prob", "error", "_then", "_done", "_event", "_watchers")
+    _guard = threading.Lock()  # one lock for all Pendings: held for a few instructions at a time
 
     def __init__(self, then=None):
         self.ticket = None
         self.idx = self.prob = self.error = None
         self._then = then
-        self._done = threading.Event()
-        self._watchers = []
-        self._lock = threading.Lock()
+        self._done = False
+        self._event = None      # made only if somebody blocks in result()
+        self._watchers = None
 
     def done(self) -> bool:
-        return self._done.is_set()
+        return self._done
 
     def result(self, timeout=None):
-        if not self._done.wait(timeout):
-            raise TimeoutError("classify_later: no result yet")
+        if not self._done:
+            with Pending._guard:
+                if not self._done and self._event is None:
+                    self._event = threading.Event()
+                ev = self._event
+            if not self._done and not ev.wait(timeout):
+                raise TimeoutError("classify_later: no result yet")
         if self.error is not None:
             raise self.error
         return self.idx, self.prob
 
     def add_done_callback(self, fn):
         """fn(pending) once the result and `then` are through (at once if they already are)."""
-        with self._lock:
-            if not self._done.is_set():
-                self._watchers.append(fn)
+        with Pending._guard:
+            if not self._done:
+                if self._watchers is None:
+                    self._watchers = [fn]
+                else:
+                    self._watchers.append(fn)
                 return
         fn(self)
+
+    @classmethod
+    def gather(cls, pendings, then=None):
+        """one Pending for a task made of several images: resolves when all of `pendings` have, with
+        idx / prob stacked in order ([n, 5]); `then(idx, prob)` runs once; the first error wins."""
+        pendings = list(pendings)
+        whole = cls(then)
+        left = [len(pendings)]
+        lock = threading.Lock()
+
+        def one_done(_p):
+            with lock:
+                left[0] -= 1
+                last = left[0] == 0
+            if last:
+                err = next((q.error for q in pendings if q.error is not None), None)
+                if err is not None:
+                    whole._resolve(None, None, err)
+                else:
+                    whole._resolve(np.stack([q.idx for q in pendings]), np.stack([q.prob for q in pendings]), None)
+
+        if not pendings:
+            whole._resolve(np.empty((0, L.TOPK), np.int32), np.empty((0, L.TOPK), np.float32), None)
+        for q in pendings:
+            q.add_done_callback(one_done)
+        return whole
 
     def _resolve(self, idx, prob, error):
         self.idx, self.prob, self.error = idx, prob, error
@@ -76,14 +111,18 @@ class Pending:
                 self._then(idx, prob)
             except BaseException as e:  # noqa: BLE001 - reported through the Pending, like a task function's exception
                 self.error = e
-        with self._lock:
-            self._done.set()
-            watchers, self._watchers = self._watchers, []
-        for fn in watchers:
-            try:
-                fn(self)
-            except BaseException:  # noqa: BLE001 - a watcher must not kill the reaper
-                pass
+        with Pending._guard:
+            self._done = True
+            watchers, self._watchers = self._watchers, None
+            ev = self._event
+        if ev is not None:
+            ev.set()
+        if watchers:
+            for fn in watchers:
+                try:
+                    fn(self)
+                except BaseException:  # noqa: BLE001 - a watcher must not kill the reaper
+                    pass
 
 
 class _Base:
@@ -152,17 +191,23 @@ class _Base:
         """submit one image and return at once; `then(idx, prob)` runs on the reaper thread when the
         micro-batch has finished.  A task function returns the Pending to `APIService`."""
         p = Pending(then)
-        self._ensure_reaper()
+        if getattr(self, "_reaper", None) is None:
+            self._ensure_reaper()
+        a = _u8_hwc(image)
         with self._pend_lock:
             self._pend_seq += 1
             tag = self._pend_seq
             self._pending[tag] = p
-        try:
-            p.ticket = int(self.submit_many([image], tags=np.array([tag], np.uint64), notify=True)[0])
-        except BaseException:
+        # one image: the same C entry point as submit_many, without its array plumbing
+        ptr = C.c_void_p(a.__array_interface__["data"][0])
+        tag_c, ticket = C.c_uint64(tag), C.c_uint64()
+        rc = self._fn_submit_many(self._h, C.byref(ptr), 1, a.shape[0], a.shape[1], a.shape[2], a.strides[0],
+                                  C.byref(tag_c), 1, C.byref(ticket))
+        if rc != L.OK:
             with self._pend_lock:
                 self._pending.pop(tag, None)
-            raise
+            L.check(rc)
+        p.ticket = ticket.value
         return p
 
     def classify_many_later(self, images, then=None):
@@ -195,27 +240,34 @@ class _Base:
                 return
             self._pend_lock = threading.Lock()
             self._pending, self._pend_seq = {}, 0
+            self._fn_submit_many = self._fn("submit_many")
             self._reaper_stop = False
             self._reaper = threading.Thread(target=self._reap, daemon=True, name="ai4e-reaper")
             self._reaper.start()
 
     def _reap(self):
+        cap = 1024
+        tg, st = np.empty(cap, np.uint64), np.empty(cap, np.int32)
+        idx, prob = self._results(cap)
+        n_c = C.c_int()
+        poll, args = self._fn("poll"), (cap, 50_000, None, _vp(tg), _vp(st), _vp(idx), _vp(prob), C.byref(n_c))
         while not self._reaper_stop:
-            try:
-                tk, tg, st, idx, prob = self.poll(512, 0.05)
-            except Exception:  # noqa: BLE001 - the handle went away under us: stop
+            if poll(self._h, *args) != L.OK:  # the handle went away under us: stop
                 return
-            if not len(tk):
+            n = n_c.value
+            if not n:
                 continue
+            tags, status = tg[:n].tolist(), st[:n].tolist()
+            ii, pp = idx[:n].copy(), prob[:n].copy()  # rows handed to the callbacks outlive the next poll
             with self._pend_lock:
-                ps = [self._pending.pop(t, None) for t in tg.tolist()]
+                ps = [self._pending.pop(t, None) for t in tags]
             for i, p in enumerate(ps):
                 if p is None:
                     continue
-                if st[i] == L.OK:
-                    p._resolve(idx[i].copy(), prob[i].copy(), None)
+                if status[i] == L.OK:
+                    p._resolve(ii[i], pp[i], None)
                 else:
-                    p._resolve(None, None, L.Ai4eError(int(st[i]), "the micro-batch of this task failed on the GPU"))
+                    p._resolve(None, None, L.Ai4eError(status[i], "the micro-batch of this task failed on the GPU"))
 
     def _stop_reaper(self):
         r = getattr(self, "_reaper", None)

@@ -451,8 +451,10 @@ def main():
         # BASELINE.json configs[2] on this GPU: tasks through the drop-in APIService async endpoint
         try:
             from tools import async_bench
-            out["async_path"] = {m: async_bench.measure(1, m, args.async_seconds, 32 if m != "native" else 4, devices=[local_rank])
+            out["async_path"] = {m: async_bench.measure(1, m, args.async_seconds, 8 if m != "native" else 4, devices=[local_rank])
                                  for m in ("later", "native")}
+            out["async_path"]["later_16_images_per_task"] = async_bench.measure(1, "later", args.async_seconds, 8,
+                                                                                devices=[local_rank], per_task=16)
             out["async_path"]["shell_only"] = async_bench.measure(1, "shell_only", min(2.0, args.async_seconds), 8)
         except Exception as err:  # noqa: BLE001 - the headline numbers above stand on their own
             out["async_path"] = {"error": repr(err)}

@@ -15,6 +15,8 @@ Modes (what the task function does with the image):
   shell_only  no engine at all (the task completes at once): the host shell's own ceiling in Python
   native      no shell: feeder threads hand batches to Pool.submit_many and one thread drains
               Pool.poll - what the C side of the dispatcher sustains behind the Python shell
+`--images-per-task K` lets one task body carry K images (batch-style APIs): the per-task cost of the
+Python shell is then paid once per K images.
 
 The clients call the WSGI application directly with a prebuilt environ (what a WSGI server hands
 over after parsing a request); `werkzeug.test.Client` costs more per request than the shell does.
@@ -55,7 +57,7 @@ class _NullLog:
         pass
 
 
-def build_service(engine, mode, store):
+def build_service(engine, mode, store, per_task=1):
     """the API project: an unmodified-signature async endpoint over the engine."""
     os.environ.setdefault("AI4E_B200_MAX_WORKERS", "2048")
     from ai4e_b200.compat.miniflask import Flask
@@ -67,16 +69,21 @@ def build_service(engine, mode, store):
     svc.api_task_manager = tm
 
     def read_image(request):
-        return {"image": np.frombuffer(request.get_data(), np.uint8).reshape(HW, HW, IN_C)}
+        a = np.frombuffer(request.get_data(), np.uint8)
+        return {"image": a.reshape(HW, HW, IN_C)} if per_task == 1 else {"images": a.reshape(per_task, HW, HW, IN_C)}
 
     @svc.api_async_func(api_path=PATH, methods=["POST"], request_processing_function=read_image,
                         maximum_concurrent_requests=1 << 20, content_types=["application/octet-stream"],
-                        content_max_length=1 << 20, trace_name="post:classify")
+                        content_max_length=1 << 26, trace_name="post:classify")
     def classify(*args, **kwargs):
         tid = kwargs["taskId"]
         tm.UpdateTaskStatus(tid, "running")
         if mode == "shell_only":
             tm.CompleteTask(tid, "completed - []")
+        elif per_task > 1:  # a task that carries several images (camera-trap style batches): one C call, one completion
+            from ai4e_b200.engine import Pending
+            return Pending.gather(engine.classify_many_later(kwargs["images"]),
+                                  then=lambda idx, prob: tm.CompleteTask(tid, "completed - " + json.dumps(idx[:, 0].tolist())))
         elif mode == "blocked":
             idx, prob = engine.classify(kwargs["image"])
             tm.CompleteTask(tid, "completed - " + json.dumps(idx.tolist()))
@@ -87,10 +94,10 @@ def build_service(engine, mode, store):
     return app, svc, tm
 
 
-def run_shell(engine, mode, seconds, clients, inflight, images):
+def run_shell(engine, mode, seconds, clients, inflight, images, per_task=1):
     from task_management.local_task_store import LocalTaskStore
     store = LocalTaskStore()
-    app, svc, tm = build_service(engine, mode, store)
+    app, svc, tm = build_service(engine, mode, store, per_task)
     t_post, lat, lock = {}, [], threading.Lock()
     slots = threading.Semaphore(inflight)
     counted = [False]
@@ -112,7 +119,10 @@ def run_shell(engine, mode, seconds, clients, inflight, images):
                 "wsgi.version": (1, 0), "wsgi.url_scheme": "http", "wsgi.errors": sys.stderr,
                 "wsgi.multithread": True, "wsgi.multiprocess": False, "wsgi.run_once": False,
                 "CONTENT_TYPE": "application/octet-stream", "HTTP_HOST": "container"}
-    bodies = [im.tobytes() for im in images]
+    if per_task == 1:
+        bodies = [im.tobytes() for im in images]
+    else:
+        bodies = [images[(np.arange(per_task) + k * per_task) % len(images)].tobytes() for k in range(max(1, 64 // per_task))]
     stop = [False]
     posted = [0] * clients
     bad = []
@@ -158,7 +168,8 @@ def run_shell(engine, mode, seconds, clients, inflight, images):
     while t_post and time.time() < deadline:
         time.sleep(0.01)
     p50, p99 = _percentiles(done_lat)
-    return {"tasks_per_s": n_done / dt, "tasks": n_done, "seconds": dt, "p50_ms": p50, "p99_ms": p99,
+    return {"tasks_per_s": n_done / dt, "images_per_s": n_done * per_task / dt, "images_per_task": per_task,
+            "tasks": n_done, "seconds": dt, "p50_ms": p50, "p99_ms": p99,
             "latency_of": "POST with taskId header -> CompleteTask written to the store", "rejected": len(bad),
             "store_upserts": store.upserts, "store_gets": store.gets}
 
@@ -218,12 +229,13 @@ def run_native(engine, seconds, feeders, batch, images):
         t.join(timeout=2)
     rp.join(timeout=5)
     p50, p99 = _percentiles(l)
-    return {"tasks_per_s": n / dt, "tasks": n, "seconds": dt, "p50_ms": p50, "p99_ms": p99,
+    return {"tasks_per_s": n / dt, "images_per_s": n / dt, "images_per_task": 1, "tasks": n, "seconds": dt,
+            "p50_ms": p50, "p99_ms": p99,
             "latency_of": f"submit_many({batch}) -> last image of the call announced by poll"}
 
 
 def measure(gpus: int, mode: str, seconds: float, clients: int, inflight: int | None = None, max_batch: int = 64,
-            max_wait_us: int = 2000, devices=None, arch: str = "resnet50") -> dict:
+            max_wait_us: int = 2000, devices=None, arch: str = "resnet50", per_task: int = 1) -> dict:
     from ai4e_b200.engine import Pool
     from ai4e_b200.models import build_resnet_program, synthetic_state_dict
     rng = np.random.default_rng(1234)
@@ -241,8 +253,8 @@ def measure(gpus: int, mode: str, seconds: float, clients: int, inflight: int | 
         if mode == "native":
             out.update(run_native(pool, seconds, clients, max_batch, images))
         else:
-            inflight = inflight or 256 * gpus
-            out.update(run_shell(pool, mode, seconds, clients, inflight, images))
+            inflight = inflight or max(2 * max_batch * gpus // per_task, 2 * gpus)
+            out.update(run_shell(pool, mode, seconds, clients, inflight, images, per_task))
             out["inflight_limit"] = inflight
         st = pool.stats()
         out["batch_hist"] = np.sum([s["batch_hist"] for s in st], axis=0).tolist()
@@ -260,9 +272,11 @@ def main():
     ap.add_argument("--mode", default="later", choices=["blocked", "later", "shell_only", "native"])
     ap.add_argument("--max-batch", type=int, default=64)
     ap.add_argument("--max-wait-us", type=int, default=2000)
+    ap.add_argument("--images-per-task", type=int, default=1,
+                    help="images carried by one task body (shell modes); 1 = BASELINE's one image per task")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
-    r = measure(a.gpus, a.mode, a.seconds, a.clients, a.inflight, a.max_batch, a.max_wait_us)
+    r = measure(a.gpus, a.mode, a.seconds, a.clients, a.inflight, a.max_batch, a.max_wait_us, per_task=a.images_per_task)
     r["cores"] = os.cpu_count()
     print(json.dumps(r), flush=True)
     if a.out:

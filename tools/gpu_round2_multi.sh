@@ -1,0 +1,26 @@
+#!/bin/bash
+# multi-GPU visit: N = $1 GPUs of one box.  One Pool over N GPUs in ONE process (async path, land-cover,
+# open loop), the pool test, and the torchrun bench for comparison.
+N=${1:-2}
+mkdir -p gpurun_out
+nvidia-smi topo -m > gpurun_out/m${N}_topo.txt 2>&1
+timeout 300 python -m pytest tests/test_gpu_dispatch.py -m gpu -x -q -k "two_gpus or pool_bulk" 2>&1 | tail -3
+timeout 200 python tools/async_bench.py --gpus $N --mode native --seconds 5 --clients $((N*2)) --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 200 python tools/async_bench.py --gpus $N --mode later --seconds 5 --clients 8 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 200 python tools/async_bench.py --gpus $N --mode later --seconds 5 --clients 8 --images-per-task 16 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 200 python tools/async_bench.py --gpus $N --mode blocked --seconds 5 --clients 64 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 300 python tools/landcover_bench.py --gpus $N --seconds 4 --classify-rate 77000 --out gpurun_out/m${N}_landcover.jsonl 2>&1 | tail -4 | cut -c1-300
+PEAK=$(python - <<PY
+import json
+rows=[json.loads(l) for l in open('gpurun_out/m${N}_async.jsonl')]
+print(int([r for r in rows if r['mode']=='native'][0]['tasks_per_s']))
+PY
+)
+timeout 200 python tools/openloop_bench.py --gpus $N --peak $PEAK --load 0.5 0.8 --seconds 4 --out gpurun_out/m${N}_openloop.jsonl 2>&1 | tail -2 | cut -c1-420
+timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 60 --warmup 5 --sustained-seconds 3 > gpurun_out/m${N}_bench.json 2> gpurun_out/m${N}_bench.err
+python - <<PY
+import json
+try:
+    d=json.load(open('gpurun_out/m${N}_bench.json')); print('torchrun N=${N}: value', round(d['value']), 'e2e', round(d['e2e']['value']), 'sustained', round(d['sustained']['value']), round(d['sustained']['e2e']))
+except Exception as e: print('bench parse failed', e)
+PY
