@@ -18,6 +18,7 @@ CONV_AUTO, CONV_IGEMM, CONV_DIRECT = 0, 1, 2
 OP_CONV, OP_MAXPOOL, OP_HEAD = 0, 1, 2
 TOPK = 5
 HEAD_NOALLOC_MAX_FLOATS = 64 * 2048
+IMAGE_UNKNOWN, IMAGE_JPEG, IMAGE_PNG = 0, 1, 2
 
 
 class Ai4eLibraryError(RuntimeError):
@@ -75,6 +76,8 @@ SIGNATURES = {
     "ai4e_jpeg_entropy_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(JpegInfo)]),
     "ai4e_jpeg_reconstruct": (_i, [_vp, _i, C.POINTER(JpegInfo), _vp, _vp, _vp]),
     "ai4e_jpeg_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), _vp]),
+    "ai4e_png_decode": (_i, [_vp, _u64, _vp, _u64, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "ai4e_image_probe": (_i, [_vp, _u64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "ai4e_bottleneck_tail": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp]),
     "ai4e_maxpool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ai4e_head": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),
@@ -85,6 +88,8 @@ SIGNATURES = {
     "ai4e_engine_forward_device": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "ai4e_engine_submit": (_i, [_vp, _vp, _i, _i, _i, _i, _u64, _u64p]),
     "ai4e_engine_submit_jpeg": (_i, [_vp, _vp, _u64, _u64, C.POINTER(_u64)]),
+    "ai4e_engine_submit_image": (_i, [_vp, _vp, _u64, _u64, C.POINTER(_u64)]),
+    "ai4e_pool_submit_image": (_i, [_vp, _vp, _u64, _u64, _u64p]),
     "ai4e_engine_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
     "ai4e_engine_profile": (_i, [_vp, _vp, _i, _i, _i, _i, _fp, _i]),
     "ai4e_engine_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),

@@ -125,6 +125,19 @@ class Pending:
                     pass
 
 
+def require_decodable(data: bytes):
+    """For a `request_processing_function`: returns ("jpeg" | "png", height, width) when the engine can
+    decode the payload and otherwise ends the request with 415 Unsupported Media Type - while the
+    request is still open, instead of accepting a task that can only fail later (the reference's
+    content gate, ai4e_service.py:127-129, sees the MIME type only)."""
+    from . import ops
+    try:
+        return ops.image_probe(data)
+    except L.Ai4eError as e:
+        from werkzeug.exceptions import UnsupportedMediaType
+        raise UnsupportedMediaType(description=str(e)) from e
+
+
 class _Base:
     """what Engine and Pool share: both C handles answer the same calls under two prefixes."""
     _h = None
@@ -302,6 +315,19 @@ class _Base:
     def classify(self, image, want_logits: bool = False):
         """submit + wait for one image: the call a user `func` makes."""
         return self.wait(self.submit(image), want_logits)
+
+    def submit_encoded(self, data: bytes, tag: int = 0) -> int:
+        """one encoded image (baseline JPEG or 8-bit PNG, sniffed from its first bytes) -> ticket.
+        The sequential part of the decode (Huffman / inflate + un-filter) runs on this thread with
+        the GIL released.  Unsupported payloads raise Ai4eError(ERR_UNSUPPORTED) and queue nothing."""
+        buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+        t = C.c_uint64()
+        L.check(self._fn("submit_image")(self._h, buf, len(data), tag, C.byref(t)))
+        return t.value
+
+    def classify_encoded(self, data: bytes, want_logits: bool = False):
+        """blocking: submit_encoded + wait."""
+        return self.wait(self.submit_encoded(data), want_logits)
 
     def submit_tile(self, tile_u8_hwc: np.ndarray, chip: int = 256) -> np.ndarray:
         """every chip x chip chip of a [H, W, C] uint8 tile (row-major over the chip grid) in one C

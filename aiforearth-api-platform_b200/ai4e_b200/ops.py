@@ -91,6 +91,28 @@ def conv_layer(x_nhwc: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tens
     return out
 
 
+def png_decode(data: bytes):
+    """host only: PNG bytes -> uint8 [H, W, 3] RGB, what Pillow's `Image.open(...).convert("RGB")` gives."""
+    import numpy as np
+    lib = L.load()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    h, w = C.c_int32(), C.c_int32()
+    L.check(lib.ai4e_png_decode(buf, len(data), None, 0, C.byref(h), C.byref(w)))
+    out = np.empty((h.value, w.value, 3), np.uint8)
+    L.check(lib.ai4e_png_decode(buf, len(data), out.ctypes.data_as(C.c_void_p), out.nbytes, C.byref(h), C.byref(w)))
+    return out
+
+
+def image_probe(data: bytes):
+    """host only, headers only: ("jpeg" | "png", height, width) when the engine can decode the payload;
+    raises Ai4eError(ERR_UNSUPPORTED) otherwise.  See `require_decodable` for the 415 answer."""
+    lib = L.load()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    kind, h, w = C.c_int32(), C.c_int32(), C.c_int32()
+    L.check(lib.ai4e_image_probe(buf, len(data), C.byref(kind), C.byref(h), C.byref(w)))
+    return {L.IMAGE_JPEG: "jpeg", L.IMAGE_PNG: "png"}[kind.value], h.value, w.value
+
+
 def jpeg_entropy_decode(data: bytes):
     """host only: baseline JPEG bytes -> (JpegInfo, int16 record [3 x 64 quantisation values, then
     the quantised coefficients per component, natural order]).  Raises Ai4eError for unsupported

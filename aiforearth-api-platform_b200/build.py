@@ -72,7 +72,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
         objs = list(ex.map(compile_one, srcs))
-    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-cudart", "static", "-lpthread", "-ldl"]
+    cmd = [nvcc, "-shared", "-o", LIB, *objs, "-cudart", "static", "-lpthread", "-ldl", "-lz"]  # zlib: PNG inflate (png.cu)
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")

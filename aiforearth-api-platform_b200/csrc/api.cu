@@ -61,6 +61,36 @@ int ai4e_preprocess_tile(const uint8_t* d_tile, int tile_h, int tile_w, int chan
   return rc < 0 ? rc : AI4E_OK;
 }
 
+int ai4e_png_decode(const uint8_t* png, uint64_t len, uint8_t* h_rgb_hwc, uint64_t capacity_bytes, int32_t* out_height,
+                    int32_t* out_width) {
+  int h = 0, w = 0;
+  const int rc = png_host_decode(png, len, h_rgb_hwc, capacity_bytes, &h, &w);
+  if (out_height) *out_height = h;
+  if (out_width) *out_width = w;
+  return rc;
+}
+
+int ai4e_image_probe(const uint8_t* data, uint64_t len, int32_t* out_kind, int32_t* out_height, int32_t* out_width) {
+  AI4E_REQUIRE(data && out_kind && out_height && out_width, "image_probe: null pointer");
+  *out_kind = AI4E_IMAGE_UNKNOWN; *out_height = *out_width = 0;
+  if (len >= 3 && data[0] == 0xFF && data[1] == 0xD8) {
+    ai4e_jpeg_info info;
+    const int rc = jpeg_host_decode(data, len, nullptr, 0, &info);
+    if (rc) return rc;
+    *out_kind = AI4E_IMAGE_JPEG; *out_height = info.height; *out_width = info.width;
+    return AI4E_OK;
+  }
+  if (len >= 8 && data[0] == 0x89 && data[1] == 'P' && data[2] == 'N' && data[3] == 'G') {
+    int h = 0, w = 0;
+    const int rc = png_host_decode(data, len, nullptr, 0, &h, &w);
+    if (rc) return rc;
+    *out_kind = AI4E_IMAGE_PNG; *out_height = h; *out_width = w;
+    return AI4E_OK;
+  }
+  set_last_error("image_probe: neither a JPEG nor a PNG stream (first bytes %02x %02x)", len > 0 ? data[0] : 0, len > 1 ? data[1] : 0);
+  return AI4E_ERR_UNSUPPORTED;
+}
+
 int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
                     const void* d_weight_krsc, const float* d_bias, int cout, int kh, int kw,
                     int stride, int pad, const void* d_residual_or_null, int relu,

@@ -1052,6 +1052,29 @@ int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, u
   return AI4E_OK;
 }
 
+// An encoded payload of either supported format: a JPEG goes the hybrid K0 way, a PNG is inflated and
+// un-filtered on this thread (lossless: nothing for the GPU to do) and its pixels take the plain path.
+int ai4e_engine_submit_image(ai4e_engine* e, const uint8_t* data, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
+  AI4E_REQUIRE(e && data && out_ticket, "submit_image: null pointer");
+  if (len >= 3 && data[0] == 0xFF && data[1] == 0xD8) return ai4e_engine_submit_jpeg(e, data, len, tag, out_ticket);
+  if (len >= 8 && data[0] == 0x89 && data[1] == 'P' && data[2] == 'N' && data[3] == 'G') {
+    AI4E_REQUIRE(e->desc.in_c == 3, "submit_image: the model takes %d channels, a PNG decodes to 3", e->desc.in_c);
+    int h = 0, w = 0;
+    int rc = png_host_decode(data, len, nullptr, 0, &h, &w);
+    if (rc) return rc;
+    const size_t bytes = (size_t)h * w * 3;
+    AI4E_REQUIRE(bytes <= e->slot_bytes, "submit_image: a %d x %d image needs %zu bytes of staging, the slot holds %zu (AI4E_B200_MAX_SRC_BYTES)",
+                 w, h, bytes, e->slot_bytes);
+    thread_local std::vector<uint8_t> px;
+    if (px.size() < bytes) px.resize(bytes);
+    rc = png_host_decode(data, len, px.data(), px.size(), &h, &w);
+    if (rc) return rc;
+    return ai4e_engine_submit(e, px.data(), h, w, 3, 0, tag, out_ticket);
+  }
+  set_last_error("submit_image: neither a JPEG nor a PNG stream");
+  return AI4E_ERR_UNSUPPORTED;
+}
+
 int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count, int h, int w, int c,
                              uint64_t* out_first_ticket) {
   AI4E_REQUIRE(e && h_images && out_first_ticket, "submit_batch: null pointer");
@@ -1456,6 +1479,16 @@ int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint6
   POOL_PICK_OR_FAIL("pool_submit_jpeg");
   uint64_t t = 0;
   int rc = ai4e_engine_submit_jpeg(p->engines[best], jpeg, len, tag, &t);
+  if (rc) return rc;
+  *out_ticket = ((uint64_t)best << 56) | (t & kLocalMask);
+  return AI4E_OK;
+}
+
+int ai4e_pool_submit_image(ai4e_pool* p, const uint8_t* data, uint64_t len, uint64_t tag, uint64_t* out_ticket) {
+  AI4E_REQUIRE(p && out_ticket, "pool_submit_image: null pointer");
+  POOL_PICK_OR_FAIL("pool_submit_image");
+  uint64_t t = 0;
+  int rc = ai4e_engine_submit_image(p->engines[best], data, len, tag, &t);
   if (rc) return rc;
   *out_ticket = ((uint64_t)best << 56) | (t & kLocalMask);
   return AI4E_OK;

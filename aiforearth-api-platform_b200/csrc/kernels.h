@@ -30,6 +30,9 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
 int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry, uint8_t* d_scratch,
                      uint8_t* d_out, cudaStream_t stream, const float* norm_mean_std = nullptr);
 
+// ---- PNG (png.cu): host only; rgb == nullptr sizes the output
+int png_host_decode(const uint8_t* data, uint64_t len, uint8_t* rgb, uint64_t capacity, int* out_h, int* out_w);
+
 // ---- direct convolution on CUDA cores (conv_direct.cu)
 int launch_conv_direct(const void* in, int N, int H, int W, int Cin, const void* weight,
                        const float* bias, int Cout, int R, int S, int stride, int pad,

@@ -151,6 +151,26 @@ AI4E_API int ai4e_jpeg_reconstruct(const int16_t* d_records, int batch, const ai
 AI4E_API int ai4e_jpeg_decode(const uint8_t* jpeg, uint64_t len, uint8_t* d_rgb_hwc, uint64_t capacity_bytes,
                               int32_t* out_height, int32_t* out_width, void* stream);
 
+/* PNG payloads.  PNG is lossless: chunk walk, zlib inflate and the scan-line filters
+ * run on the calling thread's host core and there is no arithmetic for the GPU; the pixels then take
+ * the ordinary submit path.  Output = `Image.open(BytesIO(data)).convert("RGB")` of Pillow, bit for
+ * bit (the decode inside the callback at APIs/1.0/base-py/ai4e_service.py:203).  8-bit grey / RGB /
+ * palette, with or without alpha, non-interlaced; anything else -> AI4E_ERR_UNSUPPORTED.
+ * h_rgb_hwc == NULL only reports the size. */
+AI4E_API int ai4e_png_decode(const uint8_t* png, uint64_t len, uint8_t* h_rgb_hwc, uint64_t capacity_bytes,
+                             int32_t* out_height, int32_t* out_width);
+
+/* Admission check for an encoded payload, host only, headers only: AI4E_OK with the format and size
+ * when the engine can decode it, AI4E_ERR_UNSUPPORTED otherwise (progressive / CMYK JPEG, 16-bit or
+ * interlaced PNG, any other format).  A request_processing_function calls it while the request is
+ * still open and answers 415 instead of accepting a task that could only fail - the content gate
+ * of APIs/1.0/base-py/ai4e_service.py:127-129 only looks at the MIME type. */
+#define AI4E_IMAGE_UNKNOWN 0
+#define AI4E_IMAGE_JPEG 1
+#define AI4E_IMAGE_PNG 2
+AI4E_API int ai4e_image_probe(const uint8_t* data, uint64_t len, int32_t* out_kind, int32_t* out_height,
+                              int32_t* out_width);
+
 /* K4b.  The tail of a ResNet bottleneck block in one kernel:
  *   y = relu(conv_khxkw(x; w2) + bias2)       [batch][p][q][cmid]   (conv2 + bn2 + relu, BN folded)
  *   z = relu(y * w3^T + bias3 + residual)     [batch][p][q][cout]   (conv3 1x1 + bn3 + add + relu)
@@ -292,6 +312,10 @@ AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, i
  * the callback at APIs/1.0/base-py/ai4e_service.py:203. */
 AI4E_API int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag,
                                      uint64_t* out_ticket);
+/* An encoded payload of either supported format (sniffed from its first bytes): JPEG as
+ * ai4e_engine_submit_jpeg, PNG decoded on the calling thread and submitted as pixels. */
+AI4E_API int ai4e_engine_submit_image(ai4e_engine* e, const uint8_t* data, uint64_t len, uint64_t tag,
+                                      uint64_t* out_ticket);
 /* A tile cut into chip x chip chips (row-major over the chip grid; the remainder at the right /
  * bottom is ignored), in one call: tile -> chips -> classify of the land-cover case (BASELINE.json
  * configs[3]; the reference chains such stages through AddPipelineTask,
@@ -346,6 +370,8 @@ AI4E_API int ai4e_pool_submit(ai4e_pool* p, const uint8_t* h_hwc, int h, int w, 
                      uint64_t tag, uint64_t* out_ticket);
 AI4E_API int ai4e_pool_submit_jpeg(ai4e_pool* p, const uint8_t* jpeg, uint64_t len, uint64_t tag,
                                    uint64_t* out_ticket);
+AI4E_API int ai4e_pool_submit_image(ai4e_pool* p, const uint8_t* data, uint64_t len, uint64_t tag,
+                                    uint64_t* out_ticket);
 /* The ai4e_engine_* calls of the same name behind the dispatcher.  submit_many deals the images to
  * the replicas in runs, submit_batch gives the whole batch to one replica (tickets consecutive),
  * submit_tile deals contiguous chip ranges, one per healthy replica (256 chips on 8 GPUs: 32 each)
