@@ -163,26 +163,6 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* tma
       "h"(off_w), "h"(off_h)
       : "memory");
 }
-// multicast variants: the tile lands at the same shared-memory offset in every CTA of the cluster
-// whose bit is set in `mask`, and completes bytes on the mbarrier at the same offset there
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const void* tmap, uint32_t bar, int x, int y,
-                                               uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(x), "r"(y), "h"(mask)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_im2col_4d_mc(uint32_t dst, const void* tmap, uint32_t bar, int c, int w,
-                                                      int h, int n, uint16_t off_w, uint16_t off_h,
-                                                      uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes.multicast::cluster"
-      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8}, %9;"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n),
-      "h"(off_w), "h"(off_h), "h"(mask)
-      : "memory");
-}
 // L2 prefetch of a 2-D tile (no shared-memory destination, no completion signal)
 __device__ __forceinline__ void tma_prefetch_l2_2d(const void* tmap, int x, int y) {
   asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
