@@ -154,7 +154,21 @@ class _Base:
         """`images`: a uint8 [N,H,W,C] array or a sequence of equal-sized uint8 HWC arrays -> uint64
         tickets [N], in ONE C call.  `tags` (uint64 [N]) come back from `poll`; with `notify` every
         ticket is announced there when its batch has finished."""
-        if isinstance(images, np.ndarray) and images.ndim == 4:
+        if isinstance(images, tuple):
+            # (stack, index): images stack[index[0]], stack[index[1]], ... - pointers by vector arithmetic,
+            # no per-image Python work (what a load generator or a frame ring uses)
+            a, pick = images
+            if a.dtype != np.uint8 or a.ndim != 4 or not a.flags.c_contiguous:
+                raise ValueError("expected a C-contiguous uint8 [N,H,W,C] stack")
+            pick = np.asarray(pick, np.int64)
+            if pick.size and (pick.min() < 0 or pick.max() >= a.shape[0]):
+                raise IndexError("submit_many: index outside the stack")
+            n, (h, w, c) = pick.size, a.shape[1:]
+            if n == 0:
+                return np.empty(0, np.uint64)
+            ptrs = (np.uint64(a.ctypes.data) + pick.astype(np.uint64) * np.uint64(a.strides[0]))
+            row_stride, keep = a.strides[1], a
+        elif isinstance(images, np.ndarray) and images.ndim == 4:
             a = images
             if a.dtype != np.uint8:
                 raise ValueError("expected uint8 images")

@@ -56,6 +56,11 @@ struct FusedCfg {
   static constexpr int kAcc2Col = 2 * N1;                 // acc1: [0, 2 N1), acc2: two 128-column buffers after it
   static constexpr int kTmemCols = 512;
   static constexpr int kE1Warps = 4 * (kKB2 < 2 ? kKB2 : 2);  // epilogue warps that take part in step 2
+  // Cmid = 128: the two K blocks of a w3 pass travel in ONE stage (A slot + B slot, 16 KiB each).  The
+  // ring is latency-bound (a slot takes ~3100 cycles to go round, 4 stages fit), so what counts is the
+  // number of stage fills per pixel tile: 18 + 4 instead of 18 + 8.
+  static constexpr bool kPackW3 = kKB2 == 2 && kBBytes == kABytes;
+  static constexpr int kUnitsPerPass = kPackW3 ? 1 : kKB2;
 };
 
 template <int N1>
@@ -133,7 +138,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     const int t = (int)blockIdx.x + i * (int)gridDim.x;
     return (p.reverse ? p.num_tiles - 1 - t : t) * kBlockM;
   };
-  const int units2 = passes * kKB2;  // w3 tiles per pixel tile
+  const int units2 = passes * Cfg::kUnitsPerPass;  // ring stages the second GEMM of a pixel tile takes
 
   if (warp == 0) {
     // ------------------- producer: A tiles (im2col) of the first GEMM, w3 tiles of the second ----
@@ -170,8 +175,11 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           mbar_wait(empty_bar(stage), phase ^ 1u);
           if (elect_one()) {
             mbar_expect_tx(full_bar(stage), kABytes);
-            tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), (u % kKB2) * kBlockK,
-                        (u / kKB2) * 128);
+            if constexpr (Cfg::kPackW3)  // K block 0 of pass u here, K block 1 in the B slot (the other producer)
+              tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), 0, u * 128);
+            else
+              tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), (u % kKB2) * kBlockK,
+                          (u / kKB2) * 128);
           }
           __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -197,7 +205,14 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       if (st >= 1) {
         for (int u = 0; u < units2; ++u) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (elect_one()) mbar_arrive(full_bar(stage));
+          if (elect_one()) {
+            if constexpr (Cfg::kPackW3) {
+              mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
+              tma_load_2d(smem_base + stage * Cfg::kStageBytes + kABytes, &tmap_w3, full_bar(stage), kBlockK, u * 128);
+            } else {
+              mbar_arrive(full_bar(stage));
+            }
+          }
           __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -242,14 +257,24 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           mbar_wait(acc2_empty(b), ((gp >> 1) & 1u) ^ 1u);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + Cfg::kAcc2Col + b * 128;
-          for (int kb = 0; kb < kKB2; ++kb) {
+          for (int kb = 0; kb < Cfg::kUnitsPerPass; ++kb) {
             mbar_wait(full_bar(stage), phase);
             tc_fence_after();
             if (elect_one()) {
-              const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kb * kChunkBytes, 128, 2);
-              const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes, 128, 2);
+              if constexpr (Cfg::kPackW3) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+                for (int kk = 0; kk < 2; ++kk) {  // both K blocks of the pass sit in this stage
+                  const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kk * kChunkBytes, 128, 2);
+                  const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes + kk * kABytes, 128, 2);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kk | k) != 0 ? 1u : 0u);
+                }
+              } else {
+                const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kb * kChunkBytes, 128, 2);
+                const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes, 128, 2);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+              }
               umma_commit(empty_bar(stage));
             }
             __syncwarp();
