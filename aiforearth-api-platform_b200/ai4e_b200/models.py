@@ -61,6 +61,7 @@ class Program:
     n_bufs: int = 0
     blob: bytes = b""
     stage_bufs: dict = field(default_factory=dict)  # stage name -> (slot, h, w, c) for parity tests
+    keep_stages: bool = False  # every layer's output stays in memory (the engine then fuses nothing across layers' outputs)
 
     def to_ctypes(self):
         arr = (L.LayerDesc * len(self.layers))()
@@ -72,6 +73,7 @@ class Program:
         md.n_bufs = self.n_bufs
         md.in_h, md.in_w, md.in_c, md.in_c_pad = self.in_h, self.in_w, self.in_c, self.in_c_pad
         md.num_classes = self.num_classes
+        md.reserved = 1 if self.keep_stages else 0
         for i in range(4):
             md.mean[i] = float(self.mean[i]) if i < len(self.mean) else 0.0
             md.std[i] = float(self.std[i]) if i < len(self.std) else 1.0
@@ -153,7 +155,7 @@ def build_resnet_program(arch: str, state_dict: dict, in_h: int = 224, in_w: int
     if std is None:
         std = IMAGENET_STD if in_c == 3 else IMAGENET_STD + (0.25,)
     num_classes = int(sd["fc.weight"].shape[0])
-    prog = Program(arch, in_h, in_w, in_c, 4, num_classes, tuple(mean), tuple(std))
+    prog = Program(arch, in_h, in_w, in_c, 4, num_classes, tuple(mean), tuple(std), keep_stages=keep_stages)
     blob = _Blob()
     slots_in_use = {0}
     pinned = set()

@@ -174,6 +174,19 @@ def bottleneck_tail(x_nhwc: torch.Tensor, w2_krsc: torch.Tensor, b2: torch.Tenso
     return out
 
 
+def stem_pool(x_nhwc4: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tensor, relu: bool = True, stream=None) -> torch.Tensor:
+    """7x7/2 stem + bias (+ ReLU) + 3x3/2 max-pool in one kernel: x [B,H,W,4] bf16, weight [64,7,7,4] bf16,
+    bias [64] fp32 -> [B,H/4,W/4,64] bf16; bit-identical to conv_layer followed by maxpool."""
+    lib = L.load()
+    assert x_nhwc4.is_contiguous() and x_nhwc4.dtype == torch.bfloat16 and x_nhwc4.shape[3] == 4
+    assert weight_krsc.is_contiguous() and tuple(weight_krsc.shape) == (64, 7, 7, 4) and weight_krsc.dtype == torch.bfloat16
+    b, h, w, _ = x_nhwc4.shape
+    out = torch.empty((b, h // 4, w // 4, 64), dtype=torch.bfloat16, device=x_nhwc4.device)
+    L.check(lib.ai4e_stem_pool(_ptr(x_nhwc4), b, h, w, _ptr(weight_krsc), _ptr(bias), int(relu), _ptr(out),
+                               _stream_ptr(stream)))
+    return out
+
+
 def maxpool(x_nhwc: torch.Tensor, k: int = 3, stride: int = 2, pad: int = 1, stream=None) -> torch.Tensor:
     lib = L.load()
     assert x_nhwc.is_contiguous() and x_nhwc.dtype == torch.bfloat16

@@ -154,6 +154,30 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 
+int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, const void* d_weight_krsc, const float* d_bias,
+                   int relu, void* d_out_nhwc, void* stream) {
+  AI4E_REQUIRE(d_in_nhwc4 && d_weight_krsc && d_bias && d_out_nhwc && batch > 0, "stem_pool: bad arguments");
+  if (!stem_pool_supported(h, w, 4, 64, 7, 7, 2, 3, 3, 2, 1)) {
+    set_last_error("stem_pool: input %d x %d is not supported (width a multiple of 16 and at most 256, height a multiple of 4)", h, w);
+    return AI4E_ERR_UNSUPPORTED;
+  }
+  // like the stem branch of ai4e_conv_layer this stateless entry repacks the weights on every call
+  cudaStream_t s = (cudaStream_t)stream;
+  std::vector<uint16_t> w_in(64 * 7 * 7 * 4), w_sp((size_t)stem_pool_weight_elems());
+  AI4E_CUDA_TRY(cudaMemcpyAsync(w_in.data(), d_weight_krsc, w_in.size() * 2, cudaMemcpyDeviceToHost, s));
+  AI4E_CUDA_TRY(cudaStreamSynchronize(s));
+  stem_pool_repack_weights(w_in.data(), w_sp.data());
+  void* d_sp = nullptr;
+  AI4E_CUDA_TRY(cudaMallocAsync(&d_sp, w_sp.size() * 2, s));
+  AI4E_CUDA_TRY(cudaMemcpyAsync(d_sp, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice, s));
+  AI4E_CUDA_TRY(cudaStreamSynchronize(s));
+  StemPoolPlan plan;
+  int rc = stem_pool_make_plan(&plan, d_in_nhwc4, batch, h, w, d_sp, d_bias, relu, d_out_nhwc);
+  if (rc == AI4E_OK) rc = stem_pool_launch(plan, batch, s);
+  cudaFreeAsync(d_sp, s);
+  return rc;
+}
+
 int ai4e_jpeg_entropy_decode(const uint8_t* jpeg, uint64_t len, int16_t* h_record, uint64_t capacity_int16,
                              ai4e_jpeg_info* out) {
   return jpeg_host_decode(jpeg, len, h_record, capacity_int16, out);

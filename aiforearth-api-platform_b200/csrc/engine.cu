@@ -46,6 +46,8 @@ struct LayerRt {
   bool fused_first = false;  // this layer and the next run as one bottleneck_tail_kernel (fplan)
   bool fused_second = false; // computed by the previous layer's launch
   FusedPlan fplan;
+  bool stem_pool = false;    // this stem convolution and the max-pool behind it run as one stem_pool_kernel (splan)
+  StemPoolPlan splan;
   // side branch (a block's downsample convolution): runs on the engine's second stream next to the
   // layers that follow it; `wait_ev` makes its first consumer wait for it
   bool side = false;
@@ -125,6 +127,7 @@ struct ai4e_engine {
   std::vector<size_t> buf_elems_per_image;
   uint8_t* d_blob = nullptr;
   uint16_t* d_stem_w = nullptr;  // stem weights repacked for the tensor-core stem
+  uint16_t* d_stem_pool_w = nullptr;  // ... and for the fused stem + max-pool kernel
   size_t slot_bytes = 0;  // staging bytes per image
   int launches = 0;
 
@@ -273,6 +276,8 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
     if (d.op == AI4E_OP_CONV) {
       if (L.fused_second) {
         rc = AI4E_OK;
+      } else if (L.stem_pool) {
+        rc = stem_pool_launch(L.splan, batch, stream);
       } else if (L.fused_first) {
         rc = fused_tail_launch(L.fplan, batch, stream);
       } else if (L.igemm) {
@@ -284,8 +289,9 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
                                 stream);
       }
     } else if (d.op == AI4E_OP_MAXPOOL) {
-      rc = launch_maxpool(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, d.kh, d.stride, d.pad,
-                          e->bufs[d.out_buf], stream, L.reverse ? 1 : 0);
+      rc = L.fused_second ? AI4E_OK
+                          : launch_maxpool(e->bufs[d.in_buf], batch, L.in_h, L.in_w, d.cin, d.kh, d.stride, d.pad,
+                                           e->bufs[d.out_buf], stream, L.reverse ? 1 : 0);
     } else {
       rc = launch_head(e->bufs[d.in_buf], batch, L.in_h * L.in_w, d.cin, eng->d_blob + d.w_off,
                        (const float*)(eng->d_blob + d.b_off), d.cout, e->d_pooled, d_logits, d_idx, d_prob,
@@ -662,6 +668,42 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
     L.plan.grid_sms = grid_sms;
   }
 
+  // ---- stem + max-pool: a row-mode stem whose only consumer is a 3x3/2 max-pool runs with it in one
+  // kernel (stem_pool.cu); the stem's output - the largest tensor of the network - is never written.
+  // Not when the program keeps every stage in memory (desc.reserved bit 0: stage read-back).
+  if (!getenv("AI4E_B200_NO_STEM_POOL") && !(desc->reserved & 1)) {
+    for (size_t i = 0; i + 1 < ln.layers.size(); ++i) {
+      LayerRt& A = ln.layers[i];
+      LayerRt& B = ln.layers[i + 1];
+      const ai4e_layer_desc& a = A.d;
+      const ai4e_layer_desc& b = B.d;
+      if (a.op != AI4E_OP_CONV || !A.igemm || A.plan.stem_mode == 0 || b.op != AI4E_OP_MAXPOOL || b.in_buf != a.out_buf ||
+          b.out_buf == a.in_buf || a.res_buf >= 0)
+        continue;
+      if (!stem_pool_supported(A.in_h, A.in_w, a.cin, a.cout, a.kh, a.kw, a.stride, a.pad, b.kh, b.stride, b.pad)) continue;
+      bool sole_consumer = true;
+      for (size_t k = i + 2; k < ln.layers.size() && sole_consumer; ++k) {
+        const ai4e_layer_desc& c = ln.layers[k].d;
+        if (c.in_buf == a.out_buf || c.res_buf == a.out_buf) sole_consumer = false;
+        if (c.out_buf == a.out_buf) break;
+      }
+      if (!sole_consumer) continue;
+      if (!e->d_stem_pool_w) {
+        std::vector<uint16_t> w_sp((size_t)stem_pool_weight_elems());
+        stem_pool_repack_weights(reinterpret_cast<const uint16_t*>(static_cast<const uint8_t*>(blob) + a.w_off), w_sp.data());
+        TRY_OR_FAIL(cudaMalloc((void**)&e->d_stem_pool_w, w_sp.size() * 2));
+        TRY_OR_FAIL(cudaMemcpy(e->d_stem_pool_w, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice));
+      }
+      int rc = stem_pool_make_plan(&A.splan, ln.bufs[a.in_buf], max_batch, A.in_h, A.in_w, e->d_stem_pool_w,
+                                   (const float*)(e->d_blob + a.b_off), a.relu, ln.bufs[b.out_buf]);
+      if (rc) return fail(rc);
+      A.splan.grid_sms = grid_sms;
+      A.stem_pool = true;
+      B.fused_second = true;
+      if (li == 0) e->launches -= 1;
+    }
+  }
+
   // ---- bottleneck tails: a convolution + ReLU whose only consumer is a 1x1 convolution with a
   // residual runs with it in one kernel (conv_fused.cu); the intermediate buffer is never written.
   if (!getenv("AI4E_B200_NO_FUSE")) {
@@ -852,6 +894,7 @@ int ai4e_engine_destroy(ai4e_engine* e) {
   if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
   if (e->d_blob) cudaFree(e->d_blob);
   if (e->d_stem_w) cudaFree(e->d_stem_w);
+  if (e->d_stem_pool_w) cudaFree(e->d_stem_pool_w);
   delete e;
   return AI4E_OK;
 }

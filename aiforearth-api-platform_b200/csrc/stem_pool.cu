@@ -1,0 +1,361 @@
+// K2+K3 in one kernel: the 7x7/2 stem convolution (+ folded BatchNorm, bias, ReLU) and the 3x3/2
+// max-pool behind it.  The stem's output (103 MB of bf16 at micro-batch 64, the largest tensor of the
+// network) is then never written to HBM and never read back: the kernel reads the preprocessed image
+// (25.7 MB) and writes the pooled tensor (25.7 MB).
+//
+// It builds on the row mode of the tensor-core stem (conv_igemm.cu, kModeStemRows): input rows sit in
+// plain shared-memory row buffers and the A operand of a filter row is that buffer seen through an
+// un-swizzled K-major descriptor whose core matrices overlap.  New here:
+//   * one tile = one POOLED output row j: stem rows 2j and 2j+1 come out of ONE accumulator of 128
+//     columns.  Input row i of the tile (image row 4j-3+i, i = 0..8) meets filter row i of stem row 2j
+//     and filter row i-2 of stem row 2j+1, so the weights are repacked (host, once) into nine
+//     [128][32] blocks [W_i ; W_(i-2)] (zero where a filter row does not exist) and every MMA has
+//     N = 128 - which costs the tensor core the same 67 cycles as the N = 64 of the plain stem:
+//     18 MMAs per two stem rows instead of 28.
+//   * a CTA walks RUNS of consecutive pooled rows of one image, so that stem row 2j-1, the third row
+//     of the pooling window, is simply what the previous tile left in registers; a run that does not
+//     start at the top of an image first computes the tile above it and stores nothing.
+//   * epilogue: eight warps, (TMEM lane quadrant) x (channel half).  A thread owns one stem column:
+//     bias + ReLU + rounding to bf16 as the plain stem does, vertical max over the three rows in
+//     packed bf16 (max commutes with the monotonic bias/ReLU/rounding, so the result is bit-identical
+//     to pooling the stored stem output), horizontal max through warp shuffles - the one column that
+//     lies in the neighbouring quadrant crosses through 64 bytes of shared memory and a 128-thread
+//     named barrier - and 64-byte global stores of the pooled pixels from the even lanes.
+//
+// Stands in for conv1 + bn1 + relu + maxpool of torchvision's ResNet, i.e. the first four modules of
+// the model the callback at /root/reference/APIs/1.0/base-py/ai4e_service.py:203 runs.  Oracle:
+// oracle/resnet_oracle.py forward_bf16_emul stages "stem" -> "pool".
+#include "../../include/ai4e_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+#include "igemm_tiles.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+namespace ai4e {
+
+namespace {
+
+constexpr int kSpRows = 9;                    // input rows per tile
+constexpr int kSpTaps = 4;                    // super-pixel taps per filter row (see conv_igemm.cu)
+constexpr int kSpN = 128;                     // accumulator columns: stem row 2j | stem row 2j+1
+constexpr int kSpMaxGroups = 18;              // 128-byte groups per row buffer (output rows up to 128 wide)
+constexpr int kSpStage = kSpRows * kSpMaxGroups * 128 + 256;   // 20,992 B incl. over-read slack
+constexpr int kSpSlab = kSpN * 16;            // one tap of one input row: [128 channels][16 B]
+constexpr int kSpResidentB = kSpRows * kSpTaps * kSpSlab;      // 73,728 B of weights, resident
+constexpr int kSpXchg = 2 * 2 * 4 * 64;       // [tile parity][side][quadrant][32 channels bf16]
+constexpr int kSpMaxStages = 8;
+constexpr int kSpBarBytes = (2 * kSpMaxStages + 4 + 2) * 8 + 16;
+constexpr int kSpSmemLimit = 227 * 1024;
+constexpr int kSpStages = (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpBarBytes) / kSpStage > kSpMaxStages
+                              ? kSpMaxStages
+                              : (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpBarBytes) / kSpStage;
+constexpr int kSpSmem = kSpStages * kSpStage + kSpResidentB + kSpXchg + 256 + kSpBarBytes;
+constexpr int kSpRun = 8;                     // pooled rows per run
+constexpr uint32_t kNegInf2 = 0xFF80FF80u;    // two bf16 -inf: max-pool padding
+
+__device__ __forceinline__ uint32_t hmax2(uint32_t a, uint32_t b) {
+  uint32_t d;
+  asm("max.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+
+}  // namespace
+
+struct StemPoolParams {
+  int H;            // input rows
+  int P, Q;         // stem output rows / columns
+  int Pp, Qp;       // pooled rows / columns
+  int runs_per_img, num_runs;
+  int stem_rb;      // bytes per input-row buffer
+  int relu;
+  const float* bias;
+  bf16* out;        // [N][Pp][Qp][64]
+};
+
+__global__ void __launch_bounds__(kIgemmThreads, 1)
+stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const StemPoolParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t smem_base = smem_u32(smem_raw);
+  if (smem_base & 127u) __trap();
+  const uint32_t bres_base = smem_base + kSpStages * kSpStage;
+  const uint32_t xchg_base = bres_base + kSpResidentB;
+  const uint32_t bias_base = xchg_base + kSpXchg;
+  const uint32_t bar_base = bias_base + 256;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kSpMaxStages + s); };
+  auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kSpMaxStages + s); };
+  auto tmem_empty_bar = [&](int s) { return bar_base + 8u * (2 * kSpMaxStages + 2 + s); };
+  const uint32_t b_full_bar = bar_base + 8u * (2 * kSpMaxStages + 4);
+  const uint32_t tmem_ptr_addr = bar_base + 8u * (2 * kSpMaxStages + 5);
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_ptr_addr - smem_base));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+    for (int s = 0; s < kSpStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tmem_full_bar(s), 1);
+      mbar_init(tmem_empty_bar(s), kEpiWarps);
+    }
+    mbar_init(b_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr_addr, 2 * kSpN);
+    tmem_relinquish();
+  }
+  if (warp == 2 && lane < 16) {
+    // bias: 64 floats, read by every epilogue warp
+    reinterpret_cast<float4*>(smem_raw + (bias_base - smem_base))[lane] = __ldg(reinterpret_cast<const float4*>(p.bias) + lane);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+  pdl_launch_dependents();
+
+  // Every role walks the same tile sequence: runs blockIdx.x, + gridDim.x, ...; inside a run the
+  // pooled rows j0 - 1 (only to seed the window, skipped at the top of an image) .. j0 + kSpRun - 1.
+  auto run_geom = [&](int run, int& n_img, int& j_first, int& j_end, int& j_store) {
+    n_img = run / p.runs_per_img;
+    const int j0 = (run - n_img * p.runs_per_img) * kSpRun;
+    j_store = j0;
+    j_first = j0 > 0 ? j0 - 1 : 0;
+    j_end = min(j0 + kSpRun, p.Pp);
+  };
+
+  if (warp == 0) {
+    // ------------------------------- TMA producer -------------------------------
+    if (elect_one()) {
+      mbar_expect_tx(b_full_bar, kSpResidentB);
+      for (int i = 0; i < kSpRows * kSpTaps; ++i) tma_load_2d(bres_base + i * kSpSlab, &tmap_b, b_full_bar, i * 8, 0);
+    }
+    __syncwarp();
+    pdl_wait();  // the image is the preprocessing kernel's output
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int run = blockIdx.x; run < p.num_runs; run += gridDim.x) {
+      int n_img, j_first, j_end, j_store;
+      run_geom(run, n_img, j_first, j_end, j_store);
+      for (int j = j_first; j < j_end; ++j) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint32_t a_dst = smem_base + stage * kSpStage;
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), (uint32_t)kSpRows * p.stem_rb);
+#pragma unroll
+          for (int i = 0; i < kSpRows; ++i)  // group -1 = super-pixels -8..-1 and rows outside the image: zero fill = padding
+            tma_load_4d(a_dst + i * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, 4 * j - 3 + i, n_img);
+        }
+        __syncwarp();
+        if (++stage == kSpStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------- MMA issuer ---------------------------------
+    constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM, kSpN);
+    int stage = 0;
+    uint32_t phase = 0, it = 0;
+    mbar_wait(b_full_bar, 0);
+    for (int run = blockIdx.x; run < p.num_runs; run += gridDim.x) {
+      int n_img, j_first, j_end, j_store;
+      run_geom(run, n_img, j_first, j_end, j_store);
+      for (int j = j_first; j < j_end; ++j, ++it) {
+        const uint32_t acc = it & 1u;
+        mbar_wait(tmem_empty_bar(acc), ((it >> 1) & 1u) ^ 1u);
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kSpN;
+        const uint32_t a_addr = smem_base + stage * kSpStage;
+        if (elect_one()) {
+#pragma unroll
+          for (int i = 0; i < kSpRows; ++i) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {  // taps (2h, 2h+1) = one K = 16 step
+              const uint64_t adesc = umma_smem_desc(a_addr + i * p.stem_rb + (6 + 2 * h) * 16, 16, 128, 0);
+              const uint64_t bdesc = umma_smem_desc(bres_base + (i * kSpTaps + 2 * h) * kSpSlab, kSpSlab, 128, 0);
+              umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (i | h) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(empty_bar(stage));
+          umma_commit(tmem_full_bar(acc));
+        }
+        __syncwarp();
+        if (++stage == kSpStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp < 2 + kEpiWarps) {
+    // ------------------------------- epilogue -----------------------------------
+    const int side = (warp - 2) >> 2;   // channel half: channels [32 * side, 32 * side + 32)
+    const int quad = warp & 3;          // TMEM lane quadrant = stem columns [32 * quad, 32 * quad + 32)
+    const float4* const b4 = reinterpret_cast<const float4*>(smem_raw + (bias_base - smem_base)) + side * 8;
+    const uint32_t lane_tmem = (uint32_t)(quad * 32) << 16;
+    const int q = quad * 32 + lane;     // this thread's stem column
+    uint4* const xch = reinterpret_cast<uint4*>(smem_raw + (xchg_base - smem_base));  // [parity][side][quad][4 x uint4]
+    const bool relu = p.relu != 0;
+    pdl_wait();  // the pooled tensor's buffer may still be read by an earlier kernel
+    uint32_t it = 0;      // tiles computed (accumulator stage and phase)
+    uint32_t stored = 0;  // tiles stored (exchange-buffer parity: consecutive barriers must alternate buffers)
+    for (int run = blockIdx.x; run < p.num_runs; run += gridDim.x) {
+      int n_img, j_first, j_end, j_store;
+      run_geom(run, n_img, j_first, j_end, j_store);
+      uint32_t prev[16];  // stem row 2j - 1 of this thread's column: bf16 pairs, after bias / ReLU / rounding
+#pragma unroll
+      for (int k = 0; k < 16; ++k) prev[k] = kNegInf2;
+      for (int j = j_first; j < j_end; ++j, ++it) {
+        const uint32_t acc = it & 1u;
+        mbar_wait(tmem_full_bar(acc), (it >> 1) & 1u);
+        tc_fence_after();
+        uint32_t ra[32], rb[32];
+        tmem_ld_32x32b_x32(tmem_base + acc * kSpN + side * 32 + lane_tmem, ra);        // stem row 2j
+        tmem_ld_32x32b_x32(tmem_base + acc * kSpN + 64 + side * 32 + lane_tmem, rb);   // stem row 2j + 1
+        tmem_wait_ld_pin(ra);
+        tmem_wait_ld_pin(rb);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
+        uint32_t vm[16];  // max over the window's three rows
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float4 b = b4[k];
+          uint32_t a0 = pack_bf16x2(__uint_as_float(ra[4 * k]) + b.x, __uint_as_float(ra[4 * k + 1]) + b.y);
+          uint32_t a1 = pack_bf16x2(__uint_as_float(ra[4 * k + 2]) + b.z, __uint_as_float(ra[4 * k + 3]) + b.w);
+          uint32_t c0 = pack_bf16x2(__uint_as_float(rb[4 * k]) + b.x, __uint_as_float(rb[4 * k + 1]) + b.y);
+          uint32_t c1 = pack_bf16x2(__uint_as_float(rb[4 * k + 2]) + b.z, __uint_as_float(rb[4 * k + 3]) + b.w);
+          if (relu) { a0 = relu_bf16x2(a0); a1 = relu_bf16x2(a1); c0 = relu_bf16x2(c0); c1 = relu_bf16x2(c1); }
+          vm[2 * k] = hmax2(hmax2(prev[2 * k], a0), c0);
+          vm[2 * k + 1] = hmax2(hmax2(prev[2 * k + 1], a1), c1);
+          prev[2 * k] = c0;
+          prev[2 * k + 1] = c1;
+        }
+        if (j < j_store) continue;  // the tile above the run: it only seeded `prev`
+        // horizontal max over columns q - 1, q, q + 1 (needed on the even columns).  Column q - 1 of a
+        // quadrant's first lane belongs to the neighbouring warp: it crosses through shared memory.
+        const uint32_t par = stored++ & 1u;
+        if (lane == 31) {
+          uint4* dst = xch + ((par * 2 + side) * 4 + quad) * 4;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) dst[k] = make_uint4(vm[4 * k], vm[4 * k + 1], vm[4 * k + 2], vm[4 * k + 3]);
+        }
+        named_bar_sync(1 + side, 128);
+        uint32_t o[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) o[k] = __shfl_up_sync(0xffffffffu, vm[k], 1);
+        if (lane == 0) {
+          if (quad > 0) {
+            const uint4* src = xch + ((par * 2 + side) * 4 + quad - 1) * 4;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint4 t = src[k];
+              o[4 * k] = t.x; o[4 * k + 1] = t.y; o[4 * k + 2] = t.z; o[4 * k + 3] = t.w;
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 16; ++k) o[k] = kNegInf2;  // column -1: padding
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < 16; ++k) o[k] = hmax2(hmax2(o[k], vm[k]), __shfl_down_sync(0xffffffffu, vm[k], 1));
+        const int i = q >> 1;  // pooled column
+        if ((lane & 1) == 0 && i < p.Qp) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (((long long)n_img * p.Pp + j) * p.Qp + i) * 64 + side * 32);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) dst[k] = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * kSpN);
+  }
+}
+
+// ----------------------------------------------------------------------------------------
+// host side
+// ----------------------------------------------------------------------------------------
+int stem_pool_supported(int H, int W, int Cin, int Cout, int R, int S, int stride, int pad, int pool_k, int pool_stride,
+                        int pool_pad) {
+  if (!stem_supported(H, W, Cin, Cout, R, S, stride, pad)) return 0;
+  const int P = (H + 6 - 7) / 2 + 1, Q = (W + 6 - 7) / 2 + 1;
+  return pool_k == 3 && pool_stride == 2 && pool_pad == 1 && W % 16 == 0 && H % 4 == 0 && Q <= kBlockM && P % 2 == 0 &&
+         Q % 2 == 0 && (Q + 10 + 7) / 8 <= kSpMaxGroups;
+}
+
+// [64][7][7][4] KRSC bf16 weights -> [128][9 input rows][4 taps][8]: row n < 64 is output channel n of
+// stem row 2j (filter row i), row 64 + n the same channel of stem row 2j + 1 (filter row i - 2); taps
+// as in stem_repack_weights (tap t: channels 0-3 <- filter column 2t - 1, channels 4-7 <- column 2t).
+void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp) {
+  memset(w_sp, 0, (size_t)kSpN * kSpRows * kSpTaps * 8 * sizeof(uint16_t));
+  for (int n = 0; n < kSpN; ++n) {
+    const int co = n & 63, shift = n < 64 ? 0 : 2;
+    for (int i = 0; i < kSpRows; ++i) {
+      const int r = i - shift;
+      if (r < 0 || r >= 7) continue;
+      for (int t = 0; t < kSpTaps; ++t)
+        for (int c = 0; c < 8; ++c) {
+          const int s = (c < 4) ? 2 * t - 1 : 2 * t;
+          if (s < 0) continue;
+          w_sp[((n * kSpRows + i) * kSpTaps + t) * 8 + c] = w_krsc[((co * 7 + r) * 7 + s) * 4 + (c & 3)];
+        }
+    }
+  }
+}
+
+int stem_pool_weight_elems() { return kSpN * kSpRows * kSpTaps * 8; }
+
+int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
+                        const float* bias, int relu, void* out) {
+  AI4E_REQUIRE(stem_pool_supported(H, W, 4, 64, 7, 7, 2, 3, 3, 2, 1), "stem+pool: unsupported input %dx%d", H, W);
+  AI4E_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(weight_sp) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(out) & 15) == 0 && (reinterpret_cast<uintptr_t>(bias) & 15) == 0,
+               "stem+pool: pointers must be 16-byte aligned");
+  const int P = (H + 6 - 7) / 2 + 1, Q = (W + 6 - 7) / 2 + 1;
+  plan->H = H; plan->P = P; plan->Q = Q; plan->Pp = P / 2; plan->Qp = Q / 2;
+  plan->runs_per_img = (plan->Pp + kSpRun - 1) / kSpRun;
+  const int groups = (Q + 10 + 7) / 8;
+  plan->stem_rb = groups * 128;
+  plan->relu = relu; plan->bias = bias; plan->out = out;
+  plan->max_batch = N;
+  plan->grid_sms = 0;
+  const uint32_t es4[4] = {1, 1, 1, 1};
+  const uint64_t adims[4] = {64, (uint64_t)W / 16, (uint64_t)H, (uint64_t)N};
+  const uint64_t astr[3] = {128, (uint64_t)W * 8, (uint64_t)H * W * 8};
+  const uint32_t abox[4] = {64, (uint32_t)groups, 1, 1};
+  int rc = tmap_encode_tiled(&plan->tmap_a, in, 4, adims, astr, abox, es4, CU_TENSOR_MAP_SWIZZLE_NONE);
+  if (rc) return rc;
+  const uint32_t es[2] = {1, 1};
+  const uint64_t wdims[2] = {(uint64_t)kSpRows * kSpTaps * 8, (uint64_t)kSpN};
+  const uint64_t wstr[1] = {(uint64_t)kSpRows * kSpTaps * 8 * 2};
+  const uint32_t wbox[2] = {8, (uint32_t)kSpN};
+  return tmap_encode_tiled(&plan->tmap_b, weight_sp, 2, wdims, wstr, wbox, es, CU_TENSOR_MAP_SWIZZLE_NONE);
+}
+
+int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream) {
+  AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "stem+pool: batch %d outside plan (max %d)", batch, plan.max_batch);
+  StemPoolParams prm{};
+  prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
+  prm.runs_per_img = plan.runs_per_img; prm.num_runs = plan.runs_per_img * batch;
+  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
+  const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
+  static std::atomic<unsigned long long> attr_done{0};
+  if (int rc = ensure_dyn_smem(stem_pool_kernel, kSpSmem, attr_done)) return rc;
+  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmem, stream,
+                           plan.tmap_a, plan.tmap_b, prm));
+  return AI4E_OK;
+}
+
+}  // namespace ai4e

@@ -184,6 +184,16 @@ AI4E_API int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w
                          const void* d_w3_kc, const float* d_bias3, int cout, const void* d_residual,
                          void* d_out_nhwc, void* stream);
 
+/* K2 + K3 in one kernel: the 7x7 stride-2 pad-3 stem convolution (4 input channels, 64 outputs, folded
+ * BatchNorm, bias, optional ReLU) and the 3x3 stride-2 pad-1 max-pool behind it.  The stem's output -
+ * the largest tensor of a ResNet - never reaches memory.  d_in is [batch][h][w][4] bf16 (the NHWC4
+ * output of ai4e_preprocess), d_weight_krsc [64][7][7][4] bf16, d_out [batch][h/4][w/4][64] bf16;
+ * w % 16 == 0, w <= 256, h % 4 == 0, else AI4E_ERR_UNSUPPORTED.  Bit-identical to ai4e_conv_layer
+ * followed by ai4e_maxpool.  Stands in for conv1 + bn1 + relu + maxpool of torchvision's ResNet
+ * inside the callback at APIs/1.0/base-py/ai4e_service.py:203; the engine uses it automatically. */
+AI4E_API int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, const void* d_weight_krsc,
+                   const float* d_bias, int relu, void* d_out_nhwc, void* stream);
+
 /* K3.  Max pooling (padding = -inf).  Stands in for torchvision's `maxpool`. */
 AI4E_API int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
                  void* d_out_nhwc, void* stream);
@@ -237,7 +247,7 @@ typedef struct ai4e_model_desc {
   int32_t in_c;         /* image channels (3 or 4) */
   int32_t in_c_pad;     /* channels of slot 0 (stem Cin; 4) */
   int32_t num_classes;
-  int32_t reserved;
+  int32_t reserved;     /* bit 0: keep every layer's output in memory (stage read-back): no cross-layer fusion */
   float mean[4], std[4];
   const ai4e_layer_desc* layers;
 } ai4e_model_desc;

@@ -368,6 +368,27 @@ def test_resnet50_microbatch_64_as_benchmarked():
         assert e.stats()["healthy"]
 
 
+def test_engine_with_and_without_stem_pool_fusion_agree_bit_for_bit(monkeypatch):
+    """the fused stem + max-pool kernel inside the engine gives exactly the logits of the two separate
+    kernels (AI4E_B200_NO_STEM_POOL=1), for the 3-band 224 x 224 and the 4-band 256 x 256 model."""
+    from ai4e_b200.engine import Engine
+    for name, arch, in_ch, hw in (("resnet50_b64", "resnet50", 3, 224), ("resnet50_landcover4", "resnet50", 4, 256)):
+        g, imgs = util.load_golden(name)
+        imgs = imgs[:16]
+        prog = util.program_for(arch, in_ch, hw)
+        with Engine(prog, device=0, max_batch=16) as e:
+            fused = e.forward(imgs, want_logits=True)
+            launches_fused = e.stats()["launches_per_forward"]
+        monkeypatch.setenv("AI4E_B200_NO_STEM_POOL", "1")
+        with Engine(prog, device=0, max_batch=16) as e:
+            plain = e.forward(imgs, want_logits=True)
+            launches_plain = e.stats()["launches_per_forward"]
+        monkeypatch.delenv("AI4E_B200_NO_STEM_POOL")
+        assert launches_fused == launches_plain - 1
+        assert np.array_equal(fused[2], plain[2]) and np.array_equal(fused[0], plain[0])
+        assert np.array_equal(fused[0], g["top5_idx"][:16])
+
+
 def test_gain1_model_report():
     """SURVEY 8(d)'s literal recipe leaves the residual branches at gain 1: a far worse conditioned
     network than the golden model.  This test REPORTS how the engine agrees with the

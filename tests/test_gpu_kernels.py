@@ -165,6 +165,51 @@ def test_conv_stem_tensor_core_vs_oracle(case):
     assert (out.float() - direct.float()).abs().max() <= 2.0 ** -6 * want.abs().max()
 
 
+STEM_POOL_CASES = [
+    (2, 224, 224, True),    # the network's stem: 112 x 112 -> 56 x 56, 7 runs of 8 pooled rows per image
+    (3, 256, 256, True),    # land-cover chips: 128 output columns fill all four TMEM lane quadrants
+    (1, 224, 224, False),   # no ReLU: negative values, -inf padding must not leak
+    (5, 32, 64, True),      # small: pooled 8 x 16, one run per image, most taps in the padding
+    (2, 40, 48, True),      # pooled 10 x 12: the second run of an image is ragged (2 rows) and starts with a seed tile
+    (150, 64, 32, True),    # more runs than SMs: CTAs take several runs, accumulator stages wrap many times
+]
+
+
+@pytest.mark.parametrize("case", STEM_POOL_CASES, ids=lambda c: "x".join(str(v) for v in c))
+def test_stem_pool_fused_is_bit_identical_to_stem_then_maxpool(case):
+    """K2 + K3 in one kernel == ai4e_conv_layer (tensor-core stem) followed by ai4e_maxpool, bit for bit,
+    and within one bf16 rounding of conv2d + relu + max_pool2d in fp32."""
+    from ai4e_b200 import ops, _lib as L
+    b, h, w, relu = case
+    g = torch.Generator().manual_seed(h * 1000 + w + b)
+    x = (torch.randn((b, h, w, 4), generator=g) * 0.8).to(torch.bfloat16)
+    x[..., 3] = 0
+    wt = (torch.randn((64, 7, 7, 4), generator=g) * 0.08).to(torch.bfloat16)
+    bias = torch.randn(64, generator=g) * 0.3
+    stem = ops.conv_layer(x.cuda(), wt.cuda(), bias.cuda(), 2, 3, None, relu, algo=L.CONV_AUTO)
+    want = ops.maxpool(stem)
+    got = ops.stem_pool(x.cuda(), wt.cuda(), bias.cuda(), relu)
+    torch.cuda.synchronize()
+    assert got.shape == want.shape == (b, h // 4, w // 4, 64)
+    assert torch.equal(got, want), f"{(got != want).sum().item()} of {got.numel()} values differ"
+    y = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), wt.float().permute(0, 3, 1, 2), bias, stride=2, padding=3)
+    if relu:
+        y = torch.relu(y)
+    ref = torch.nn.functional.max_pool2d(y, 3, 2, 1).permute(0, 2, 3, 1)
+    err = (got.float().cpu() - ref).abs()
+    assert (err <= 2.0 ** -7 * ref.abs() + 2e-3).all(), err.max()
+
+
+def test_stem_pool_rejects_unsupported_sizes():
+    from ai4e_b200 import ops, Ai4eError, _lib as L
+    wt = torch.zeros((64, 7, 7, 4), dtype=torch.bfloat16, device="cuda")
+    bias = torch.zeros(64, device="cuda")
+    for h, w in ((30, 50), (224, 520), (18, 16)):   # width not a multiple of 16 / too wide / height not a multiple of 4
+        with pytest.raises(Ai4eError) as ei:
+            ops.stem_pool(torch.zeros((1, h, w, 4), dtype=torch.bfloat16, device="cuda"), wt, bias)
+        assert ei.value.code == L.ERR_UNSUPPORTED
+
+
 # (b, h, w, cin, cout, k, stride, pad, relu, residual): every conv geometry of ResNet-18/50
 # after the stem, at small batch, plus ragged tails (M not a multiple of 128)
 IGEMM_CASES = [
