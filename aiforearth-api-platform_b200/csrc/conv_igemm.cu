@@ -239,10 +239,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t a_dst = smem_base + stage * Cfg::kStageBytes;
           if (elect_one()) {
+            // one load for the seven rows (box 64 x groups x 7 x 1; row r lands at r * stem_rb): seven
+            // separate loads cost the issuing thread more than the tile's MMAs.  Group -1 = super-pixels
+            // -8..-1 and rows outside the image: zero padding by OOB fill
             mbar_expect_tx(full_bar(stage), 7u * p.stem_rb);
-#pragma unroll
-            for (int r = 0; r < 7; ++r)  // group -1 = super-pixels -8..-1: zero padding by OOB fill
-              tma_load_4d(a_dst + r * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, y0 + r, n_img);
+            tma_load_4d(a_dst, &tmap_a, full_bar(stage), 0, -1, y0, n_img);
           }
           __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -755,7 +756,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
     q.stem_rb = groups * 128;
     const uint64_t adims[4] = {64, (uint64_t)W / 16, (uint64_t)H, (uint64_t)N};
     const uint64_t astr[3] = {128, (uint64_t)W * 8, (uint64_t)H * W * 8};
-    const uint32_t abox[4] = {64, (uint32_t)groups, 1, 1};
+    const uint32_t abox[4] = {64, (uint32_t)groups, 7, 1};
     rc = tmap_encode_tiled(&plan->tmap_a, in, 4, adims, astr, abox, es4, CU_TENSOR_MAP_SWIZZLE_NONE);
   } else {
     // input as [N][H][W/2][8]: 4 taps from super-pixel q-2, traversal stride 1 in W and 2 in H.

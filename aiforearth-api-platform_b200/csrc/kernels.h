@@ -113,7 +113,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
 
 // ---- K2 + K3 in one kernel (stem_pool.cu): 7x7/2 stem + bias + ReLU + 3x3/2 max-pool, NHWC4 in, pooled NHWC out
 struct StemPoolPlan {
-  CUtensorMap tmap_a;  // input rows, [N][H][W/16][64 elements], one row per load
+  CUtensorMap tmap_a;  // input rows, [N][H][W/16][64 elements], nine rows per load
   CUtensorMap tmap_b;  // repacked weights [128][9 * 4 * 8], box 8 x 128
   int H, P, Q, Pp, Qp, runs_per_img, stem_rb, relu;
   const float* bias;

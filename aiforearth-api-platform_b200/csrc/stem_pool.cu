@@ -151,10 +151,12 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t a_dst = smem_base + stage * kSpStage;
         if (elect_one()) {
+          // ONE load for the tile's nine rows (box = 64 x groups x 9 x 1; row i lands at i * stem_rb): a
+          // thread needs ~200-350 cycles per TMA instruction, and nine of them per tile - not the MMAs -
+          // set the pace of the first version (49 us).  Group -1 = super-pixels -8..-1 and rows outside
+          // the image are filled with zeros: the convolution's padding.
           mbar_expect_tx(full_bar(stage), (uint32_t)kSpRows * p.stem_rb);
-#pragma unroll
-          for (int i = 0; i < kSpRows; ++i)  // group -1 = super-pixels -8..-1 and rows outside the image: zero fill = padding
-            tma_load_4d(a_dst + i * p.stem_rb, &tmap_a, full_bar(stage), 0, -1, 4 * j - 3 + i, n_img);
+          tma_load_4d(a_dst, &tmap_a, full_bar(stage), 0, -1, 4 * j - 3, n_img);
         }
         __syncwarp();
         if (++stage == kSpStages) { stage = 0; phase ^= 1u; }
@@ -291,7 +293,7 @@ int stem_pool_supported(int H, int W, int Cin, int Cout, int R, int S, int strid
                         int pool_pad) {
   if (!stem_supported(H, W, Cin, Cout, R, S, stride, pad)) return 0;
   const int P = (H + 6 - 7) / 2 + 1, Q = (W + 6 - 7) / 2 + 1;
-  return pool_k == 3 && pool_stride == 2 && pool_pad == 1 && W % 16 == 0 && H % 4 == 0 && Q <= kBlockM && P % 2 == 0 &&
+  return pool_k == 3 && pool_stride == 2 && pool_pad == 1 && W % 16 == 0 && H % 4 == 0 && H >= 12 && Q <= kBlockM && P % 2 == 0 &&
          Q % 2 == 0 && (Q + 10 + 7) / 8 <= kSpMaxGroups;
 }
 
@@ -334,7 +336,7 @@ int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W,
   const uint32_t es4[4] = {1, 1, 1, 1};
   const uint64_t adims[4] = {64, (uint64_t)W / 16, (uint64_t)H, (uint64_t)N};
   const uint64_t astr[3] = {128, (uint64_t)W * 8, (uint64_t)H * W * 8};
-  const uint32_t abox[4] = {64, (uint32_t)groups, 1, 1};
+  const uint32_t abox[4] = {64, (uint32_t)groups, (uint32_t)kSpRows, 1};
   int rc = tmap_encode_tiled(&plan->tmap_a, in, 4, adims, astr, abox, es4, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc) return rc;
   const uint32_t es[2] = {1, 1};
