@@ -80,6 +80,7 @@ SIGNATURES = {
     "ai4e_image_probe": (_i, [_vp, _u64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "ai4e_bottleneck_tail": (_i, [_vp, _i, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp]),
     "ai4e_stem_pool": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp]),
+    "ai4e_preprocess_stem_pool": (_i, [_vp, _i, _i, _i, _fp, _fp, _vp, _vp, _i, _vp, _vp]),
     "ai4e_maxpool": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "ai4e_head": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),
     "ai4e_head_noalloc": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _i, _vp]),

@@ -187,6 +187,19 @@ def stem_pool(x_nhwc4: torch.Tensor, weight_krsc: torch.Tensor, bias: torch.Tens
     return out
 
 
+def preprocess_stem_pool(images_u8: torch.Tensor, mean, std, weight_krsc: torch.Tensor, bias: torch.Tensor,
+                         relu: bool = True, stream=None) -> torch.Tensor:
+    """uint8 [B,H,W,3] -> normalise + 7x7/2 stem + bias (+ ReLU) + 3x3/2 max-pool in ONE kernel ->
+    [B,H/4,W/4,64] bf16; bit-identical to preprocess(layout="nhwc", out_channels=4) followed by stem_pool."""
+    lib = L.load()
+    assert images_u8.is_cuda and images_u8.is_contiguous() and images_u8.dtype == torch.uint8 and images_u8.shape[3] == 3
+    b, h, w, _ = images_u8.shape
+    out = torch.empty((b, h // 4, w // 4, 64), dtype=torch.bfloat16, device=images_u8.device)
+    L.check(lib.ai4e_preprocess_stem_pool(_ptr(images_u8), b, h, w, _farr(mean, 3), _farr(std, 3), _ptr(weight_krsc),
+                                          _ptr(bias), int(relu), _ptr(out), _stream_ptr(stream)))
+    return out
+
+
 def maxpool(x_nhwc: torch.Tensor, k: int = 3, stride: int = 2, pad: int = 1, stream=None) -> torch.Tensor:
     lib = L.load()
     assert x_nhwc.is_contiguous() and x_nhwc.dtype == torch.bfloat16

@@ -154,8 +154,23 @@ int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int cin,
   return igemm_launch(plan, batch, 0, (cudaStream_t)stream);
 }
 
+static int stem_pool_any(const void* d_in, bool u8, const float* h_mean, const float* h_std, int batch, int h, int w,
+                         const void* d_weight_krsc, const float* d_bias, int relu, void* d_out_nhwc, void* stream);
+
 int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, const void* d_weight_krsc, const float* d_bias,
                    int relu, void* d_out_nhwc, void* stream) {
+  return stem_pool_any(d_in_nhwc4, false, nullptr, nullptr, batch, h, w, d_weight_krsc, d_bias, relu, d_out_nhwc, stream);
+}
+
+int ai4e_preprocess_stem_pool(const uint8_t* d_images_hwc3, int batch, int h, int w, const float* h_mean, const float* h_std,
+                              const void* d_weight_krsc, const float* d_bias, int relu, void* d_out_nhwc, void* stream) {
+  AI4E_REQUIRE(h_mean && h_std, "preprocess_stem_pool: null mean/std");
+  for (int c = 0; c < 3; ++c) AI4E_REQUIRE(h_std[c] != 0.0f, "preprocess_stem_pool: std[%d] is zero", c);
+  return stem_pool_any(d_images_hwc3, true, h_mean, h_std, batch, h, w, d_weight_krsc, d_bias, relu, d_out_nhwc, stream);
+}
+
+static int stem_pool_any(const void* d_in_nhwc4, bool u8, const float* h_mean, const float* h_std, int batch, int h, int w,
+                         const void* d_weight_krsc, const float* d_bias, int relu, void* d_out_nhwc, void* stream) {
   AI4E_REQUIRE(d_in_nhwc4 && d_weight_krsc && d_bias && d_out_nhwc && batch > 0, "stem_pool: bad arguments");
   if (!stem_pool_supported(h, w, 4, 64, 7, 7, 2, 3, 3, 2, 1)) {
     set_last_error("stem_pool: input %d x %d is not supported (width a multiple of 16 and at most 256, height a multiple of 4)", h, w);
@@ -172,8 +187,10 @@ int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, const void* 
   AI4E_CUDA_TRY(cudaMemcpyAsync(d_sp, w_sp.data(), w_sp.size() * 2, cudaMemcpyHostToDevice, s));
   AI4E_CUDA_TRY(cudaStreamSynchronize(s));
   StemPoolPlan plan;
-  int rc = stem_pool_make_plan(&plan, d_in_nhwc4, batch, h, w, d_sp, d_bias, relu, d_out_nhwc);
-  if (rc == AI4E_OK) rc = stem_pool_launch(plan, batch, s);
+  // (u8 mode: the plan's bf16 input map is unused; any aligned pointer encodes)
+  int rc = stem_pool_make_plan(&plan, u8 ? d_out_nhwc : d_in_nhwc4, batch, h, w, d_sp, d_bias, relu, d_out_nhwc);
+  if (rc == AI4E_OK)
+    rc = u8 ? stem_pool_launch_u8(plan, (const uint8_t*)d_in_nhwc4, batch, h_mean, h_std, s) : stem_pool_launch(plan, batch, s);
   cudaFreeAsync(d_sp, s);
   return rc;
 }

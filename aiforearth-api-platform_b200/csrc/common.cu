@@ -60,6 +60,13 @@ static void resolve_driver_entry_points() {
 int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes, const uint32_t* box,
                       const uint32_t* elem_strides, CUtensorMapSwizzle swizzle) {
+  return tmap_encode_tiled_as(out, gaddr, rank, dims, strides_bytes, box, elem_strides, swizzle, /*u32=*/false);
+}
+
+// same with 32-bit elements (raw bytes moved four at a time: uint8 image rows)
+int tmap_encode_tiled_as(CUtensorMap* out, const void* gaddr, int rank, const uint64_t* dims,
+                         const uint64_t* strides_bytes, const uint32_t* box,
+                         const uint32_t* elem_strides, CUtensorMapSwizzle swizzle, bool u32) {
   std::call_once(g_once, resolve_driver_entry_points);
   if (!g_encode_tiled) {
     set_last_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -69,7 +76,7 @@ int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint6
   cuuint32_t b[5], e[5];
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = elem_strides[i]; }
   for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
-  CUresult r = g_encode_tiled(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+  CUresult r = g_encode_tiled(out, u32 ? CU_TENSOR_MAP_DATA_TYPE_UINT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
                               const_cast<void*>(gaddr), d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE,
                               swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

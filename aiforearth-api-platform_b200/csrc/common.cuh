@@ -134,6 +134,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(x), "r"(y)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2,
                                             int c3) {
   asm volatile(
@@ -446,6 +452,9 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 int tmap_encode_tiled(CUtensorMap* out, const void* gaddr, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box,
                       const uint32_t* elem_strides, CUtensorMapSwizzle swizzle);
+int tmap_encode_tiled_as(CUtensorMap* out, const void* gaddr, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box,
+                      const uint32_t* elem_strides, CUtensorMapSwizzle swizzle, bool u32);
 int tmap_encode_im2col_nhwc(CUtensorMap* out, const void* gaddr, int n, int h, int w, int c,
                             int filt_r, int filt_s, int stride, int pad, int channels_per_pixel,
                             int pixels_per_column);

@@ -116,6 +116,7 @@ struct Lane {
   float* d_logits = nullptr;  // where the logits go when the caller of forward_device passes no buffer
   cudaEvent_t ev_chain = nullptr;
   bool chain_valid = false;
+  bool u8_stem = false;       // layer 0 is the fused stem + max-pool and may take the uint8 batch itself (K1 fused in)
   cudaStream_t side_stream = nullptr;
 };
 
@@ -129,7 +130,8 @@ struct ai4e_engine {
   uint16_t* d_stem_w = nullptr;  // stem weights repacked for the tensor-core stem
   uint16_t* d_stem_pool_w = nullptr;  // ... and for the fused stem + max-pool kernel
   size_t slot_bytes = 0;  // staging bytes per image
-  int launches = 0;
+  int launches = 0;       // kernels one forward launches
+  int launches_u8 = 0;    // ... when the batch is raw pixels of the model's input size (K1 runs inside the stem); 0 = never
 
   // lanes are handed out round-robin under launch_mu
   std::mutex launch_mu;
@@ -246,7 +248,12 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
   if (marks) AI4E_CUDA_TRY(cudaEventRecord(marks[mark++], stream));
   const bool resize = src_h != m.in_h || src_w != m.in_w;
   int rc = AI4E_OK;
-  if (jpeg && !resize && m.in_c == 3 && m.in_c_pad == 4) {
+  // K1 inside the stem: a raw 3-channel batch of the model's input size needs no preprocessing launch at
+  // all when the first layer is the fused stem + max-pool kernel (its converter warps apply K1's table)
+  const bool u8_stem = e->u8_stem && !jpeg && !chips && !resize;
+  if (u8_stem) {
+    // nothing: the stem reads d_images
+  } else if (jpeg && !resize && m.in_c == 3 && m.in_c_pad == 4) {
     // K0 fused into K1: the JPEG colour kernel writes the normalised bf16 NHWC4 pixels itself
     const float ms[6] = {m.mean[0], m.mean[1], m.mean[2], m.std[0], m.std[1], m.std[2]};
     rc = jpeg_reconstruct(jpeg->d_rec, batch, &jpeg->jinfo, jpeg->d_planes, (uint8_t*)e->bufs[0], stream, ms);
@@ -277,7 +284,8 @@ int forward_enqueue(ai4e_engine* eng, Lane* e, const uint8_t* d_images, int batc
       if (L.fused_second) {
         rc = AI4E_OK;
       } else if (L.stem_pool) {
-        rc = stem_pool_launch(L.splan, batch, stream);
+        rc = (u8_stem && &L == &e->layers.front()) ? stem_pool_launch_u8(L.splan, d_images, batch, m.mean, m.std, stream)
+                                                   : stem_pool_launch(L.splan, batch, stream);
       } else if (L.fused_first) {
         rc = fused_tail_launch(L.fplan, batch, stream);
       } else if (L.igemm) {
@@ -701,6 +709,11 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
       A.stem_pool = true;
       B.fused_second = true;
       if (li == 0) e->launches -= 1;
+      if (i == 0 && a.in_buf == 0 && desc->in_c == 3 && stem_pool_u8_supported(A.in_h, A.in_w, desc->in_c) &&
+          !getenv("AI4E_B200_NO_U8_STEM")) {
+        ln.u8_stem = true;
+        if (li == 0) e->launches_u8 = -1;  // ... and no preprocessing launch for raw batches of the input size (counted below)
+      }
     }
   }
 
@@ -811,6 +824,7 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   }
 
   }  // lanes
+  if (e->launches_u8 < 0) e->launches_u8 = e->launches - 1;
 
   // ---- staging: images up to 2x the model input's bytes: covers a 256 -> 224 resize+crop (1.31x)
   // and the int16 coefficient record of a 4:4:4 JPEG of the input size (2x + tables)
@@ -1297,7 +1311,7 @@ int ai4e_engine_stats_get(ai4e_engine* e, ai4e_engine_stats* out) {
   *out = e->st;
   out->queue_depth = e->next_ticket - e->done_upto;  // == n_submitted - n_completed
   out->healthy = e->healthy.load();
-  out->launches_per_forward = e->launches;
+  out->launches_per_forward = e->launches_u8 > 0 ? e->launches_u8 : e->launches;  // the serving path's usual case
   const uint64_t n = std::min<uint64_t>(e->lat_n, kLatRing);
   if (n) {
     std::vector<float> v(e->lat_ms.begin(), e->lat_ms.begin() + n);

@@ -128,6 +128,10 @@ void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][
 int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
                         const float* bias, int relu, void* out);
 int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream);
+// K1 fused in as well: the uint8 HWC batch (3 channels, no resize) goes straight into the stem
+int stem_pool_u8_supported(int H, int W, int channels);
+int stem_pool_launch_u8(const StemPoolPlan& plan, const uint8_t* d_images, int batch, const float* mean, const float* stdv,
+                        cudaStream_t stream);
 
 // ---- K3 / K5 (pool_head.cu)
 int launch_maxpool(const void* in, int N, int H, int W, int C, int k, int stride, int pad, void* out,

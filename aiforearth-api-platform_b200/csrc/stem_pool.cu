@@ -53,6 +53,13 @@ constexpr int kSpStages = (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpBarB
                               ? kSpMaxStages
                               : (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpBarBytes) / kSpStage;
 constexpr int kSpSmem = kSpStages * kSpStage + kSpResidentB + kSpXchg + 256 + kSpBarBytes;
+// u8 mode (K1 fused in): the image arrives as uint8 HWC rows, two converter warps turn them into the bf16
+// row buffers through K1's look-up table.  Its ring pairs every A stage with a stage of raw rows.
+constexpr int kSpU8Stage = 7168;              // 9 rows x 768 B (W <= 256, 3 channels), rounded up
+constexpr int kSpLutBytes = 3 * 256 * 2;
+constexpr int kSpStagesU8 = (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpLutBytes - 2 * kSpBarBytes) / (kSpStage + kSpU8Stage);
+constexpr int kSpSmemU8 = kSpStagesU8 * (kSpStage + kSpU8Stage) + kSpResidentB + kSpXchg + 256 + kSpLutBytes + 2 * kSpBarBytes;
+static_assert(kSpStagesU8 >= 3 && kSpStagesU8 <= kSpMaxStages, "u8 ring");
 constexpr int kSpRun = 8;                     // pooled rows per run
 constexpr uint32_t kNegInf2 = 0xFF80FF80u;    // two bf16 -inf: max-pool padding
 
@@ -65,6 +72,8 @@ __device__ __forceinline__ uint32_t hmax2(uint32_t a, uint32_t b) {
 }  // namespace
 
 struct StemPoolParams {
+  int W;            // input columns (u8 mode)
+  float mean[3], stdv[3];  // u8 mode: K1's normalisation
   int H;            // input rows
   int P, Q;         // stem output rows / columns
   int Pp, Qp;       // pooled rows / columns
@@ -75,16 +84,22 @@ struct StemPoolParams {
   bf16* out;        // [N][Pp][Qp][64]
 };
 
+template <bool kU8>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
 stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const StemPoolParams p) {
+  constexpr int kStages = kU8 ? kSpStagesU8 : kSpStages;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = smem_u32(smem_raw);
   if (smem_base & 127u) __trap();
-  const uint32_t bres_base = smem_base + kSpStages * kSpStage;
+  const uint32_t u8_base = smem_base + kStages * kSpStage;                       // u8 mode: raw rows, one stage per A stage
+  const uint32_t bres_base = u8_base + (kU8 ? kStages * kSpU8Stage : 0);
   const uint32_t xchg_base = bres_base + kSpResidentB;
   const uint32_t bias_base = xchg_base + kSpXchg;
-  const uint32_t bar_base = bias_base + 256;
+  const uint32_t lut_base = bias_base + 256;                                     // u8 mode: [3][256] bf16
+  const uint32_t bar_base = lut_base + (kU8 ? kSpLutBytes : 0);
+  auto u8_full_bar = [&](int s) { return bar_base + kSpBarBytes + 8u * s; };     // (second barrier block, u8 mode only)
+  auto u8_empty_bar = [&](int s) { return bar_base + kSpBarBytes + 8u * (kSpMaxStages + s); };
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kSpMaxStages + s); };
   auto tmem_full_bar = [&](int s) { return bar_base + 8u * (2 * kSpMaxStages + s); };
@@ -99,9 +114,13 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
-    for (int s = 0; s < kSpStages; ++s) {
-      mbar_init(full_bar(s), 1);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(full_bar(s), kU8 ? 2 : 1);  // u8 mode: the two converter warps; else the TMA load
       mbar_init(empty_bar(s), 1);
+      if constexpr (kU8) {
+        mbar_init(u8_full_bar(s), 1);
+        mbar_init(u8_empty_bar(s), 2);
+      }
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);
@@ -117,6 +136,16 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 2 && lane < 16) {
     // bias: 64 floats, read by every epilogue warp
     reinterpret_cast<float4*>(smem_raw + (bias_base - smem_base))[lane] = __ldg(reinterpret_cast<const float4*>(p.bias) + lane);
+  }
+  if constexpr (kU8) {
+    // the table of K1 (three separately rounded IEEE operations per entry: bit-identical to preprocess.cu)
+    uint16_t* lut = reinterpret_cast<uint16_t*>(smem_raw + (lut_base - smem_base));
+    for (int e = threadIdx.x; e < 768; e += blockDim.x) lut[e] = norm_to_bf16((float)(e & 255), p.mean[e >> 8], p.stdv[e >> 8]);
+    // the A stages start as zeros and the converters only ever write pixel units: the padding units of
+    // every row buffer (left of the image, right of it, the over-read slack) stay zero for good
+    uint4* z = reinterpret_cast<uint4*>(smem_raw);
+    for (int e = threadIdx.x; e < kStages * kSpStage / 16; e += blockDim.x) z[e] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async_smem();  // the tensor core reads them through the async proxy
   }
   tc_fence_before();
   __syncthreads();
@@ -148,6 +177,18 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       int n_img, j_first, j_end, j_store;
       run_geom(run, n_img, j_first, j_end, j_store);
       for (int j = j_first; j < j_end; ++j) {
+        if constexpr (kU8) {
+          // raw uint8 rows: box = (W * 3 / 4 words) x 9 rows x 1 image, rows outside the image arrive as
+          // zero BYTES (the converters turn them into zero VALUES, not into lut[0])
+          mbar_wait(u8_empty_bar(stage), phase ^ 1u);
+          if (elect_one()) {
+            mbar_expect_tx(u8_full_bar(stage), (uint32_t)kSpRows * p.W * 3);
+            tma_load_3d(u8_base + stage * kSpU8Stage, &tmap_a, u8_full_bar(stage), 0, 4 * j - 3, n_img);
+          }
+          __syncwarp();
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          continue;
+        }
         mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t a_dst = smem_base + stage * kSpStage;
         if (elect_one()) {
@@ -159,7 +200,56 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           tma_load_4d(a_dst, &tmap_a, full_bar(stage), 0, -1, 4 * j - 3, n_img);
         }
         __syncwarp();
-        if (++stage == kSpStages) { stage = 0; phase ^= 1u; }
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (kU8 && warp >= 2 + kEpiWarps) {
+    // ------------------------------- converters (u8 mode): K1 inside the stem ------
+    // Two warps turn a stage of raw rows into the stage's bf16 row buffers: a lane takes four pixels
+    // (12 bytes, three aligned words), looks every byte up in its channel's table and writes
+    // (c0, c1, c2, 0) x 4 = 32 bytes.  Pixel x of row i lives in unit 8 + x / 2 of row buffer i.
+    const int cw = warp - (2 + kEpiWarps);
+    const uint16_t* lut = reinterpret_cast<const uint16_t*>(smem_raw + (lut_base - smem_base));
+    const int quads_per_row = p.W >> 2, row_bytes = p.W * 3;
+    const int slots = kSpRows * quads_per_row;
+    pdl_wait();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int run = blockIdx.x; run < p.num_runs; run += gridDim.x) {
+      int n_img, j_first, j_end, j_store;
+      run_geom(run, n_img, j_first, j_end, j_store);
+      for (int j = j_first; j < j_end; ++j) {
+        mbar_wait(u8_full_bar(stage), phase);
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const uint8_t* src = smem_raw + (u8_base - smem_base) + stage * kSpU8Stage;
+        uint8_t* dst = smem_raw + stage * kSpStage;
+        for (int slot = cw * 32 + lane; slot < slots; slot += 64) {
+          const int i = slot / quads_per_row, xg = slot - i * quads_per_row;
+          const int y = 4 * j - 3 + i;
+          uint4 o0 = make_uint4(0u, 0u, 0u, 0u), o1 = o0;
+          if (y >= 0 && y < p.H) {
+            const uint32_t* w = reinterpret_cast<const uint32_t*>(src + i * row_bytes + xg * 12);
+            const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+            auto px = [&](uint32_t r, uint32_t g, uint32_t b, uint32_t& lo, uint32_t& hi) {
+              lo = (uint32_t)lut[r] | ((uint32_t)lut[256 + g] << 16);
+              hi = (uint32_t)lut[512 + b];
+            };
+            px(w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u, o0.x, o0.y);
+            px(w0 >> 24, w1 & 255u, (w1 >> 8) & 255u, o0.z, o0.w);
+            px((w1 >> 16) & 255u, w1 >> 24, w2 & 255u, o1.x, o1.y);
+            px((w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24, o1.z, o1.w);
+          }
+          uint4* d = reinterpret_cast<uint4*>(dst + i * p.stem_rb + 128 + xg * 32);
+          d[0] = o0;
+          d[1] = o1;
+        }
+        fence_proxy_async_smem();  // generic-proxy writes -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(full_bar(stage));
+          mbar_arrive(u8_empty_bar(stage));
+        }
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
@@ -192,7 +282,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           umma_commit(tmem_full_bar(acc));
         }
         __syncwarp();
-        if (++stage == kSpStages) { stage = 0; phase ^= 1u; }
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp < 2 + kEpiWarps) {
@@ -354,9 +444,43 @@ int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream) {
   prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   static std::atomic<unsigned long long> attr_done{0};
-  if (int rc = ensure_dyn_smem(stem_pool_kernel, kSpSmem, attr_done)) return rc;
-  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmem, stream,
-                           plan.tmap_a, plan.tmap_b, prm));
+  if (int rc = ensure_dyn_smem(stem_pool_kernel<false>, kSpSmem, attr_done)) return rc;
+  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<false>, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmem,
+                           stream, plan.tmap_a, plan.tmap_b, prm));
+  return AI4E_OK;
+}
+
+// u8 mode: K1 (no resize, 3 channels) inside the kernel.  `d_images` is the dense uint8 [batch][H][W][3]
+// batch; its tensor map is encoded per call (a host-side computation) because the batch lives wherever the
+// caller put it.
+int stem_pool_u8_supported(int H, int W, int channels) {
+  return channels == 3 && stem_pool_supported(H, W, 4, 64, 7, 7, 2, 3, 3, 2, 1) && W * 3 / 4 <= 256;
+}
+
+int stem_pool_launch_u8(const StemPoolPlan& plan, const uint8_t* d_images, int batch, const float* mean, const float* stdv,
+                        cudaStream_t stream) {
+  AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "stem+pool: batch %d outside plan (max %d)", batch, plan.max_batch);
+  const int W = plan.Q * 2;
+  AI4E_REQUIRE(stem_pool_u8_supported(plan.H, W, 3), "stem+pool(u8): unsupported input %d x %d", plan.H, W);
+  AI4E_REQUIRE((reinterpret_cast<uintptr_t>(d_images) & 15) == 0, "stem+pool(u8): the image batch must be 16-byte aligned");
+  CUtensorMap tmap_u8;
+  const uint32_t es3[3] = {1, 1, 1};
+  const uint64_t dims[3] = {(uint64_t)W * 3 / 4, (uint64_t)plan.H, (uint64_t)batch};
+  const uint64_t str[2] = {(uint64_t)W * 3, (uint64_t)plan.H * W * 3};
+  const uint32_t box[3] = {(uint32_t)(W * 3 / 4), (uint32_t)kSpRows, 1};
+  int rc = tmap_encode_tiled_as(&tmap_u8, d_images, 3, dims, str, box, es3, CU_TENSOR_MAP_SWIZZLE_NONE, /*u32=*/true);
+  if (rc) return rc;
+  StemPoolParams prm{};
+  prm.W = W;
+  for (int c = 0; c < 3; ++c) { prm.mean[c] = mean[c]; prm.stdv[c] = stdv[c]; }
+  prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
+  prm.runs_per_img = plan.runs_per_img; prm.num_runs = plan.runs_per_img * batch;
+  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
+  const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
+  static std::atomic<unsigned long long> attr_done{0};
+  if (int rc2 = ensure_dyn_smem(stem_pool_kernel<true>, kSpSmemU8, attr_done)) return rc2;
+  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<true>, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmemU8,
+                           stream, tmap_u8, plan.tmap_b, prm));
   return AI4E_OK;
 }
 

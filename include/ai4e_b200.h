@@ -194,6 +194,18 @@ AI4E_API int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w
 AI4E_API int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, const void* d_weight_krsc,
                    const float* d_bias, int relu, void* d_out_nhwc, void* stream);
 
+/* K1 + K2 + K3 in one kernel: the same with the uint8 image as input.  d_images is the dense
+ * [batch][h][w][3] uint8 batch; two warps of every CTA normalise the rows it needs through K1's
+ * look-up table ((x/255 - mean)/std, bit-identical to ai4e_preprocess) while the tensor core works on
+ * the previous ones, so the normalised bf16 image (401 KB per 224 x 224 image) is never written or read.
+ * No resize: h, w are the model's input size.  Bit-identical to ai4e_preprocess (NHWC, 4 channels)
+ * followed by ai4e_stem_pool.  Stands in for ToTensor + Normalize + conv1 + bn1 + relu + maxpool of the
+ * callback at APIs/1.0/base-py/ai4e_service.py:203; the engine uses it for raw 3-channel batches of
+ * the model's input size. */
+AI4E_API int ai4e_preprocess_stem_pool(const uint8_t* d_images_hwc3, int batch, int h, int w, const float* h_mean,
+                              const float* h_std, const void* d_weight_krsc, const float* d_bias, int relu,
+                              void* d_out_nhwc, void* stream);
+
 /* K3.  Max pooling (padding = -inf).  Stands in for torchvision's `maxpool`. */
 AI4E_API int ai4e_maxpool(const void* d_in_nhwc, int batch, int h, int w, int c, int k, int stride, int pad,
                  void* d_out_nhwc, void* stream);

@@ -369,8 +369,9 @@ def test_resnet50_microbatch_64_as_benchmarked():
 
 
 def test_engine_with_and_without_stem_pool_fusion_agree_bit_for_bit(monkeypatch):
-    """the fused stem + max-pool kernel inside the engine gives exactly the logits of the two separate
-    kernels (AI4E_B200_NO_STEM_POOL=1), for the 3-band 224 x 224 and the 4-band 256 x 256 model."""
+    """the fused stem + max-pool kernel inside the engine - with the uint8 batch as its input (K1 fused in
+    as well) for the 3-band model, behind K1 for the 4-band one - gives exactly the logits of the separate
+    kernels (AI4E_B200_NO_U8_STEM=1: K1 + fused stem/pool; AI4E_B200_NO_STEM_POOL=1: K1, stem, max-pool)."""
     from ai4e_b200.engine import Engine
     for name, arch, in_ch, hw in (("resnet50_b64", "resnet50", 3, 224), ("resnet50_landcover4", "resnet50", 4, 256)):
         g, imgs = util.load_golden(name)
@@ -379,13 +380,20 @@ def test_engine_with_and_without_stem_pool_fusion_agree_bit_for_bit(monkeypatch)
         with Engine(prog, device=0, max_batch=16) as e:
             fused = e.forward(imgs, want_logits=True)
             launches_fused = e.stats()["launches_per_forward"]
+        monkeypatch.setenv("AI4E_B200_NO_U8_STEM", "1")
+        with Engine(prog, device=0, max_batch=16) as e:
+            no_u8 = e.forward(imgs, want_logits=True)
+            launches_no_u8 = e.stats()["launches_per_forward"]
         monkeypatch.setenv("AI4E_B200_NO_STEM_POOL", "1")
         with Engine(prog, device=0, max_batch=16) as e:
             plain = e.forward(imgs, want_logits=True)
             launches_plain = e.stats()["launches_per_forward"]
         monkeypatch.delenv("AI4E_B200_NO_STEM_POOL")
-        assert launches_fused == launches_plain - 1
-        assert np.array_equal(fused[2], plain[2]) and np.array_equal(fused[0], plain[0])
+        monkeypatch.delenv("AI4E_B200_NO_U8_STEM")
+        assert launches_no_u8 == launches_plain - 1
+        assert launches_fused == launches_plain - (2 if in_ch == 3 else 1)   # K1 disappears too for 3-band pixels
+        for other in (no_u8, plain):
+            assert np.array_equal(fused[2], other[2]) and np.array_equal(fused[0], other[0])
         assert np.array_equal(fused[0], g["top5_idx"][:16])
 
 

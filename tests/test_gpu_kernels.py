@@ -200,6 +200,24 @@ def test_stem_pool_fused_is_bit_identical_to_stem_then_maxpool(case):
     assert (err <= 2.0 ** -7 * ref.abs() + 2e-3).all(), err.max()
 
 
+@pytest.mark.parametrize("b,h,w,relu", [(3, 224, 224, True), (2, 256, 256, True), (70, 32, 64, False), (1, 12, 16, True)])
+def test_preprocess_stem_pool_is_bit_identical_to_the_three_kernels(b, h, w, relu):
+    """K1 + K2 + K3 in one kernel (uint8 in, pooled bf16 out) == ai4e_preprocess (NHWC4) -> ai4e_stem_pool."""
+    from ai4e_b200 import ops
+    rng = np.random.default_rng(b * 7 + h)
+    imgs = torch.from_numpy(rng.integers(0, 256, (b, h, w, 3), dtype=np.uint8)).cuda()
+    imgs[0, :3] = 0          # a zero byte is lut[0], not the zero of the padding
+    imgs[-1, -2:] = 255
+    g = torch.Generator().manual_seed(w)
+    wt = (torch.randn((64, 7, 7, 4), generator=g) * 0.08).to(torch.bfloat16).cuda()
+    bias = (torch.randn(64, generator=g) * 0.3).cuda()
+    x = ops.preprocess(imgs, ro.IMAGENET_MEAN, ro.IMAGENET_STD, layout="nhwc", out_channels=4)
+    want = ops.stem_pool(x, wt, bias, relu)
+    got = ops.preprocess_stem_pool(imgs, ro.IMAGENET_MEAN, ro.IMAGENET_STD, wt, bias, relu)
+    torch.cuda.synchronize()
+    assert torch.equal(got, want), f"{(got != want).sum().item()} of {got.numel()} values differ"
+
+
 def test_stem_pool_rejects_unsupported_sizes():
     from ai4e_b200 import ops, Ai4eError, _lib as L
     wt = torch.zeros((64, 7, 7, 4), dtype=torch.bfloat16, device="cuda")

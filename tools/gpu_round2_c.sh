@@ -12,7 +12,7 @@ try:
 except Exception as e: print(sys.argv[1], 'bench failed', e)
 PY
 done
-AI4E_B200_NO_STEM_POOL=1 timeout 300 python bench.py --steps 60 --warmup 6 --no-cpu-baseline --sustained-seconds 0 --async-seconds 0 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('unfused stem', round(d['value']), {k:round(v,4) for k,v in d['layer_ms'].items()})"
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:stem_pool --launch-skip 4 -c 1 -f -o gpurun_out/c_stem_pool python bench.py --steps 2 --warmup 3 --no-cpu-baseline --sustained-seconds 0 --async-seconds 0 > gpurun_out/c_ncu.txt 2>&1
-ls -la gpurun_out/c_stem_pool.ncu-rep | awk '{print $5}'
+AI4E_B200_NO_U8_STEM=1 timeout 300 python bench.py --steps 60 --warmup 6 --no-cpu-baseline --sustained-seconds 0 --async-seconds 0 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('K1 launched separately', round(d['value']), {k:round(v,4) for k,v in d['layer_ms'].items()})"
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:stem_pool --launch-skip 4 -c 1 -f -o gpurun_out/c_stem_pool_u8 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --sustained-seconds 0 --async-seconds 0 > gpurun_out/c_ncu.txt 2>&1
+ls -la gpurun_out/c_stem_pool_u8.ncu-rep | awk '{print $5}'
