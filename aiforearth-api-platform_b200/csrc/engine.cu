@@ -709,8 +709,12 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
       A.stem_pool = true;
       B.fused_second = true;
       if (li == 0) e->launches -= 1;
+      // K1 inside the stem as well is built and bit-exact but OFF by default: two converter warps per CTA
+      // cannot keep up with the tensor core (92 us against 51 + 20 us for the two kernels at micro-batch 64,
+      // profiles/r02_ncu_full.md), so it only pays where a launch matters more than throughput.
+      // AI4E_B200_U8_STEM=1 turns it on.
       if (i == 0 && a.in_buf == 0 && desc->in_c == 3 && stem_pool_u8_supported(A.in_h, A.in_w, desc->in_c) &&
-          !getenv("AI4E_B200_NO_U8_STEM")) {
+          getenv("AI4E_B200_U8_STEM")) {
         ln.u8_stem = true;
         if (li == 0) e->launches_u8 = -1;  // ... and no preprocessing launch for raw batches of the input size (counted below)
       }

@@ -200,8 +200,9 @@ AI4E_API int ai4e_stem_pool(const void* d_in_nhwc4, int batch, int h, int w, con
  * the previous ones, so the normalised bf16 image (401 KB per 224 x 224 image) is never written or read.
  * No resize: h, w are the model's input size.  Bit-identical to ai4e_preprocess (NHWC, 4 channels)
  * followed by ai4e_stem_pool.  Stands in for ToTensor + Normalize + conv1 + bn1 + relu + maxpool of the
- * callback at APIs/1.0/base-py/ai4e_service.py:203; the engine uses it for raw 3-channel batches of
- * the model's input size. */
+ * callback at APIs/1.0/base-py/ai4e_service.py:203.  Measured slower than the two kernels at
+ * micro-batch 64 (its two converter warps cannot keep up with the tensor core), so the engine uses it
+ * only with AI4E_B200_U8_STEM=1; it saves a launch where latency matters more than throughput. */
 AI4E_API int ai4e_preprocess_stem_pool(const uint8_t* d_images_hwc3, int batch, int h, int w, const float* h_mean,
                               const float* h_std, const void* d_weight_krsc, const float* d_bias, int relu,
                               void* d_out_nhwc, void* stream);

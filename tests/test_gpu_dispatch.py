@@ -369,18 +369,19 @@ def test_resnet50_microbatch_64_as_benchmarked():
 
 
 def test_engine_with_and_without_stem_pool_fusion_agree_bit_for_bit(monkeypatch):
-    """the fused stem + max-pool kernel inside the engine - with the uint8 batch as its input (K1 fused in
-    as well) for the 3-band model, behind K1 for the 4-band one - gives exactly the logits of the separate
-    kernels (AI4E_B200_NO_U8_STEM=1: K1 + fused stem/pool; AI4E_B200_NO_STEM_POOL=1: K1, stem, max-pool)."""
+    """the fused stem + max-pool kernel inside the engine - behind K1 (the default) or, with
+    AI4E_B200_U8_STEM=1, with the uint8 batch as its own input for the 3-band model - gives exactly the
+    logits of the three separate kernels (AI4E_B200_NO_STEM_POOL=1: K1, stem, max-pool)."""
     from ai4e_b200.engine import Engine
     for name, arch, in_ch, hw in (("resnet50_b64", "resnet50", 3, 224), ("resnet50_landcover4", "resnet50", 4, 256)):
         g, imgs = util.load_golden(name)
         imgs = imgs[:16]
         prog = util.program_for(arch, in_ch, hw)
+        monkeypatch.setenv("AI4E_B200_U8_STEM", "1")
         with Engine(prog, device=0, max_batch=16) as e:
             fused = e.forward(imgs, want_logits=True)
             launches_fused = e.stats()["launches_per_forward"]
-        monkeypatch.setenv("AI4E_B200_NO_U8_STEM", "1")
+        monkeypatch.delenv("AI4E_B200_U8_STEM")
         with Engine(prog, device=0, max_batch=16) as e:
             no_u8 = e.forward(imgs, want_logits=True)
             launches_no_u8 = e.stats()["launches_per_forward"]
@@ -389,7 +390,6 @@ def test_engine_with_and_without_stem_pool_fusion_agree_bit_for_bit(monkeypatch)
             plain = e.forward(imgs, want_logits=True)
             launches_plain = e.stats()["launches_per_forward"]
         monkeypatch.delenv("AI4E_B200_NO_STEM_POOL")
-        monkeypatch.delenv("AI4E_B200_NO_U8_STEM")
         assert launches_no_u8 == launches_plain - 1
         assert launches_fused == launches_plain - (2 if in_ch == 3 else 1)   # K1 disappears too for 3-band pixels
         for other in (no_u8, plain):
