@@ -45,7 +45,10 @@ constexpr int kSpMaxGroups = 18;              // 128-byte groups per row buffer 
 constexpr int kSpStage = kSpRows * kSpMaxGroups * 128 + 256;   // 20,992 B incl. over-read slack
 constexpr int kSpSlab = kSpN * 16;            // one tap of one input row: [128 channels][16 B]
 constexpr int kSpResidentB = kSpRows * kSpTaps * kSpSlab;      // 73,728 B of weights, resident
-constexpr int kSpXchg = 2 * 2 * 4 * 64;       // [tile parity][side][quadrant][32 channels bf16]
+constexpr int kSpParts = 4;                   // epilogue: channel quarters (16 channels per warp)
+constexpr int kSpEpiWarps = 4 * kSpParts;     // x four TMEM lane quadrants
+constexpr int kSpThreads = (2 + kSpEpiWarps + 2) * 32;  // producer, MMA, 16 epilogue warps, 2 converter warps (u8 mode)
+constexpr int kSpXchg = 2 * kSpParts * 4 * 32;  // [tile parity][channel quarter][quadrant][16 channels bf16]
 constexpr int kSpMaxStages = 8;
 constexpr int kSpBarBytes = (2 * kSpMaxStages + 4 + 2) * 8 + 16;
 constexpr int kSpSmemLimit = 227 * 1024;
@@ -85,7 +88,7 @@ struct StemPoolParams {
 };
 
 template <bool kU8>
-__global__ void __launch_bounds__(kIgemmThreads, 1)
+__global__ void __launch_bounds__(kSpThreads, 1)
 stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const StemPoolParams p) {
   constexpr int kStages = kU8 ? kSpStagesU8 : kSpStages;
@@ -124,7 +127,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tmem_full_bar(s), 1);
-      mbar_init(tmem_empty_bar(s), kEpiWarps);
+      mbar_init(tmem_empty_bar(s), kSpEpiWarps);
     }
     mbar_init(b_full_bar, 1);
     fence_mbar_init();
@@ -203,12 +206,12 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (kU8 && warp >= 2 + kEpiWarps) {
+  } else if (kU8 && warp >= 2 + kSpEpiWarps) {
     // ------------------------------- converters (u8 mode): K1 inside the stem ------
     // Two warps turn a stage of raw rows into the stage's bf16 row buffers: a lane takes four pixels
     // (12 bytes, three aligned words), looks every byte up in its channel's table and writes
     // (c0, c1, c2, 0) x 4 = 32 bytes.  Pixel x of row i lives in unit 8 + x / 2 of row buffer i.
-    const int cw = warp - (2 + kEpiWarps);
+    const int cw = warp - (2 + kSpEpiWarps);
     const uint16_t* lut = reinterpret_cast<const uint16_t*>(smem_raw + (lut_base - smem_base));
     const int quads_per_row = p.W >> 2, row_bytes = p.W * 3;
     const int slots = kSpRows * quads_per_row;
@@ -285,14 +288,17 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (warp < 2 + kEpiWarps) {
+  } else if (warp < 2 + kSpEpiWarps) {
     // ------------------------------- epilogue -----------------------------------
-    const int side = (warp - 2) >> 2;   // channel half: channels [32 * side, 32 * side + 32)
+    // Sixteen warps: (TMEM lane quadrant) x (channel quarter).  With eight warps of 32 channels the kernel
+    // ran at the pace of one warp's dependent instruction chain per tile (~2,150 cycles against 1,150 of
+    // MMAs, ncu: profiles/r02_ncu_full.md); 16 channels per warp halve the chain and the registers.
+    const int part = (warp - 2) >> 2;   // channel quarter: channels [16 * part, 16 * part + 16)
     const int quad = warp & 3;          // TMEM lane quadrant = stem columns [32 * quad, 32 * quad + 32)
-    const float4* const b4 = reinterpret_cast<const float4*>(smem_raw + (bias_base - smem_base)) + side * 8;
+    const float4* const b4 = reinterpret_cast<const float4*>(smem_raw + (bias_base - smem_base)) + part * 4;
     const uint32_t lane_tmem = (uint32_t)(quad * 32) << 16;
     const int q = quad * 32 + lane;     // this thread's stem column
-    uint4* const xch = reinterpret_cast<uint4*>(smem_raw + (xchg_base - smem_base));  // [parity][side][quad][4 x uint4]
+    uint4* const xch = reinterpret_cast<uint4*>(smem_raw + (xchg_base - smem_base));  // [parity][part][quad][2 x uint4]
     const bool relu = p.relu != 0;
     pdl_wait();  // the pooled tensor's buffer may still be read by an earlier kernel
     uint32_t it = 0;      // tiles computed (accumulator stage and phase)
@@ -300,24 +306,24 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int run = blockIdx.x; run < p.num_runs; run += gridDim.x) {
       int n_img, j_first, j_end, j_store;
       run_geom(run, n_img, j_first, j_end, j_store);
-      uint32_t prev[16];  // stem row 2j - 1 of this thread's column: bf16 pairs, after bias / ReLU / rounding
+      uint32_t prev[8];  // stem row 2j - 1 of this thread's column: bf16 pairs, after bias / ReLU / rounding
 #pragma unroll
-      for (int k = 0; k < 16; ++k) prev[k] = kNegInf2;
+      for (int k = 0; k < 8; ++k) prev[k] = kNegInf2;
       for (int j = j_first; j < j_end; ++j, ++it) {
         const uint32_t acc = it & 1u;
         mbar_wait(tmem_full_bar(acc), (it >> 1) & 1u);
         tc_fence_after();
-        uint32_t ra[32], rb[32];
-        tmem_ld_32x32b_x32(tmem_base + acc * kSpN + side * 32 + lane_tmem, ra);        // stem row 2j
-        tmem_ld_32x32b_x32(tmem_base + acc * kSpN + 64 + side * 32 + lane_tmem, rb);   // stem row 2j + 1
-        tmem_wait_ld_pin(ra);
-        tmem_wait_ld_pin(rb);
+        uint32_t ra[16], rb[16];
+        tmem_ld_32x32b_x16(tmem_base + acc * kSpN + part * 16 + lane_tmem, ra);        // stem row 2j
+        tmem_ld_32x32b_x16(tmem_base + acc * kSpN + 64 + part * 16 + lane_tmem, rb);   // stem row 2j + 1
+        tmem_wait_ld_pin16(ra);
+        tmem_wait_ld_pin16(rb);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tmem_empty_bar(acc));
-        uint32_t vm[16];  // max over the window's three rows
+        uint32_t vm[8];  // max over the window's three rows
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < 4; ++k) {
           const float4 b = b4[k];
           uint32_t a0 = pack_bf16x2(__uint_as_float(ra[4 * k]) + b.x, __uint_as_float(ra[4 * k + 1]) + b.y);
           uint32_t a1 = pack_bf16x2(__uint_as_float(ra[4 * k + 2]) + b.z, __uint_as_float(ra[4 * k + 3]) + b.w);
@@ -334,34 +340,32 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         // quadrant's first lane belongs to the neighbouring warp: it crosses through shared memory.
         const uint32_t par = stored++ & 1u;
         if (lane == 31) {
-          uint4* dst = xch + ((par * 2 + side) * 4 + quad) * 4;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) dst[k] = make_uint4(vm[4 * k], vm[4 * k + 1], vm[4 * k + 2], vm[4 * k + 3]);
+          uint4* dst = xch + ((par * kSpParts + part) * 4 + quad) * 2;
+          dst[0] = make_uint4(vm[0], vm[1], vm[2], vm[3]);
+          dst[1] = make_uint4(vm[4], vm[5], vm[6], vm[7]);
         }
-        named_bar_sync(1 + side, 128);
-        uint32_t o[16];
+        named_bar_sync(1 + part, 128);  // the four quadrant warps of this channel quarter
+        uint32_t o[8];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) o[k] = __shfl_up_sync(0xffffffffu, vm[k], 1);
+        for (int k = 0; k < 8; ++k) o[k] = __shfl_up_sync(0xffffffffu, vm[k], 1);
         if (lane == 0) {
           if (quad > 0) {
-            const uint4* src = xch + ((par * 2 + side) * 4 + quad - 1) * 4;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint4 t = src[k];
-              o[4 * k] = t.x; o[4 * k + 1] = t.y; o[4 * k + 2] = t.z; o[4 * k + 3] = t.w;
-            }
+            const uint4* src = xch + ((par * kSpParts + part) * 4 + quad - 1) * 2;
+            const uint4 t0 = src[0], t1 = src[1];
+            o[0] = t0.x; o[1] = t0.y; o[2] = t0.z; o[3] = t0.w;
+            o[4] = t1.x; o[5] = t1.y; o[6] = t1.z; o[7] = t1.w;
           } else {
 #pragma unroll
-            for (int k = 0; k < 16; ++k) o[k] = kNegInf2;  // column -1: padding
+            for (int k = 0; k < 8; ++k) o[k] = kNegInf2;  // column -1: padding
           }
         }
 #pragma unroll
-        for (int k = 0; k < 16; ++k) o[k] = hmax2(hmax2(o[k], vm[k]), __shfl_down_sync(0xffffffffu, vm[k], 1));
+        for (int k = 0; k < 8; ++k) o[k] = hmax2(hmax2(o[k], vm[k]), __shfl_down_sync(0xffffffffu, vm[k], 1));
         const int i = q >> 1;  // pooled column
         if ((lane & 1) == 0 && i < p.Qp) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out + (((long long)n_img * p.Pp + j) * p.Qp + i) * 64 + side * 32);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) dst[k] = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+          uint4* dst = reinterpret_cast<uint4*>(p.out + (((long long)n_img * p.Pp + j) * p.Qp + i) * 64 + part * 16);
+          dst[0] = make_uint4(o[0], o[1], o[2], o[3]);
+          dst[1] = make_uint4(o[4], o[5], o[6], o[7]);
         }
       }
     }
@@ -445,7 +449,7 @@ int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream) {
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   static std::atomic<unsigned long long> attr_done{0};
   if (int rc = ensure_dyn_smem(stem_pool_kernel<false>, kSpSmem, attr_done)) return rc;
-  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<false>, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmem,
+  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<false>, dim3(std::min(prm.num_runs, sms)), dim3(kSpThreads), (size_t)kSpSmem,
                            stream, plan.tmap_a, plan.tmap_b, prm));
   return AI4E_OK;
 }
@@ -479,7 +483,7 @@ int stem_pool_launch_u8(const StemPoolPlan& plan, const uint8_t* d_images, int b
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   static std::atomic<unsigned long long> attr_done{0};
   if (int rc2 = ensure_dyn_smem(stem_pool_kernel<true>, kSpSmemU8, attr_done)) return rc2;
-  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<true>, dim3(std::min(prm.num_runs, sms)), dim3(kIgemmThreads), (size_t)kSpSmemU8,
+  AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<true>, dim3(std::min(prm.num_runs, sms)), dim3(kSpThreads), (size_t)kSpSmemU8,
                            stream, tmap_u8, plan.tmap_b, prm));
   return AI4E_OK;
 }
