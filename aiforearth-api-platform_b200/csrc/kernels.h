@@ -115,7 +115,7 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
 struct StemPoolPlan {
   CUtensorMap tmap_a;  // input rows, [N][H][W/16][64 elements], nine rows per load
   CUtensorMap tmap_b;  // repacked weights [128][9 * 4 * 8], box 8 x 128
-  int H, P, Q, Pp, Qp, runs_per_img, stem_rb, relu;
+  int H, P, Q, Pp, Qp, stem_rb, relu;
   const float* bias;
   void* out;
   int max_batch;

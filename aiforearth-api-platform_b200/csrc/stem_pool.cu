@@ -63,7 +63,6 @@ constexpr int kSpLutBytes = 3 * 256 * 2;
 constexpr int kSpStagesU8 = (kSpSmemLimit - kSpResidentB - kSpXchg - 256 - kSpLutBytes - 2 * kSpBarBytes) / (kSpStage + kSpU8Stage);
 constexpr int kSpSmemU8 = kSpStagesU8 * (kSpStage + kSpU8Stage) + kSpResidentB + kSpXchg + 256 + kSpLutBytes + 2 * kSpBarBytes;
 static_assert(kSpStagesU8 >= 3 && kSpStagesU8 <= kSpMaxStages, "u8 ring");
-constexpr int kSpRun = 8;                     // pooled rows per run
 constexpr uint32_t kNegInf2 = 0xFF80FF80u;    // two bf16 -inf: max-pool padding
 
 __device__ __forceinline__ uint32_t hmax2(uint32_t a, uint32_t b) {
@@ -80,6 +79,7 @@ struct StemPoolParams {
   int H;            // input rows
   int P, Q;         // stem output rows / columns
   int Pp, Qp;       // pooled rows / columns
+  int run_len;      // pooled rows per run
   int runs_per_img, num_runs;
   int stem_rb;      // bytes per input-row buffer
   int relu;
@@ -157,13 +157,13 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   pdl_launch_dependents();
 
   // Every role walks the same tile sequence: runs blockIdx.x, + gridDim.x, ...; inside a run the
-  // pooled rows j0 - 1 (only to seed the window, skipped at the top of an image) .. j0 + kSpRun - 1.
+  // pooled rows j0 - 1 (only to seed the window, skipped at the top of an image) .. j0 + run_len - 1.
   auto run_geom = [&](int run, int& n_img, int& j_first, int& j_end, int& j_store) {
     n_img = run / p.runs_per_img;
-    const int j0 = (run - n_img * p.runs_per_img) * kSpRun;
+    const int j0 = (run - n_img * p.runs_per_img) * p.run_len;
     j_store = j0;
     j_first = j0 > 0 ? j0 - 1 : 0;
-    j_end = min(j0 + kSpRun, p.Pp);
+    j_end = min(j0 + p.run_len, p.Pp);
   };
 
   if (warp == 0) {
@@ -421,7 +421,6 @@ int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W,
                "stem+pool: pointers must be 16-byte aligned");
   const int P = (H + 6 - 7) / 2 + 1, Q = (W + 6 - 7) / 2 + 1;
   plan->H = H; plan->P = P; plan->Q = Q; plan->Pp = P / 2; plan->Qp = Q / 2;
-  plan->runs_per_img = (plan->Pp + kSpRun - 1) / kSpRun;
   const int groups = (Q + 10 + 7) / 8;
   plan->stem_rb = groups * 128;
   plan->relu = relu; plan->bias = bias; plan->out = out;
@@ -440,13 +439,32 @@ int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W,
   return tmap_encode_tiled(&plan->tmap_b, weight_sp, 2, wdims, wstr, wbox, es, CU_TENSOR_MAP_SWIZZLE_NONE);
 }
 
+// Runs are the unit of work of a CTA: `run_len` pooled rows of one image plus, below the top of the image,
+// one seed tile.  Short runs balance better, long runs recompute fewer seed tiles; the pick minimises the
+// tiles of the busiest CTA (micro-batch 64, 56 pooled rows, 132 CTAs: 128 runs of 28 rows -> 29 tiles per
+// CTA, where runs of 8 gave 36).
+static void stem_pool_pick_runs(int Pp, int batch, int ctas, StemPoolParams* prm) {
+  long long best_cost = -1;
+  for (int len = 2; len <= Pp; ++len) {
+    const int rpi = (Pp + len - 1) / len;
+    const long long runs = (long long)rpi * batch;
+    const long long rounds = (runs + ctas - 1) / ctas;
+    const long long cost = rounds * (len + 1) * 1000 + rpi;  // ties: fewer seed tiles
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      prm->run_len = len; prm->runs_per_img = rpi; prm->num_runs = (int)runs;
+    }
+  }
+  if (best_cost < 0) { prm->run_len = Pp; prm->runs_per_img = 1; prm->num_runs = batch; }
+}
+
 int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream) {
   AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "stem+pool: batch %d outside plan (max %d)", batch, plan.max_batch);
   StemPoolParams prm{};
   prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
-  prm.runs_per_img = plan.runs_per_img; prm.num_runs = plan.runs_per_img * batch;
   prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
+  stem_pool_pick_runs(plan.Pp, batch, sms, &prm);
   static std::atomic<unsigned long long> attr_done{0};
   if (int rc = ensure_dyn_smem(stem_pool_kernel<false>, kSpSmem, attr_done)) return rc;
   AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<false>, dim3(std::min(prm.num_runs, sms)), dim3(kSpThreads), (size_t)kSpSmem,
@@ -478,9 +496,9 @@ int stem_pool_launch_u8(const StemPoolPlan& plan, const uint8_t* d_images, int b
   prm.W = W;
   for (int c = 0; c < 3; ++c) { prm.mean[c] = mean[c]; prm.stdv[c] = stdv[c]; }
   prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
-  prm.runs_per_img = plan.runs_per_img; prm.num_runs = plan.runs_per_img * batch;
   prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
+  stem_pool_pick_runs(plan.Pp, batch, sms, &prm);
   static std::atomic<unsigned long long> attr_done{0};
   if (int rc2 = ensure_dyn_smem(stem_pool_kernel<true>, kSpSmemU8, attr_done)) return rc2;
   AI4E_CUDA_TRY(launch_pdl(stem_pool_kernel<true>, dim3(std::min(prm.num_runs, sms)), dim3(kSpThreads), (size_t)kSpSmemU8,
