@@ -114,7 +114,8 @@ int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, c
 // ---- K2 + K3 in one kernel (stem_pool.cu): 7x7/2 stem + bias + ReLU + 3x3/2 max-pool, NHWC4 in, pooled NHWC out
 struct StemPoolPlan {
   CUtensorMap tmap_a;  // input rows, [N][H][W/16][64 elements], nine rows per load
-  CUtensorMap tmap_b;  // repacked weights [128][9 * 4 * 8], box 8 x 128
+  CUtensorMap tmap_b;  // (unused)
+  const void* weights;  // repacked weights, slab-major [36][128][8]: one bulk copy
   int H, P, Q, Pp, Qp, stem_rb, relu;
   const float* bias;
   void* out;
@@ -124,7 +125,7 @@ struct StemPoolPlan {
 int stem_pool_supported(int H, int W, int Cin, int Cout, int R, int S, int stride, int pad, int pool_k, int pool_stride,
                         int pool_pad);
 int stem_pool_weight_elems();
-void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][7][7][4] -> [128][9][4][8]
+void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][7][7][4] -> [9][4][128][8]
 int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
                         const float* bias, int relu, void* out);
 int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream);

@@ -84,6 +84,7 @@ struct StemPoolParams {
   int stem_rb;      // bytes per input-row buffer
   int relu;
   const float* bias;
+  const void* weights;  // repacked, slab-major
   bf16* out;        // [N][Pp][Qp][64]
 };
 
@@ -169,8 +170,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
     if (elect_one()) {
+      // all 36 weight slabs in ONE bulk copy: the host repacks them slab-major ([slab][channel][16 B], the
+      // resident layout itself).  (36 separate tensor loads took the issuing thread ~10 k cycles before the
+      // first MMA could start.)
       mbar_expect_tx(b_full_bar, kSpResidentB);
-      for (int i = 0; i < kSpRows * kSpTaps; ++i) tma_load_2d(bres_base + i * kSpSlab, &tmap_b, b_full_bar, i * 8, 0);
+      bulk_load_1d(bres_base, p.weights, kSpResidentB, b_full_bar);
     }
     __syncwarp();
     pdl_wait();  // the image is the preprocessing kernel's output
@@ -391,9 +395,10 @@ int stem_pool_supported(int H, int W, int Cin, int Cout, int R, int S, int strid
          Q % 2 == 0 && (Q + 10 + 7) / 8 <= kSpMaxGroups;
 }
 
-// [64][7][7][4] KRSC bf16 weights -> [128][9 input rows][4 taps][8]: row n < 64 is output channel n of
-// stem row 2j (filter row i), row 64 + n the same channel of stem row 2j + 1 (filter row i - 2); taps
-// as in stem_repack_weights (tap t: channels 0-3 <- filter column 2t - 1, channels 4-7 <- column 2t).
+// [64][7][7][4] KRSC bf16 weights -> [9 input rows][4 taps][128][8] (slab-major: exactly the resident
+// shared-memory layout): row n < 64 of slab (i, t) is output channel n of stem row 2j (filter row i), row
+// 64 + n the same channel of stem row 2j + 1 (filter row i - 2); taps as in stem_repack_weights (tap t:
+// channels 0-3 <- filter column 2t - 1, channels 4-7 <- column 2t).
 void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp) {
   memset(w_sp, 0, (size_t)kSpN * kSpRows * kSpTaps * 8 * sizeof(uint16_t));
   for (int n = 0; n < kSpN; ++n) {
@@ -405,7 +410,7 @@ void stem_pool_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp) {
         for (int c = 0; c < 8; ++c) {
           const int s = (c < 4) ? 2 * t - 1 : 2 * t;
           if (s < 0) continue;
-          w_sp[((n * kSpRows + i) * kSpTaps + t) * 8 + c] = w_krsc[((co * 7 + r) * 7 + s) * 4 + (c & 3)];
+          w_sp[(((i * kSpTaps + t) * kSpN) + n) * 8 + c] = w_krsc[((co * 7 + r) * 7 + s) * 4 + (c & 3)];
         }
     }
   }
@@ -432,11 +437,9 @@ int stem_pool_make_plan(StemPoolPlan* plan, const void* in, int N, int H, int W,
   const uint32_t abox[4] = {64, (uint32_t)groups, (uint32_t)kSpRows, 1};
   int rc = tmap_encode_tiled(&plan->tmap_a, in, 4, adims, astr, abox, es4, CU_TENSOR_MAP_SWIZZLE_NONE);
   if (rc) return rc;
-  const uint32_t es[2] = {1, 1};
-  const uint64_t wdims[2] = {(uint64_t)kSpRows * kSpTaps * 8, (uint64_t)kSpN};
-  const uint64_t wstr[1] = {(uint64_t)kSpRows * kSpTaps * 8 * 2};
-  const uint32_t wbox[2] = {8, (uint32_t)kSpN};
-  return tmap_encode_tiled(&plan->tmap_b, weight_sp, 2, wdims, wstr, wbox, es, CU_TENSOR_MAP_SWIZZLE_NONE);
+  plan->weights = weight_sp;  // [36 slabs][128 channels][8], fetched by one bulk copy
+  plan->tmap_b = plan->tmap_a;  // (unused)
+  return AI4E_OK;
 }
 
 // Runs are the unit of work of a CTA: `run_len` pooled rows of one image plus, below the top of the image,
@@ -462,7 +465,7 @@ int stem_pool_launch(const StemPoolPlan& plan, int batch, cudaStream_t stream) {
   AI4E_REQUIRE(batch > 0 && batch <= plan.max_batch, "stem+pool: batch %d outside plan (max %d)", batch, plan.max_batch);
   StemPoolParams prm{};
   prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
-  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
+  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out; prm.weights = plan.weights;
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   stem_pool_pick_runs(plan.Pp, batch, sms, &prm);
   static std::atomic<unsigned long long> attr_done{0};
@@ -496,7 +499,7 @@ int stem_pool_launch_u8(const StemPoolPlan& plan, const uint8_t* d_images, int b
   prm.W = W;
   for (int c = 0; c < 3; ++c) { prm.mean[c] = mean[c]; prm.stdv[c] = stdv[c]; }
   prm.H = plan.H; prm.P = plan.P; prm.Q = plan.Q; prm.Pp = plan.Pp; prm.Qp = plan.Qp;
-  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out;
+  prm.stem_rb = plan.stem_rb; prm.relu = plan.relu; prm.bias = plan.bias; prm.out = (bf16*)plan.out; prm.weights = plan.weights;
   const int sms = plan.grid_sms > 0 ? std::min(plan.grid_sms, sm_count()) : sm_count();
   stem_pool_pick_runs(plan.Pp, batch, sms, &prm);
   static std::atomic<unsigned long long> attr_done{0};
