@@ -39,7 +39,9 @@ Built differently underneath:
     micro-batches.  A task function may instead `return engine.classify_later(image, then=...)`:
     the worker is released at once, the engine's single reaper thread runs `then` (which calls
     CompleteTask) when the micro-batch has finished, and the shell keeps the request counted and
-    maps a failure to FailTask until then - no thread is blocked per task;
+    maps a failure to FailTask until then - no thread is blocked per task.  Such a non-blocking
+    function may also be registered with `inline=True` (`api_async_func(..., inline=True)`): it
+    then runs on the request thread and a task needs no thread hand-off on its way in;
   * in-flight counters are guarded by a lock (:148-156 is unsynchronised);
   * `kwargs['request']` is a snapshot that stays readable on the worker thread (the reference
     passes the context-bound proxy, :181);
@@ -241,6 +243,12 @@ class APIService():
 
     def api_func(self, is_async, api_path, methods, request_processing_function, maximum_concurrent_requests,
                  content_types=None, content_max_length=None, trace_name=None, *args, **kwargs):
+        # `inline=True` (through the reference's unused **kwargs, so the signature stays as it is): the task
+        # function of an async endpoint runs on the request thread itself.  Only for functions that do not
+        # block - they hand their work to the engine with `classify_later` and return the Pending - and
+        # then a task costs no thread hand-off at all on its way in.
+        inline = bool(kwargs.pop('inline', False)) and is_async
+
         def register(func):
             if api_path not in self.func_properties:
                 self.func_properties[api_path] = {MAX_REQUESTS_KEY_NAME: maximum_concurrent_requests,
@@ -256,7 +264,12 @@ class APIService():
                     return self.wrap_sync_endpoint(trace_name, *view_args, **call_kwargs)
                 task = self.api_task_manager.AddTask(request)
                 call_kwargs['taskId'] = str(task['TaskId'])
-                self.wrap_async_endpoint(trace_name, *view_args, **call_kwargs)
+                if inline:
+                    call_kwargs['request'] = self._detached_request()
+                    with self._span(trace_name, call_kwargs):
+                        self._execute_func_with_counter(True, *view_args, **call_kwargs)
+                else:
+                    self.wrap_async_endpoint(trace_name, *view_args, **call_kwargs)
                 return 'TaskId: ' + call_kwargs['taskId']
 
             view.__name__ = 'api_' + api_path.replace('/', '')

@@ -325,6 +325,37 @@ def test_deferred_task_keeps_the_request_counted_and_fails_like_an_exception():
     assert fails == [["FailTask", "bad", "Task failed - try again"]]
 
 
+def test_inline_async_endpoint_runs_on_the_request_thread():
+    """`api_async_func(..., inline=True)`: a non-blocking task function (one that returns a Pending) runs on the
+    request thread - same response, same kwargs, same accounting and failure mapping, no worker hand-off."""
+    from ai4e_service import APIService
+    app = _flask()("i")
+    svc = APIService(app, type("L", (), {"tracer": None, "log_exception": lambda *a, **k: None})())
+    tm = RecordingTaskManager()
+    svc.api_task_manager = tm
+    seen, pend = {}, {}
+
+    @svc.api_async_func(api_path="/c", methods=["POST"], maximum_concurrent_requests=4, inline=True,
+                        request_processing_function=lambda request: {"n": len(request.get_data())})
+    def c_(*args, **kwargs):
+        seen[kwargs["taskId"]] = (threading.current_thread(), sorted(kwargs), kwargs["request"].headers.get("taskId"))
+        if kwargs["taskId"] == "boom":
+            raise RuntimeError("x")
+        p = pend[kwargs["taskId"]] = _FakePending()
+        return p
+
+    cl = app.test_client()
+    assert cl.post("/c", data=b"abc", headers={"taskId": "a"}).get_data(as_text=True) == "TaskId: a"
+    assert seen["a"][0] is threading.current_thread()                 # ran before the response, on this thread
+    assert seen["a"][1] == ["api_path", "func", "n", "request", "taskId"] and seen["a"][2] == "a"
+    assert svc.func_request_counts["/c"] == 1                          # still in flight: the Pending is open
+    pend["a"].resolve()
+    assert svc.func_request_counts["/c"] == 0
+    assert cl.post("/c", data=b"", headers={"taskId": "boom"}).get_data(as_text=True) == "TaskId: boom"
+    assert [c for c in tm.calls if c[0] == "FailTask"] == [["FailTask", "boom", "Task failed - try again"]]
+    assert svc.func_request_counts["/c"] == 0
+
+
 def test_metrics_endpoint_uses_the_platform_metric_names(monkeypatch):
     """in-flight requests under the name the HPA consumes
     (CURRENT_REQUESTS/{cluster}{prefix}{path}), counted while a request is being served, plus the

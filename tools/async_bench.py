@@ -12,6 +12,8 @@ UpdateTaskStatus('running') -> engine -> CompleteTask.  Task latency = CompleteT
 Modes (what the task function does with the image):
   blocked     engine.classify(image): one worker thread blocked per task
   later       return engine.classify_later(image, then=CompleteTask): no blocked thread, one reaper
+  inline      the same, registered with inline=True: the (non-blocking) task function runs on the request
+              thread, so a task needs no thread hand-off on its way in
   shell_only  no engine at all (the task completes at once): the host shell's own ceiling in Python
   native      no shell: feeder threads hand batches to Pool.submit_many and one thread drains
               Pool.poll - what the C side of the dispatcher sustains behind the Python shell
@@ -74,7 +76,7 @@ def build_service(engine, mode, store, per_task=1):
 
     @svc.api_async_func(api_path=PATH, methods=["POST"], request_processing_function=read_image,
                         maximum_concurrent_requests=1 << 20, content_types=["application/octet-stream"],
-                        content_max_length=1 << 26, trace_name="post:classify")
+                        content_max_length=1 << 26, trace_name="post:classify", inline=(mode == "inline"))
     def classify(*args, **kwargs):
         tid = kwargs["taskId"]
         tm.UpdateTaskStatus(tid, "running")
@@ -269,7 +271,7 @@ def main():
     ap.add_argument("--seconds", type=float, default=6.0)
     ap.add_argument("--clients", type=int, default=64)
     ap.add_argument("--inflight", type=int, default=None)
-    ap.add_argument("--mode", default="later", choices=["blocked", "later", "shell_only", "native"])
+    ap.add_argument("--mode", default="later", choices=["blocked", "later", "inline", "shell_only", "native"])
     ap.add_argument("--max-batch", type=int, default=64)
     ap.add_argument("--max-wait-us", type=int, default=2000)
     ap.add_argument("--images-per-task", type=int, default=1,

@@ -56,9 +56,9 @@ def main():
     print(f"\ntotal {tot:.1f} us over {sum(g[0] for g in agg.values())} launches")
     if a.traffic_json:
         steps = a.steps_in_capture or 1.0
-        conv = [g for k, g in agg.items() if "conv_igemm" in k or "bottleneck_tail" in k]
+        conv = [g for k, g in agg.items() if "conv_igemm" in k or "bottleneck_tail" in k or "stem_pool" in k]
         byts = sum(g[2] for g in conv) / steps
-        json.dump({"kernel": "conv_igemm_kernel + bottleneck_tail_kernel", "dram_bytes_per_step": byts, "launches_per_step": sum(g[0] for g in conv) / steps,
+        json.dump({"kernel": "conv_igemm_kernel + bottleneck_tail_kernel + stem_pool_kernel", "dram_bytes_per_step": byts, "launches_per_step": sum(g[0] for g in conv) / steps,
                    "us_per_step_under_ncu": sum(g[1] for g in conv) / steps, "steps_in_capture": steps,
                    "note": a.note}, open(a.traffic_json, "w"), indent=1)
 
