@@ -7,7 +7,8 @@ nvidia-smi topo -m > gpurun_out/m${N}_topo.txt 2>&1
 timeout 300 python -m pytest tests/test_gpu_dispatch.py -m gpu -x -q -k "two_gpus or pool_bulk" 2>&1 | tail -3
 timeout 200 python tools/async_bench.py --gpus $N --mode native --seconds 5 --clients $((N*2)) --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
 timeout 200 python tools/async_bench.py --gpus $N --mode later --seconds 5 --clients 8 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
-timeout 200 python tools/async_bench.py --gpus $N --mode later --seconds 5 --clients 8 --images-per-task 16 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 200 python tools/async_bench.py --gpus $N --mode inline --seconds 5 --clients 8 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
+timeout 200 python tools/async_bench.py --gpus $N --mode inline --seconds 5 --clients 8 --images-per-task 16 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
 timeout 200 python tools/async_bench.py --gpus $N --mode blocked --seconds 5 --clients 64 --out gpurun_out/m${N}_async.jsonl 2>&1 | tail -1 | cut -c1-420
 timeout 300 python tools/landcover_bench.py --gpus $N --seconds 4 --classify-rate 77000 --out gpurun_out/m${N}_landcover.jsonl 2>&1 | tail -4 | cut -c1-300
 PEAK=$(python - <<PY
@@ -21,6 +22,6 @@ timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 python - <<PY
 import json
 try:
-    d=json.load(open('gpurun_out/m${N}_bench.json')); print('torchrun N=${N}: value', round(d['value']), 'e2e', round(d['e2e']['value']), 'sustained', round(d['sustained']['value']), round(d['sustained']['e2e']))
+    d=json.loads(open('gpurun_out/m${N}_bench.json').read().strip().splitlines()[-1]); print('torchrun N=${N}: value', round(d['value']), 'e2e', round(d['e2e']['value']), 'sustained', round(d['sustained']['value']), round(d['sustained']['e2e']))
 except Exception as e: print('bench parse failed', e)
 PY
