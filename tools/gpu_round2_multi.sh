@@ -17,7 +17,15 @@ rows=[json.loads(l) for l in open('gpurun_out/m${N}_async.jsonl')]
 print(int([r for r in rows if r['mode']=='native'][0]['tasks_per_s']))
 PY
 )
-timeout 200 python tools/openloop_bench.py --gpus $N --peak $PEAK --load 0.5 0.8 --seconds 4 --out gpurun_out/m${N}_openloop.jsonl 2>&1 | tail -2 | cut -c1-420
+timeout 200 python tools/openloop_bench.py --gpus $N --peak $PEAK --load 0.5 0.8 --seconds 4 --feeders $((N*2)) --out gpurun_out/m${N}_openloop.jsonl 2>&1 | tail -2 | cut -c1-420
+timeout 600 python tools/extra_benches.py gpurun_out/m${N}_sweep.json --gpus $N --batches 1,8,64,512 > /dev/null 2> gpurun_out/m${N}_sweep.err
+python - <<PY
+import json
+try:
+    for r in json.load(open('gpurun_out/m${N}_sweep.json'))['batch_sweep']:
+        print('sweep N=${N}', r.get('batch'), round(r.get('images_per_s',0)), round(r.get('e2e_images_per_s',0)), r.get('latency_ms',{}).get('p50'), r.get('latency_ms',{}).get('p99'), r.get('error','')[:100])
+except Exception as e: print('sweep failed', e)
+PY
 timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 60 --warmup 5 --sustained-seconds 3 > gpurun_out/m${N}_bench.json 2> gpurun_out/m${N}_bench.err
 python - <<PY
 import json
