@@ -43,6 +43,7 @@ class Flask:
         self.view_functions = {}
         self.before_request_funcs = []
         self.config = {}
+        self._static_rules = {}  # path without converters -> (endpoint, methods): matched by one dict look-up
 
     # ---- registration
     def add_url_rule(self, rule, endpoint=None, view_func=None, methods=None, provide_automatic_options=None, **_):
@@ -55,6 +56,8 @@ class Flask:
             raise AssertionError(f"View function mapping is overwriting an existing endpoint function: {endpoint}")
         self.url_map.add(Rule(rule, endpoint=endpoint, methods=methods))
         self.view_functions[endpoint] = view_func
+        if "<" not in rule and rule not in self._static_rules:
+            self._static_rules[rule] = (endpoint, frozenset(methods))
 
     def route(self, rule, **options):
         def deco(f):
@@ -88,12 +91,15 @@ class Flask:
         return resp
 
     def full_dispatch(self, req: Request) -> Response:
-        adapter = self.url_map.bind_to_environ(req.environ)
         try:
             for f in self.before_request_funcs:
                 rv = f()
                 if rv is not None:
                     return self.make_response(rv)
+            hit = self._static_rules.get(req.path)
+            if hit is not None and req.method in hit[1] and req.method != "OPTIONS":
+                return self.make_response(self.view_functions[hit[0]]())  # a fixed path: no need for the matcher
+            adapter = self.url_map.bind_to_environ(req.environ)
             endpoint, values = adapter.match()
             if req.method == "OPTIONS":
                 resp = Response()

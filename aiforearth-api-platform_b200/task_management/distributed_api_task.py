@@ -109,26 +109,29 @@ class DistributedApiTaskManager:
         return s
 
     def _post(self, payload):
+        """-> (status code, stored task dict or None)"""
+        if self.store is not None:  # in-process store: the dict itself, no JSON round trip
+            return self.store.upsert_task(payload) if payload is not None else (400, None)
         body = json.dumps(payload) if payload is not None else None
-        if self.store is not None:
-            return self.store.upsert(body)
         try:
             r = self._session().post(self.cache_connector_upsert_url, data=body,
                                      headers={"Content-Type": "application/json"}, timeout=30)
-            return r.status_code, r.text
+            return r.status_code, (json.loads(r.text) if r.status_code == 200 else None)
         except Exception as e:  # noqa: BLE001
             print("task store POST failed: " + str(e))
-            return 599, ""
+            return 599, None
 
     def _get(self, task_id):
+        """-> (status code, task dict or None)"""
         if self.store is not None:
-            return self.store.get(task_id)
+            t = self.store.get_task(task_id)
+            return (200, t) if t is not None else (204, None)
         try:
             r = self._session().get(self.cache_connector_get_url, params={'taskId': task_id}, timeout=30)
-            return r.status_code, r.text
+            return r.status_code, (json.loads(r.text) if r.status_code == 200 else None)
         except Exception as e:  # noqa: BLE001
             print("task store GET failed: " + str(e))
-            return 599, ""
+            return 599, None
 
     @staticmethod
     def _now():
@@ -136,8 +139,8 @@ class DistributedApiTaskManager:
 
     # ---- the reference's public methods
     def AddTask(self):
-        code, text = self._post(None)  # an empty body: the platform answers 400 -> the error sentinel
-        return json.loads(text if code == 200 else _ERROR)
+        code, task = self._post(None)  # an empty body: the platform answers 400 -> the error sentinel
+        return task if code == 200 else json.loads(_ERROR)
 
     def _UpdateTaskStatus(self, taskId, status, backendStatus):
         final = backendStatus in ('completed', 'failed')
@@ -156,11 +159,11 @@ class DistributedApiTaskManager:
         if self.write_behind:
             self._enqueue(payload)
             return dict(payload)
-        code, text = self._post(payload)
+        code, task = self._post(payload)
         if code != 200:
             print("status code: " + str(code))
             return json.loads(_NOT_FOUND.format(taskId))
-        return json.loads(text)
+        return task
 
     def CompleteTask(self, taskId, status):
         return self._UpdateTaskStatus(taskId, status, 'completed')
@@ -180,20 +183,19 @@ class DistributedApiTaskManager:
         path = '{}/{}/{}'.format(version, organization_moniker, api_name)
         next_endpoint = '{}://{}/{}'.format(parsed_endpoint.scheme, parsed_endpoint.netloc, path)
         print("Sending to next endpoint: " + next_endpoint)
-        code, text = self._post({'TaskId': taskId, 'Timestamp': self._now(), 'Status': 'created',
+        code, task = self._post({'TaskId': taskId, 'Timestamp': self._now(), 'Status': 'created',
                                  'BackendStatus': 'created', 'Endpoint': next_endpoint, 'Body': body,
                                  'PublishToGrid': True})
         if code != 200:
             print("status code: " + str(code))
             return json.loads(_NOT_FOUND.format(taskId))
-        return json.loads(text)
+        return task
 
     def GetTaskStatus(self, taskId):
         if self.write_behind:
             self.flush()  # a read must see the writes this client has already accepted
-        code, text = self._get(taskId)
+        code, status = self._get(taskId)
         if code != 200:
             return json.loads(_NOT_FOUND.format(taskId))
-        status = json.loads(text)
         self._remember(taskId, status)
         return status

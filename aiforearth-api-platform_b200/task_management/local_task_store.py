@@ -31,7 +31,9 @@ ORIG_SUFFIX = "_ORIG"
 class LocalTaskStore:
     def __init__(self, publisher=None):
         self._lock = threading.Lock()
-        self.strings: dict[str, str] = {}
+        self.strings: dict[str, str] = {}        # "{TaskId}_ORIG" -> original body
+        self.tasks: dict[str, dict] = {}         # TaskId -> stored task (what Redis holds as JSON text)
+        self._paths: dict[str, str] = {}         # Endpoint -> its path (urlparse is the costly part of an upsert)
         self.sorted_sets: dict[str, dict[str, int]] = {}
         self.publisher = publisher  # callable(task_dict, body) -> bool, the "Event Grid / Service Bus" stand-in
         self.upserts = 0
@@ -39,17 +41,27 @@ class LocalTaskStore:
 
     # ---- the two HTTP functions, as (status_code, text)
     def upsert(self, body_text: str | None):
-        self.upserts += 1
+        """the HTTP function: JSON text in, (status, JSON text) out."""
         if not body_text or not body_text.strip():
+            self.upserts += 1
             return 400, ""
         try:
             task = json.loads(body_text)
             if isinstance(task, list):  # upstream takes the first element of an array body (:60-63)
                 task = task[0]
         except (ValueError, IndexError):
+            self.upserts += 1
             return 500, ""  # upstream: the deserialiser throws and the function answers 500 (:76-82)
+        code, stored = self.upsert_task(task)
+        return code, (json.dumps(stored) if code == 200 else "")
+
+    def upsert_task(self, task):
+        """the same state machine for a caller in this process that already holds the task as a dict (no
+        JSON round trip): -> (status, stored task dict)."""
+        self.upserts += 1
         if not isinstance(task, dict) or not task.get("Endpoint") or not task.get("BackendStatus"):
-            return 500, ""  # upstream: Uri(null) / BackendStatus.Equals on null throw inside the try (:130-142, :204-210)
+            return 500, None  # upstream: Uri(null) / BackendStatus.Equals on null throw inside the try (:130-142, :204-210)
+        task = dict(task)
         task_body = task.get("Body")
         if not task.get("TaskId"):
             task["TaskId"] = str(uuid.uuid4())
@@ -57,15 +69,17 @@ class LocalTaskStore:
         task["Body"] = None
         task.setdefault("Status", None)
         task.setdefault("PublishToGrid", False)
-        path = urlparse(task["Endpoint"]).path
+        endpoint = task["Endpoint"]
+        path = self._paths.get(endpoint)
+        if path is None:
+            path = self._paths[endpoint] = urlparse(endpoint).path
         task["EndpointPath"] = path  # a public getter of APITask, so the serialiser emits it (Classes/APITask.cs:20-27)
-        serialized = json.dumps(task)
         status = task["BackendStatus"]
         tid = task["TaskId"]
         now = int(time.time())
         publish = bool(task.get("PublishToGrid"))
         with self._lock:
-            self.strings[tid] = serialized
+            self.tasks[tid] = task
             self.sorted_sets.setdefault(f"{path}_{status}", {})[tid] = now
             if status == "running":
                 self.sorted_sets.get(f"{path}_created", {}).pop(tid, None)
@@ -83,27 +97,34 @@ class LocalTaskStore:
             except Exception:  # noqa: BLE001 - a failed publish moves the task to failed, as upstream
                 ok = False
             if not ok:
-                task["Status"] = "Failed - unable to send to backend service."
-                task["BackendStatus"] = "failed"
+                failed = dict(task)
+                failed["Status"] = "Failed - unable to send to backend service."
+                failed["BackendStatus"] = "failed"
                 with self._lock:
-                    self.strings[tid] = json.dumps(task)
+                    self.tasks[tid] = failed
                     self.sorted_sets.setdefault(f"{path}_failed", {})[tid] = now
                     self.sorted_sets.get(f"{path}_created", {}).pop(tid, None)
-        return 200, serialized
+        return 200, task  # (upstream answers with what it serialised before publishing, also when the publish failed)
 
     def get(self, task_id: str):
+        """the HTTP function: (200, JSON text) or (204, '')."""
+        t = self.get_task(task_id)
+        return (200, json.dumps(t)) if t is not None else (204, "")
+
+    def get_task(self, task_id: str):
+        """-> a copy of the stored task dict, or None (no JSON round trip)."""
         self.gets += 1
         with self._lock:
-            v = self.strings.get(task_id)
-        return (200, v) if v is not None else (204, "")
+            t = self.tasks.get(task_id)
+        return dict(t) if t is not None else None
 
     # ---- helpers for tests / the in-process platform
     def create_task(self, endpoint: str, body: str = "", publish: bool = False) -> dict:
         """what APIM's request policy does (APIManagement/request_policy.xml:5-21)."""
-        code, text = self.upsert(json.dumps({"TaskId": "", "Status": "created", "BackendStatus": "created",
-                                             "Endpoint": endpoint, "Body": body, "PublishToGrid": publish}))
+        code, task = self.upsert_task({"TaskId": "", "Status": "created", "BackendStatus": "created",
+                                       "Endpoint": endpoint, "Body": body, "PublishToGrid": publish})
         assert code == 200
-        return json.loads(text)
+        return dict(task)
 
     def set_members(self, key: str):
         with self._lock:
