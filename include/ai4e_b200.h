@@ -317,7 +317,9 @@ AI4E_API int ai4e_engine_submit_many(ai4e_engine* e, const uint8_t* const* h_ima
                             int row_stride, const uint64_t* tags_or_null, int notify, uint64_t* out_tickets);
 /* Up to `capacity` announced completions, oldest first; blocks up to timeout_us for the first one
  * (< 0: for ever, 0: never).  Any output array may be NULL.  status[i] is AI4E_OK or the error that
- * failed the ticket's batch; top_idx5 / top_prob5 are [capacity][5].  *out_n may be 0 (timeout). */
+ * failed the ticket's batch; top_idx5 / top_prob5 are [capacity][5].  *out_n may be 0 (timeout).
+ * Records stay queued until somebody polls them (40 bytes each): submit with notify only what a reaper
+ * will collect.  The replicas of a pool announce into the POOL's queue: poll the pool, not its engines. */
 AI4E_API int ai4e_engine_poll(ai4e_engine* e, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
                      int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n);
 /* A caller-made batch (e.g. the 256 chips of a land-cover tile, or a dispatcher that already
