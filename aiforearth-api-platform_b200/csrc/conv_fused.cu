@@ -46,7 +46,10 @@ struct FusedCfg {
   static constexpr int kMidBytes = kKB2 * kChunkBytes;    // 16 / 32 KiB
   static constexpr int kBiasBytes = kEpiWarps * kChunkN * 4;
   static constexpr int kResBytes = 4 * kChunkBytes;       // two residual/staging buffers per epilogue side
-  static constexpr int kMaxStages = 8;
+#ifndef AI4E_FUSED_MAX_STAGES
+#define AI4E_FUSED_MAX_STAGES 8
+#endif
+  static constexpr int kMaxStages = AI4E_FUSED_MAX_STAGES;  // (-DAI4E_FUSED_MAX_STAGES=n: stage-count experiments)
   // full[], empty[], acc1_full/empty[2], mid_full/empty, acc2_full/empty[2], res_full/empty[4], tmem ptr
   static constexpr int kBarBytes = (2 * kMaxStages + 4 + 2 + 4 + 8 + 1) * 8 + 16;
   static constexpr int kSmemLimit = 227 * 1024;
