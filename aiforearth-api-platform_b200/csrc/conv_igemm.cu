@@ -87,16 +87,6 @@ constexpr int kRowsMaxGroups = 18;                       // 128-byte groups per 
 constexpr int kRowsStage = 7 * kRowsMaxGroups * 128 + 256;  // 16 KiB incl. over-read slack
 constexpr int kModeGeneric = 0, kModeStemIm2col = 1, kModeStemRows = 2;
 
-// Epilogue warps of this kernel: TWO per (side, TMEM lane quadrant), each taking 32 of a chunk's 64
-// channels.  Pipeline traces put one 64-channel chunk at 1,500 (2,400 with a residual) cycles of one warp's
-// dependent instruction chain, with two epilogue warps per scheduler issuing 17 % of the time - and the
-// layers with many output channels per K block (downsample, conv3, 1x1 at K = 64) ran at exactly that
-// pace.  Halving the chain and doubling the warps per scheduler is what the registers allow (32 + 16
-// instead of 64 + 32 live values per thread: 640 threads fit).
-constexpr int kIgHalves = 2;
-constexpr int kIgEpiWarps = kEpiWarps * kIgHalves;         // 16
-constexpr int kIgThreads = 64 + kIgEpiWarps * 32 + 64;     // A producer, MMA, 16 epilogue warps, B producer, residual warp
-
 // kPair: the CTAs of a 2-CTA cluster work on one 256-row tile with tcgen05 cta_group::2 - each
 // brings its own 128 rows of A and HALF of the weight tile, the tensor cores of both SMs read both
 // halves.  Operand bytes pulled from L2 per MMA drop from 16 KB + BLOCK_N * 128 to 16 KB +
@@ -135,7 +125,7 @@ struct IgemmCfg {
 };
 
 template <int BLOCK_N, int kMode, bool kPair>
-__global__ void __launch_bounds__(kIgThreads, 1)
+__global__ void __launch_bounds__(kIgemmThreads, 1)
 conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                   const IgemmParams p) {
@@ -191,11 +181,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       mbar_init(tmem_full_bar(s), 1);
       // one arrival per epilogue warp that reads the tile (pair: of both CTAs, on the leader's
       // barrier): a 64-wide tile is drained by one side
-      mbar_init(tmem_empty_bar(s), (BLOCK_N == kChunkN ? 4 * kIgHalves : kIgEpiWarps) * kCtas);
+      mbar_init(tmem_empty_bar(s), (BLOCK_N == kChunkN ? 4 : kEpiWarps) * kCtas);
     }
     for (int s = 0; s < 4; ++s) {
       mbar_init(res_full_bar(s), 1);
-      mbar_init(res_empty_bar(s), 4 * kIgHalves);
+      mbar_init(res_empty_bar(s), 4);
     }
     mbar_init(b_full_bar, 1);
     tma_prefetch_desc(&tmap_out);
@@ -305,7 +295,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
       }
     }
-  } else if (warp == 2 + kIgEpiWarps) {
+  } else if (warp == 2 + kEpiWarps) {
     // ------------------------------- B (weights) producer, generic mode ----------
     // One thread needs ~190 cycles per TMA instruction and ~615 per stage for wait + expect_tx +
     // two loads (clock64 trace, B200): longer than a stage's MMAs.  Two threads halve that.
@@ -413,34 +403,31 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       }
       AI4E_TRACE(lane == 0, 1011);  // all MMAs issued
     }
-  } else if (warp < 2 + kIgEpiWarps) {
+  } else if (warp < 2 + kEpiWarps) {
     // ------------------------------- epilogue -----------------------------------
-    // Sixteen warps, no block-level barriers.  A warp can read only its own TMEM lane quadrant (warp id
-    // % 4); "side" and "half" complete its identity: the 64-channel chunks of the CTA's tiles, numbered
-    // q = tile_iteration * kChunks + c, alternate between the two sides, and the two warps of a (side,
-    // quadrant) take channels [0, 32) and [32, 64) of each chunk.  The pair shares a 32-row x 64-channel
-    // output staging slice (each warp writes its 64-byte half of every 128-byte swizzled row) which the
-    // first of them stores with one 4 KB TMA box; two 64-thread named barriers per chunk order "the
-    // previous store has read the slice" -> both write -> store.  Residual chunks (128 rows x 64
-    // channels) arrive through the residual warp below.  Thread = one pixel row.  The chunk's bias is
-    // staged in warp-private shared memory: with 227 KB of the SM carved out as shared memory L1 is
-    // tiny, and serialised LDG.128 of the bias were most of the arithmetic phase (pipeline trace, B200).
+    // Eight independent warps, no block-level barriers.  A warp can read only its own TMEM lane
+    // quadrant (warp id % 4), so quadrant and "side" (warp - 2) / 4 identify it; the 64-channel
+    // chunks of the CTA's tiles, numbered q = tile_iteration * kChunks + c, alternate between the two
+    // sides.  Each warp owns a 32-row x 64-channel output staging slice which it stores with its own
+    // 4 KB TMA box; residual chunks (128 rows) arrive through the residual warp below.  Per chunk:
+    // accumulator load, arithmetic into packed registers, wait until the previous store has read
+    // the staging slice, STS, store.  Thread = one pixel row, 64 channels = one 128-byte swizzled row.
+    // The bias of the chunk is staged in a warp-private 256 bytes of shared memory: with 227 KB of
+    // the SM carved out as shared memory L1 is tiny, and sixteen serialised LDG.128 of the bias
+    // were most of the ~850-cycle arithmetic phase (pipeline trace, B200).
     const int ew = warp - 2;
+    const int side = ew >> 2;
     const int quad = warp & 3;
-    const int side = (ew >> 2) & 1;
-    const int half = ew >> 3;
-    const int sq = side * 4 + quad;  // staging slice and pair barrier of this (side, quadrant)
     const bool has_res = p.residual != nullptr;
     const bool relu = p.relu != 0;
     constexpr int kChunks = BLOCK_N / kChunkN;
-    const uint32_t out_buf = epi_base + sq * kSliceBytes;                                   // [out x8]
+    const uint32_t out_buf = epi_base + ew * kSliceBytes;                                   // [out x8]
     uint8_t* const out_gen = smem_raw + (out_buf - smem_u32(smem_raw));
-    float* const bias_gen = reinterpret_cast<float*>(smem_raw + (epi_base + kEpiWarps * kSliceBytes - smem_u32(smem_raw))) + ew * 32;
+    float* const bias_gen = reinterpret_cast<float*>(smem_raw + (epi_base + kEpiWarps * kSliceBytes - smem_u32(smem_raw))) + ew * kChunkN;
     const uint8_t* const res_gen0 =                                                         // [res x2] per side
         smem_raw + (epi_base + Cfg::kEpiFixed + (2 * side) * kChunkBytes - smem_u32(smem_raw)) + quad * kSliceBytes;
     const uint32_t sw = (uint32_t)(lane & 7);
     const uint32_t row_off = (uint32_t)lane * 128u;
-    const uint32_t pair_bar = 1u + (uint32_t)sq;
     // A warp's chunks: q = side, side + 2, ... over the CTA's tiles (kChunks chunks each).  `step`
     // advances by two chunks without divisions (they cost ~290 cycles per chunk in the trace).
     struct Chunk { int tile, c, m0, n0c, tile_m, tile_n; uint32_t it; };
@@ -470,17 +457,20 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       while (k.c >= kChunks) { k.c -= kChunks; next_tile(k); }
       return place(k);
     };
-    uint32_t v[32];
+    uint32_t v[64];
+    uint32_t (&vlo)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[0]);
+    uint32_t (&vhi)[32] = *reinterpret_cast<uint32_t(*)[32]>(&v[32]);
     auto issue_ld = [&](const Chunk& k) {
-      const uint32_t t_addr = tmem_base + (k.it & 1u) * BLOCK_N + k.c * kChunkN + half * 32 + ((uint32_t)(quad * 32) << 16);
-      tmem_ld_32x32b_x32(t_addr, v);
+      const uint32_t t_addr = tmem_base + (k.it & 1u) * BLOCK_N + k.c * kChunkN + ((uint32_t)(quad * 32) << 16);
+      tmem_ld_32x32b_x32(t_addr, vlo);
+      tmem_ld_32x32b_x32(t_addr + 32, vhi);
     };
     pdl_wait();
     Chunk cur, nxt;
     bool have = first(cur);
     bool ld_issued = false;  // the accumulator load of `cur` was already issued at the end of the previous chunk
-    float bias1 = 0.f;
-    if (have) bias1 = __ldg(p.bias + cur.n0c + half * 32 + lane);
+    float2 bias2 = make_float2(0.f, 0.f);
+    if (have) bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + cur.n0c) + lane);
     uint32_t gs = 0;  // chunks this warp has processed: selects the residual buffer and phase
     for (uint32_t q = side; have; q += 2, ++gs) {
       const uint32_t acc = cur.it & 1u;
@@ -494,12 +484,13 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         issue_ld(cur);
       }
       AI4E_TRACE(etr, 768 + 8 * gs + 0);  // chunk start (accumulator load issued)
-      bias_gen[lane] = bias1;  // (the previous chunk's readers passed a __syncwarp)
+      reinterpret_cast<float2*>(bias_gen)[lane] = bias2;  // (the previous chunk's readers passed a __syncwarp)
       const uint8_t* const res_row = res_gen0 + (gs & 1u) * kChunkBytes + row_off;
       if (has_res) mbar_wait(res_full_bar(2 * side + (gs & 1u)), (gs >> 1) & 1u);
       __syncwarp();
       const float4* const b4 = reinterpret_cast<const float4*>(bias_gen);
-      tmem_wait_ld_pin(v);
+      tmem_wait_ld_pin(vlo);
+      tmem_wait_ld_pin(vhi);
       AI4E_TRACE(etr, 768 + 8 * gs + 1);  // accumulators in registers, residual landed
       // last chunk of this tile for this warp: its TMEM reads are done, free the accumulator stage
       if (cur.c + 2 >= kChunks) {
@@ -510,26 +501,22 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           else mbar_arrive(tmem_empty_bar(acc));
         }
       }
-      uint4 o[4];
+      uint4 o[8];
       if (has_res) {
-        if (relu) epi_half<true, true>(v, b4, res_row, sw, half, o);
-        else epi_half<true, false>(v, b4, res_row, sw, half, o);
+        if (relu) epi_row<true, true>(v, b4, res_row, sw, o);
+        else epi_row<true, false>(v, b4, res_row, sw, o);
       } else {
-        if (relu) epi_half<false, true>(v, b4, nullptr, sw, half, o);
-        else epi_half<false, false>(v, b4, nullptr, sw, half, o);
+        if (relu) epi_row<false, true>(v, b4, nullptr, sw, o);
+        else epi_row<false, false>(v, b4, nullptr, sw, o);
       }
       AI4E_TRACE(etr, 768 + 8 * gs + 2);  // arithmetic done
-      if (has_res) {  // this warp has read its half of the residual rows
-        __syncwarp();
-        if (lane == 0) mbar_arrive(res_empty_bar(2 * side + (gs & 1u)));
-      }
       // this warp's next chunk: fetch its bias and, if its accumulator is already complete, start
       // the TMEM load now so that it travels during the staging and the store below
       have = step(cur, nxt);
       ld_issued = false;
       AI4E_TRACE(etr, 768 + 8 * gs + 3);  // next chunk located
       if (have) {
-        bias1 = __ldg(p.bias + nxt.n0c + half * 32 + lane);
+        bias2 = __ldg(reinterpret_cast<const float2*>(p.bias + nxt.n0c) + lane);
         bool ready = true;
         if (nxt.c < 2) {
           ready = __all_sync(0xffffffffu, mbar_test_wait(tmem_full_bar(nxt.it & 1u), (nxt.it >> 1) & 1u));
@@ -541,17 +528,18 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         }
       }
       AI4E_TRACE(etr, 768 + 8 * gs + 4);  // next accumulator load issued (or not ready)
-      // the TMA store of the pair's previous chunk (issued by the half-0 warp) must have read the slice
-      if (half == 0 && lane == 0) bulk_wait_group_read<0>();
-      named_bar_sync(pair_bar, 64);
+      // the TMA store of this warp's previous chunk must have read the staging slice by now
+      if (lane == 0) bulk_wait_group_read<0>();
+      __syncwarp();
+      if (has_res && lane == 0) mbar_arrive(res_empty_bar(2 * side + (gs & 1u)));  // this warp is done with it
       AI4E_TRACE(etr, 768 + 8 * gs + 5);  // staging slice free
 #pragma unroll
-      for (int j = 0; j < 4; ++j)
-        *reinterpret_cast<uint4*>(out_gen + row_off + ((((uint32_t)(half * 4 + j)) ^ sw) << 4)) = o[j];
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<uint4*>(out_gen + row_off + ((((uint32_t)j) ^ sw) << 4)) = o[j];
       fence_proxy_async_smem();  // generic-proxy writes -> visible to the TMA (async proxy)
-      named_bar_sync(pair_bar, 64);
+      __syncwarp();
       AI4E_TRACE(etr, 768 + 8 * gs + 6);  // staged
-      if (half == 0 && lane == 0) {
+      if (lane == 0) {
         if constexpr (kRows) {
           if (quad * 32 < p.Q) tma_store_3d(&tmap_out, out_buf, 0, quad * 32, cur.tile);  // row `tile` of [N*P][Q][64]
         } else {
@@ -562,9 +550,9 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       AI4E_TRACE(etr, 768 + 8 * gs + 7);  // store issued
       cur = nxt;
     }
-    if (half == 0 && lane == 0) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
+    if (lane == 0) bulk_wait_group_read<0>();  // shared memory must outlive the last TMA store
     AI4E_TRACE(ew == 0 && lane == 0, 1012);  // epilogue done
-  } else if (warp == 3 + kIgEpiWarps) {
+  } else if (warp == 3 + kEpiWarps) {
     // ------------------------------- residual warp -------------------------------
     // One thread walks the CTA's chunks in order and keeps two 128-row x 64-channel residual
     // buffers per epilogue side filled; the four warps of a side release a buffer through
@@ -808,7 +796,7 @@ static int igemm_launch_bn(const IgemmPlan& plan, const CUtensorMap& tb, const I
   static std::atomic<unsigned long long> attr_done{0};  // bit per device
   if (int rc = ensure_dyn_smem(conv_igemm_kernel<BN, kMode, kPair>, IgemmCfg<BN, kMode, kPair>::kSmemLimit, attr_done))
     return rc;
-  AI4E_CUDA_TRY(launch_pdl_cluster(conv_igemm_kernel<BN, kMode, kPair>, dim3(grid), dim3(kIgThreads),
+  AI4E_CUDA_TRY(launch_pdl_cluster(conv_igemm_kernel<BN, kMode, kPair>, dim3(grid), dim3(kIgemmThreads),
                                    (size_t)IgemmCfg<BN, kMode, kPair>::smem_bytes(prm.residual != nullptr), stream,
                                    kPair ? 2 : 1, plan.tmap_a, tb, plan.tmap_out, plan.tmap_res, prm));
   return AI4E_OK;

@@ -43,32 +43,6 @@ __device__ __forceinline__ void epi_row(const uint32_t (&v)[64], const float4* b
     }
   }
 }
-
-// The same for half a chunk: 32 channels (`half` = 0 / 1 selects channels [0, 32) or [32, 64) of the chunk's
-// 128-byte rows), `v` = the thread's 32 fp32 accumulators, `b4` = this warp's 32 bias values in shared memory.
-template <bool kRes, bool kRelu>
-__device__ __forceinline__ void epi_half(const uint32_t (&v)[32], const float4* b4, const uint8_t* res_row, uint32_t sw,
-                                         int half, uint4 (&o)[4]) {
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float4 ba = b4[2 * j], bb = b4[2 * j + 1];
-    float x[8];
-    x[0] = __uint_as_float(v[8 * j + 0]) + ba.x; x[1] = __uint_as_float(v[8 * j + 1]) + ba.y;
-    x[2] = __uint_as_float(v[8 * j + 2]) + ba.z; x[3] = __uint_as_float(v[8 * j + 3]) + ba.w;
-    x[4] = __uint_as_float(v[8 * j + 4]) + bb.x; x[5] = __uint_as_float(v[8 * j + 5]) + bb.y;
-    x[6] = __uint_as_float(v[8 * j + 6]) + bb.z; x[7] = __uint_as_float(v[8 * j + 7]) + bb.w;
-    if constexpr (kRes) {
-      const uint4 r = *reinterpret_cast<const uint4*>(res_row + ((((uint32_t)(half * 4 + j)) ^ sw) << 4));
-      x[0] += bf16_lo(r.x); x[1] += bf16_hi(r.x); x[2] += bf16_lo(r.y); x[3] += bf16_hi(r.y);
-      x[4] += bf16_lo(r.z); x[5] += bf16_hi(r.z); x[6] += bf16_lo(r.w); x[7] += bf16_hi(r.w);
-    }
-    o[j] = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
-    if constexpr (kRelu) {
-      o[j].x = relu_bf16x2(o[j].x); o[j].y = relu_bf16x2(o[j].y);
-      o[j].z = relu_bf16x2(o[j].z); o[j].w = relu_bf16x2(o[j].w);
-    }
-  }
-}
 #endif
 
 }  // namespace ai4e
