@@ -16,6 +16,7 @@
 #include <zlib.h>
 
 #include <cstring>
+#include <new>
 #include <vector>
 
 namespace ai4e {
@@ -33,7 +34,18 @@ inline int paeth(int a, int b, int c) {
 }  // namespace
 
 // Headers only when rgb == nullptr (sizes the output); otherwise decodes into rgb[height][width][3].
+static int png_host_decode_impl(const uint8_t* data, uint64_t len, uint8_t* rgb, uint64_t capacity, int* out_h, int* out_w);
+
 int png_host_decode(const uint8_t* data, uint64_t len, uint8_t* rgb, uint64_t capacity, int* out_h, int* out_w) {
+  try {  // no exception may cross the C ABI: a payload that makes an allocation fail is an error, not a crash
+    return png_host_decode_impl(data, len, rgb, capacity, out_h, out_w);
+  } catch (const std::bad_alloc&) {
+    set_last_error("png: out of memory while decoding");
+    return AI4E_ERR_NOMEM;
+  }
+}
+
+static int png_host_decode_impl(const uint8_t* data, uint64_t len, uint8_t* rgb, uint64_t capacity, int* out_h, int* out_w) {
   static const uint8_t kSig[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1a, '\n'};
   AI4E_REQUIRE(data && out_h && out_w, "png: null pointer");
   AI4E_REQUIRE(len >= 8 + 25 && memcmp(data, kSig, 8) == 0, "png: not a PNG stream (bad signature)");
@@ -80,7 +92,7 @@ int png_host_decode(const uint8_t* data, uint64_t len, uint8_t* rgb, uint64_t ca
     pos += 12 + (uint64_t)n;
   }
   AI4E_REQUIRE(have_ihdr, "png: no IHDR");
-  AI4E_REQUIRE(!idat.empty(), "png: no image data");
+  AI4E_REQUIRE(!idat.empty() && idat.size() < (1ull << 31), "png: no image data (or more than 2 GiB of it)");
   AI4E_REQUIRE(ctype != 3 || pal_n > 0, "png: palette image without PLTE");
 
   const int bpp = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : 4;  // bytes per pixel
