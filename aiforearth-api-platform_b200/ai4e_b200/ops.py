@@ -114,9 +114,9 @@ def image_probe(data: bytes):
 
 
 def jpeg_entropy_decode(data: bytes):
-    """host only: baseline JPEG bytes -> (JpegInfo, int16 record [3 x 64 quantisation values, then
+    """host only: JPEG bytes (Huffman-coded sequential or progressive) -> (JpegInfo, int16 record [3 x 64 quantisation values, then
     the quantised coefficients per component, natural order]).  Raises Ai4eError for unsupported
-    streams (progressive, CMYK, ...)."""
+    streams (arithmetic coding, CMYK, ...)."""
     import ctypes as C
     import numpy as np
     lib = L.load()
@@ -129,7 +129,7 @@ def jpeg_entropy_decode(data: bytes):
 
 
 def jpeg_decode(data: bytes, stream=None) -> torch.Tensor:
-    """baseline JPEG bytes -> uint8 [H, W, 3] RGB on the GPU, bit-identical to Pillow / libjpeg-turbo
+    """JPEG bytes -> uint8 [H, W, 3] RGB on the GPU, bit-identical to Pillow / libjpeg-turbo
     (entropy decode on this thread, IDCT + upsampling + colour conversion on the device)."""
     import ctypes as C
     lib = L.load()

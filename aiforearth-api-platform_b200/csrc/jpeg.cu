@@ -1,9 +1,9 @@
-// K0 - baseline JPEG decode, hybrid: entropy decoding on the host, everything else on the GPU.
+// K0 - JPEG decode (baseline and progressive), hybrid: entropy decoding on the host, everything else on the GPU.
 //
 // Requests carry encoded images (the reference gates on image MIME types,
 // APIs/1.0/base-py/ai4e_service.py:72,127-129, and leaves decoding to the callback it calls at
 // :203 - Pillow / libjpeg-turbo in a PyTorch container).  This file matches libjpeg's output bit
-// for bit: Huffman decoding per ITU T.81 F.2.2, the accurate integer IDCT (jidctint.c "islow",
+// for bit: Huffman decoding per ITU T.81 F.2.2 (progressive scans per annex G, after jdphuff.c), the accurate integer IDCT (jidctint.c "islow",
 // the library default), fancy triangle-filter chroma upsampling (jdsample.c h2v1 / h2v2, edge
 // rows and columns replicated as jdmainct.c does) and the fixed-point YCbCr -> RGB tables of
 // jdcolor.c.  Oracle: oracle/jpeg_oracle.py, pinned to Pillow on tests/golden/jpeg/.
@@ -128,6 +128,148 @@ inline int extend(int v, int s) { return v < (1 << (s - 1)) ? v - (1 << s) + 1 :
 
 inline int rd16(const uint8_t* p) { return (p[0] << 8) | p[1]; }
 
+inline uint32_t getbits(BitReader& br, int k) {
+  if (k == 0) return 0;
+  if (br.n < k) br.fill();
+  return br.get(k);
+}
+
+struct ScanSpec {
+  int ns = 0;
+  int comp[3] = {0, 0, 0};  // frame component index of each scan component
+  int ss = 0, se = 63, ah = 0, al = 0;
+  bool progressive = false;
+};
+
+// One scan into the record.  Sequential scans (SOF0 / SOF1) carry all 64 coefficients of their components;
+// progressive scans (SOF2) are one of the four kinds of ITU T.81 annex G, decoded as libjpeg's jdphuff.c
+// does (DC first / refinement, AC first pass with end-of-band runs, AC refinement with correction bits).
+// A scan of one component walks that component's own blocks in raster order (without the padding to whole
+// MCUs); a scan of several walks the frame's MCUs.  Leaves br.p at (or before) the marker that ends it.
+int decode_scan(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, const int* td, const int* ta,
+                const std::vector<HuffTable>& dc, const std::vector<HuffTable>& ac, int16_t* record) {
+  const int mcus_x = f.blocks_w[0] / f.h[0], mcus_y = f.blocks_h[0] / f.v[0];
+  const bool inter = sc.ns > 1;
+  const int c0 = sc.comp[0];
+  const int bw0 = (f.comp_w[c0] + 7) / 8, bh0 = (f.comp_h[c0] + 7) / 8;
+  const int total = inter ? mcus_x * mcus_y : bw0 * bh0;
+  const int ri = f.restart_interval;
+  const int p1 = 1 << sc.al, m1 = -(1 << sc.al);
+  int pred[3] = {0, 0, 0};
+  int eobrun = 0;
+  int until_restart = ri ? ri : total;
+  for (int mcu = 0; mcu < total; ++mcu) {
+    if (until_restart == 0) {  // expect RSTn: byte-align, skip the marker, reset the predictors and the run
+      br.fill();
+      const uint8_t* q = br.p;
+      // br.p sits on the 0xFF of the marker once the reader has hit it; otherwise search forward
+      while (q + 1 < br.end && !(q[0] == 0xFF && q[1] >= 0xD0 && q[1] <= 0xD7)) ++q;
+      AI4E_REQUIRE(q + 1 < br.end, "jpeg: restart marker missing");
+      br.p = q + 2;
+      br.reset_bits();
+      pred[0] = pred[1] = pred[2] = 0;
+      eobrun = 0;
+      until_restart = ri;
+    }
+    --until_restart;
+    const int my = inter ? mcu / mcus_x : 0, mx = inter ? mcu - my * mcus_x : 0;
+    for (int si = 0; si < sc.ns; ++si) {
+      const int c = sc.comp[si];
+      const int nv = inter ? f.v[c] : 1, nh = inter ? f.h[c] : 1;
+      for (int by = 0; by < nv; ++by) {
+        for (int bx = 0; bx < nh; ++bx) {
+          const int64_t brow = inter ? my * f.v[c] + by : mcu / bw0, bcol = inter ? mx * f.h[c] + bx : mcu % bw0;
+          int16_t* blk = record + f.coef_off[c] + (brow * f.blocks_w[c] + bcol) * 64;
+          if (!sc.progressive) {
+            int s = decode_symbol(br, dc[td[c]]);
+            AI4E_REQUIRE(s >= 0 && s <= 11, "jpeg: corrupt DC code");
+            if (s) pred[c] += extend((int)getbits(br, s), s);
+            blk[0] = (int16_t)pred[c];
+            for (int k = 1; k < 64;) {
+              const int rs = decode_symbol(br, ac[ta[c]]);
+              AI4E_REQUIRE(rs >= 0, "jpeg: corrupt AC code");
+              const int r = rs >> 4;
+              s = rs & 15;
+              if (s == 0) {
+                if (r != 15) break;
+                k += 16;
+                continue;
+              }
+              k += r;
+              AI4E_REQUIRE(k < 64, "jpeg: AC coefficient index past 63");
+              blk[kZigzag[k]] = (int16_t)extend((int)getbits(br, s), s);
+              ++k;
+            }
+          } else if (sc.ss == 0) {
+            if (sc.ah == 0) {  // DC, first pass
+              const int s = decode_symbol(br, dc[td[c]]);
+              AI4E_REQUIRE(s >= 0 && s <= 11, "jpeg: corrupt DC code");
+              if (s) pred[c] += extend((int)getbits(br, s), s);
+              blk[0] = (int16_t)(pred[c] * p1);
+            } else if (getbits(br, 1)) {  // DC refinement: one more bit
+              blk[0] = (int16_t)(blk[0] | p1);
+            }
+          } else if (sc.ah == 0) {  // AC, first pass
+            if (eobrun > 0) { --eobrun; continue; }
+            for (int k = sc.ss; k <= sc.se; ++k) {
+              const int rs = decode_symbol(br, ac[ta[c]]);
+              AI4E_REQUIRE(rs >= 0, "jpeg: corrupt AC code");
+              const int r = rs >> 4, s = rs & 15;
+              if (s) {
+                k += r;
+                AI4E_REQUIRE(k < 64, "jpeg: AC coefficient index past 63");
+                blk[kZigzag[k]] = (int16_t)(extend((int)getbits(br, s), s) * p1);
+              } else if (r == 15) {
+                k += 15;  // ZRL: sixteen zeros (the loop adds the last)
+              } else {
+                eobrun = (1 << r) + (int)getbits(br, r) - 1;
+                break;
+              }
+            }
+          } else {  // AC refinement
+            int k = sc.ss;
+            if (eobrun == 0) {
+              for (; k <= sc.se; ++k) {
+                const int rs = decode_symbol(br, ac[ta[c]]);
+                AI4E_REQUIRE(rs >= 0, "jpeg: corrupt AC code");
+                int r = rs >> 4, s = rs & 15;
+                if (s) {
+                  s = getbits(br, 1) ? p1 : m1;  // the new coefficient's sign (its magnitude is 1 << al)
+                } else if (r != 15) {
+                  eobrun = (1 << r) + (int)getbits(br, r);
+                  break;  // end of band: the rest of this block gets correction bits only
+                }
+                // over already-nonzero coefficients (one correction bit each) and r still-zero ones
+                while (k <= sc.se) {
+                  int16_t& co = blk[kZigzag[k]];
+                  if (co != 0) {
+                    if (getbits(br, 1) && (co & p1) == 0) co = (int16_t)(co + (co >= 0 ? p1 : m1));
+                  } else if (--r < 0) {
+                    break;
+                  }
+                  ++k;
+                }
+                if (s) {
+                  AI4E_REQUIRE(k < 64, "jpeg: AC coefficient index past 63");
+                  blk[kZigzag[k]] = (int16_t)s;
+                }
+              }
+            }
+            if (eobrun > 0) {
+              for (; k <= sc.se; ++k) {
+                int16_t& co = blk[kZigzag[k]];
+                if (co != 0 && getbits(br, 1) && (co & p1) == 0) co = (int16_t)(co + (co >= 0 ? p1 : m1));
+              }
+              --eobrun;
+            }
+          }
+        }
+      }
+    }
+  }
+  return AI4E_OK;
+}
+
 }  // namespace
 
 // headers (+ entropy decode when `record` is given).  Returns AI4E_OK or an error with a message.
@@ -139,9 +281,12 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
   bool have_qt[4] = {false, false, false, false};
   std::vector<HuffTable> dc(4), ac(4);
   int tq[3] = {0, 0, 0}, cid[3] = {0, 0, 0}, td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
-  bool have_frame = false, have_scan = false;
+  bool have_frame = false, have_scan = false, progressive = false, done = false;
+  bool latched[3] = {false, false, false};   // quantisation table copied into the record (at the component's first scan)
+  bool seen[3] = {false, false, false};      // sequential files: the component's scan has been decoded
+  int scans = 0;
   uint64_t pos = 2;
-  while (pos + 4 <= len && !have_scan) {
+  while (pos + 4 <= len && !done) {
     AI4E_REQUIRE(data[pos] == 0xFF, "jpeg: marker expected at byte %llu", (unsigned long long)pos);
     while (pos < len && data[pos] == 0xFF) ++pos;
     AI4E_REQUIRE(pos < len, "jpeg: truncated");
@@ -175,7 +320,9 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
         AI4E_REQUIRE(build_table(tc ? ac[th] : dc[th], seg + i + 1, seg + i + 17, ns), "jpeg: invalid Huffman code lengths");
         i += 17 + ns;
       }
-    } else if (m == 0xC0 || m == 0xC1) {
+    } else if (m == 0xC0 || m == 0xC1 || m == 0xC2) {
+      AI4E_REQUIRE(!have_frame, "jpeg: second frame header");
+      progressive = m == 0xC2;
       AI4E_REQUIRE(n >= 6 && seg[0] == 8, "jpeg: only 8-bit samples are supported");
       out->height = rd16(seg + 1);
       out->width = rd16(seg + 3);
@@ -224,103 +371,87 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
       out->record_int16 = (off + 63) & ~(int64_t)63;
       out->plane_bytes = (plane + 255) & ~(int64_t)255;
       have_frame = true;
-    } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
-      set_last_error("jpeg: SOF%d (progressive / lossless / arithmetic) is not supported, only baseline Huffman", m - 0xC0);
+    } else if (m >= 0xC3 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+      set_last_error("jpeg: SOF%d (lossless / hierarchical / arithmetic coding) is not supported, only Huffman-coded "
+                     "sequential and progressive JPEG", m - 0xC0);
       return AI4E_ERR_UNSUPPORTED;
     } else if (m == 0xDD) {
       AI4E_REQUIRE(n >= 2, "jpeg: bad DRI");
       out->restart_interval = rd16(seg);
     } else if (m == 0xDA) {
       AI4E_REQUIRE(have_frame, "jpeg: SOS before SOF");
-      AI4E_REQUIRE(n >= 1 && n >= 1 + 2 * seg[0] + 3, "jpeg: bad scan header");
-      if (seg[0] != out->components) {
-        set_last_error("jpeg: multi-scan files are not supported");
-        return AI4E_ERR_UNSUPPORTED;
-      }
+      AI4E_REQUIRE(n >= 1 && seg[0] >= 1 && seg[0] <= out->components && n >= 1 + 2 * seg[0] + 3, "jpeg: bad scan header");
+      ScanSpec sc;
+      sc.ns = seg[0];
+      sc.progressive = progressive;
       bool named[3] = {false, false, false};
-      for (int i = 0; i < seg[0]; ++i) {
+      for (int i = 0; i < sc.ns; ++i) {
         int c = -1;
         for (int j = 0; j < out->components; ++j)
           if (cid[j] == seg[1 + 2 * i]) c = j;
         AI4E_REQUIRE(c >= 0, "jpeg: scan names an unknown component");
         AI4E_REQUIRE(!named[c], "jpeg: scan names component %d twice", c);
         named[c] = true;
+        sc.comp[i] = c;
         td[c] = seg[2 + 2 * i] >> 4;
         ta[c] = seg[2 + 2 * i] & 15;
-        AI4E_REQUIRE(td[c] < 4 && ta[c] < 4 && dc[td[c]].present && ac[ta[c]].present, "jpeg: scan uses an undefined Huffman table");
+        AI4E_REQUIRE(td[c] < 4 && ta[c] < 4, "jpeg: bad Huffman table selector");
+      }
+      sc.ss = seg[1 + 2 * sc.ns]; sc.se = seg[2 + 2 * sc.ns];
+      sc.ah = seg[3 + 2 * sc.ns] >> 4; sc.al = seg[3 + 2 * sc.ns] & 15;
+      if (progressive) {
+        AI4E_REQUIRE(sc.ss <= sc.se && sc.se <= 63 && sc.ah <= 13 && sc.al <= 13 && (sc.ss > 0 || sc.se == 0) &&
+                     (sc.ss == 0 || sc.ns == 1), "jpeg: bad progressive scan parameters (Ss %d, Se %d, Ah %d, Al %d, %d components)",
+                     sc.ss, sc.se, sc.ah, sc.al, sc.ns);
+      } else {
+        AI4E_REQUIRE(sc.ss == 0 && sc.se == 63 && sc.ah == 0 && sc.al == 0, "jpeg: sequential scan with a spectral selection");
+        AI4E_REQUIRE(sc.ns == out->components || sc.ns == 1, "jpeg: sequential scan of %d of %d components is not supported",
+                     sc.ns, out->components);
+      }
+      for (int i = 0; i < sc.ns; ++i) {  // the tables this kind of scan reads must exist
+        const int c = sc.comp[i];
+        const bool need_dc = !progressive || (sc.ss == 0 && sc.ah == 0), need_ac = !progressive || sc.ss > 0;
+        AI4E_REQUIRE((!need_dc || dc[td[c]].present) && (!need_ac || ac[ta[c]].present), "jpeg: scan uses an undefined Huffman table");
       }
       have_scan = true;
+      if (!record) break;  // headers only: the first scan header is as far as the caller needs
+      if (scans == 0) {
+        AI4E_REQUIRE(capacity >= (uint64_t)out->record_int16, "jpeg: record needs %lld int16, capacity %llu",
+                     (long long)out->record_int16, (unsigned long long)capacity);
+        memset(record, 0, (size_t)out->record_int16 * sizeof(int16_t));
+      }
+      for (int i = 0; i < sc.ns; ++i) {  // a component's quantisation table is the one in force at its first scan
+        const int c = sc.comp[i];
+        if (latched[c]) continue;
+        AI4E_REQUIRE(have_qt[tq[c]], "jpeg: component %d uses an undefined quantisation table", c);
+        for (int k = 0; k < 64; ++k) record[c * 64 + k] = (int16_t)qt[tq[c]][k];
+        latched[c] = true;
+      }
+      BitReader br;
+      br.p = data + pos;
+      br.end = data + len;
+      const int rc = decode_scan(br, *out, sc, td, ta, dc, ac, record);
+      if (rc) return rc;
+      ++scans;
+      AI4E_REQUIRE(scans <= 256, "jpeg: too many scans");
+      // the next marker: the reader stopped on it if it ran into it, otherwise it lies ahead
+      const uint8_t* q = br.p;
+      while (q + 1 < br.end && !(q[0] == 0xFF && q[1] != 0x00 && q[1] != 0xFF && !(q[1] >= 0xD0 && q[1] <= 0xD7))) ++q;
+      pos = (uint64_t)(q - data);
+      if (!progressive) {
+        bool all = true;
+        for (int i = 0; i < sc.ns; ++i) seen[sc.comp[i]] = true;
+        for (int c = 0; c < out->components; ++c) all = all && seen[c];
+        done = all;  // sequential: every component has had its scan
+      }
     }
   }
   AI4E_REQUIRE(have_frame, "jpeg: no frame header");
   if (!record) return AI4E_OK;
-  AI4E_REQUIRE(have_scan, "jpeg: no scan");
-  AI4E_REQUIRE(capacity >= (uint64_t)out->record_int16, "jpeg: record needs %lld int16, capacity %llu",
-               (long long)out->record_int16, (unsigned long long)capacity);
-  for (int c = 0; c < out->components; ++c) AI4E_REQUIRE(have_qt[tq[c]], "jpeg: component %d uses an undefined quantisation table", c);
-  memset(record, 0, (size_t)out->record_int16 * sizeof(int16_t));
-  for (int c = 0; c < 3; ++c) {
-    const int cc = c < out->components ? c : 0;
-    for (int k = 0; k < 64; ++k) record[c * 64 + k] = (int16_t)qt[tq[cc]][k];
-  }
-
-  // ---- entropy-coded segment
-  BitReader br;
-  br.p = data + pos;
-  br.end = data + len;
-  const int mcus_x = out->blocks_w[0] / out->h[0], mcus_y = out->blocks_h[0] / out->v[0];
-  const int total = mcus_x * mcus_y;
-  const int ri = out->restart_interval;
-  int pred[3] = {0, 0, 0};
-  int until_restart = ri ? ri : total;
-  for (int mcu = 0; mcu < total; ++mcu) {
-    if (until_restart == 0) {  // expect RSTn: byte-align, skip the marker, reset the predictors
-      br.fill();
-      const uint8_t* q = br.p;
-      // br.p sits on the 0xFF of the marker once the reader has hit it; otherwise search forward
-      while (q + 1 < br.end && !(q[0] == 0xFF && q[1] >= 0xD0 && q[1] <= 0xD7)) ++q;
-      AI4E_REQUIRE(q + 1 < br.end, "jpeg: restart marker missing");
-      br.p = q + 2;
-      br.reset_bits();
-      pred[0] = pred[1] = pred[2] = 0;
-      until_restart = ri;
-    }
-    --until_restart;
-    const int my = mcu / mcus_x, mx = mcu - my * mcus_x;
-    for (int c = 0; c < out->components; ++c) {
-      const HuffTable& tdc = dc[td[c]];
-      const HuffTable& tac = ac[ta[c]];
-      for (int by = 0; by < out->v[c]; ++by) {
-        for (int bx = 0; bx < out->h[c]; ++bx) {
-          int16_t* blk = record + out->coef_off[c] +
-                         ((int64_t)(my * out->v[c] + by) * out->blocks_w[c] + (mx * out->h[c] + bx)) * 64;
-          int s = decode_symbol(br, tdc);
-          AI4E_REQUIRE(s >= 0 && s <= 11, "jpeg: corrupt DC code");
-          if (s) {
-            if (br.n < s) br.fill();
-            pred[c] += extend((int)br.get(s), s);
-          }
-          blk[0] = (int16_t)pred[c];
-          for (int k = 1; k < 64;) {
-            const int rs = decode_symbol(br, tac);
-            AI4E_REQUIRE(rs >= 0, "jpeg: corrupt AC code");
-            const int r = rs >> 4;
-            s = rs & 15;
-            if (s == 0) {
-              if (r != 15) break;
-              k += 16;
-              continue;
-            }
-            k += r;
-            AI4E_REQUIRE(k < 64, "jpeg: AC coefficient index past 63");
-            if (br.n < s) br.fill();
-            blk[kZigzag[k]] = (int16_t)extend((int)br.get(s), s);
-            ++k;
-          }
-        }
-      }
-    }
-  }
+  AI4E_REQUIRE(have_scan && scans > 0, "jpeg: no scan");
+  for (int c = 0; c < out->components; ++c) AI4E_REQUIRE(latched[c], "jpeg: component %d has no scan", c);
+  if (out->components == 1)  // the record always carries three table slots
+    for (int c = 1; c < 3; ++c) memcpy(record + c * 64, record, 64 * sizeof(int16_t));
   return AI4E_OK;
 }
 

@@ -25,7 +25,7 @@ int launch_preprocess(const uint8_t* d_src, int batch, int src_h, int src_w, int
                       int out_h, int out_w, const float* mean, const float* stdv, int layout,
                       int out_channels, void* d_dst, cudaStream_t stream, const ChipGrid* chips = nullptr);
 
-// ---- K0 baseline JPEG (jpeg.cu): host headers + entropy decode, device IDCT / upsampling / colour
+// ---- K0 JPEG, baseline and progressive (jpeg.cu): host headers + entropy decode, device IDCT / upsampling / colour
 int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_t capacity_int16, ai4e_jpeg_info* out);
 int jpeg_reconstruct(const int16_t* d_records, int batch, const ai4e_jpeg_info* geometry, uint8_t* d_scratch,
                      uint8_t* d_out, cudaStream_t stream, const float* norm_mean_std = nullptr);

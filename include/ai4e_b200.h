@@ -111,14 +111,16 @@ AI4E_API int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int
                     int stride, int pad, const void* d_residual_or_null, int relu,
                     void* d_out_nhwc, int algo, void* stream);
 
-/* K0.  Baseline JPEG decode (requests carry encoded images; the reference
+/* K0.  JPEG decode, baseline and progressive (requests carry encoded images; the reference
  * gates on image MIME types at APIs/1.0/base-py/ai4e_service.py:72,127-129 and leaves decoding to
  * the callback it calls at :203 - Pillow / libjpeg-turbo in a PyTorch container, which this
  * matches bit for bit: accurate integer IDCT, fancy chroma upsampling, fixed-point YCbCr->RGB).
  * Split like a hybrid decoder: the entropy (Huffman) decode is sequential and runs on the
  * submitting thread's host core; dequantisation, IDCT, upsampling and colour conversion run on the
- * GPU.  8-bit baseline / extended sequential Huffman, 1 or 3 components, 4:4:4 / 4:2:2 / 4:2:0,
- * restart intervals; anything else -> AI4E_ERR_UNSUPPORTED.
+ * GPU.  8-bit baseline / extended sequential and progressive (SOF0, SOF1, SOF2) Huffman, 1 or 3
+ * components, 4:4:4 / 4:2:2 / 4:2:0, restart intervals; a progressive file's scans accumulate into the
+ * same record on the host.  Anything else (arithmetic coding, lossless, CMYK, 12-bit)
+ * -> AI4E_ERR_UNSUPPORTED.
  *
  * A decoded image travels as a RECORD of int16: 3 x 64 quantisation values (natural order, per
  * component), then the quantised coefficients, component after component, block rows padded to
@@ -161,7 +163,7 @@ AI4E_API int ai4e_png_decode(const uint8_t* png, uint64_t len, uint8_t* h_rgb_hw
                              int32_t* out_height, int32_t* out_width);
 
 /* Admission check for an encoded payload, host only, headers only: AI4E_OK with the format and size
- * when the engine can decode it, AI4E_ERR_UNSUPPORTED otherwise (progressive / CMYK JPEG, 16-bit or
+ * when the engine can decode it, AI4E_ERR_UNSUPPORTED otherwise (arithmetic-coded / CMYK JPEG, 16-bit or
  * interlaced PNG, any other format).  A request_processing_function calls it while the request is
  * still open and answers 415 instead of accepting a task that could only fail - the content gate
  * of APIs/1.0/base-py/ai4e_service.py:127-129 only looks at the MIME type. */
@@ -329,10 +331,10 @@ AI4E_API int ai4e_engine_poll(ai4e_engine* e, int capacity, int64_t timeout_us, 
  * has been waited for; pageable memory is copied to the staging slot before returning. */
 AI4E_API int ai4e_engine_submit_batch(ai4e_engine* e, const uint8_t* h_images, int count, int h, int w,
                                       int c, uint64_t* out_first_ticket);
-/* Same for one baseline JPEG (K0): headers and the entropy decode run on the calling thread,
+/* Same for one JPEG, baseline or progressive (K0): headers and the entropy decode run on the calling thread,
  * the record joins the open micro-batch (a batch holds images of one size and sampling) and the
  * GPU reconstructs the pixels in front of the preprocessing kernel.  The engine's model must
- * take 3 channels; unsupported streams (progressive, CMYK, ...) -> AI4E_ERR_UNSUPPORTED and
+ * take 3 channels; unsupported streams (arithmetic coding, CMYK, ...) -> AI4E_ERR_UNSUPPORTED and
  * nothing is queued.  This is `Image.open(BytesIO(request.data)).convert("RGB")` + the rest of
  * the callback at APIs/1.0/base-py/ai4e_service.py:203. */
 AI4E_API int ai4e_engine_submit_jpeg(ai4e_engine* e, const uint8_t* jpeg, uint64_t len, uint64_t tag,

@@ -12,8 +12,9 @@ can be checked, not only the final pixels.
 
 Pinned: tests/test_jpeg.py compares `decode()` bit for bit with Pillow 12.2 / libjpeg-turbo on
 the committed fixtures in tests/golden/jpeg/ (made by tests/golden/make_jpeg_goldens.py).
-Supported: 8-bit baseline / extended sequential Huffman (SOF0, SOF1), 1 or 3 components, chroma
-subsampling 4:4:4, 4:2:2 (h2v1), 4:2:0 (h2v2), restart intervals.  Progressive, arithmetic coding,
+Supported: 8-bit baseline / extended sequential (SOF0, SOF1) and progressive (SOF2) Huffman JPEG, single- or
+multi-scan, 1 or 3 components, chroma subsampling 4:4:4, 4:2:2 (h2v1), 4:2:0 (h2v2), restart intervals.
+Progressive scans follow jdphuff.c (DC / AC, first pass / refinement, end-of-band runs).  Arithmetic coding,
 CMYK and 12-bit are rejected (ValueError) - as the CUDA path rejects them.
 """
 from __future__ import annotations
@@ -55,6 +56,8 @@ class Frame:
     vmax: int
     mcus_x: int
     mcus_y: int
+    progressive: bool = False
+    scans: int = 0
 
 
 class _Huff:
@@ -156,7 +159,7 @@ def parse(data: bytes) -> Frame:
                 n = sum(counts)
                 huff[(tc, th)] = _Huff(counts, seg[i + 17:i + 17 + n])
                 i += 17 + n
-        elif m in (0xC0, 0xC1):
+        elif m in (0xC0, 0xC1, 0xC2):
             if seg[0] != 8:
                 raise ValueError("only 8-bit samples are supported")
             h, w, nf = (seg[1] << 8) | seg[2], (seg[3] << 8) | seg[4], seg[5]
@@ -171,29 +174,35 @@ def parse(data: bytes) -> Frame:
                 c.blocks_w, c.blocks_h = mcus_x * c.h, mcus_y * c.v
                 c.width, c.height = -(-w * c.h // hmax), -(-h * c.v // vmax)
                 c.coefs = np.zeros((c.blocks_h, c.blocks_w, 64), np.int16)
-            frame = Frame(w, h, comps, qt, 0, hmax, vmax, mcus_x, mcus_y)
-        elif 0xC2 <= m <= 0xCF and m not in (0xC4, 0xC8, 0xCC):
-            raise ValueError("only baseline / extended sequential Huffman JPEG is supported (SOF0, SOF1)")
+            frame = Frame(w, h, comps, qt, 0, hmax, vmax, mcus_x, mcus_y, progressive=(m == 0xC2))
+        elif 0xC3 <= m <= 0xCF and m not in (0xC4, 0xC8, 0xCC):
+            raise ValueError("only Huffman-coded sequential or progressive JPEG is supported (SOF0, SOF1, SOF2)")
         elif m == 0xDD:
             ri = (seg[0] << 8) | seg[1]
         elif m == 0xDA:
             if frame is None:
                 raise ValueError("SOS before SOF")
             ns = seg[0]
-            if ns != len(frame.comps):
-                raise ValueError("multi-scan files are not supported")
+            scan_comps = []
             for i in range(ns):
                 c = next(c for c in frame.comps if c.cid == seg[1 + 2 * i])
                 c.td, c.ta = seg[2 + 2 * i] >> 4, seg[2 + 2 * i] & 15
+                scan_comps.append(c)
+            ss, se, ah, al = seg[1 + 2 * ns], seg[2 + 2 * ns], seg[3 + 2 * ns] >> 4, seg[3 + 2 * ns] & 15
+            if not frame.progressive and (ss, se, ah, al) != (0, 63, 0, 0):
+                raise ValueError("sequential scan with a spectral selection")
             frame.restart_interval = ri
-            frame.qt = qt
-            pos = _decode_scan(data, pos, frame, huff)
+            frame.qt = dict(qt)
+            frame.scans += 1
+            pos = _decode_scan(data, pos, frame, huff, scan_comps, ss, se, ah, al)
     if frame is None:
         raise ValueError("no frame header")
     return frame
 
 
-def _decode_scan(data: bytes, pos: int, f: Frame, huff) -> int:
+def _decode_scan(data: bytes, pos: int, f: Frame, huff, comps, ss: int, se: int, ah: int, al: int) -> int:
+    """one scan (sequential: all 64 coefficients of the listed components; progressive: one of the four
+    kinds of jdphuff.c) into the components' coefficient arrays; returns the position of the next marker."""
     # split the entropy-coded data at restart markers, removing the stuffed zero bytes
     segs, cur = [], bytearray()
     while pos < len(data):
@@ -213,39 +222,116 @@ def _decode_scan(data: bytes, pos: int, f: Frame, huff) -> int:
         elif nb == 0xFF:
             pos += 1
         else:
-            break  # a real marker (EOI): the scan ends, `pos` stays on it
+            break  # a real marker (EOI, DHT, SOS ...): the scan ends, `pos` stays on it
     segs.append(bytes(cur))
-    total = f.mcus_x * f.mcus_y
+    if len(comps) > 1:  # interleaved: MCUs of the frame
+        total = f.mcus_x * f.mcus_y
+
+        def blocks(mcu):
+            my, mx = divmod(mcu, f.mcus_x)
+            for c in comps:
+                for by in range(c.v):
+                    for bx in range(c.h):
+                        yield c, my * c.v + by, mx * c.h + bx
+    else:  # one component: its own blocks in raster order, without the padding to whole MCUs
+        c0 = comps[0]
+        bw, bh = -(-c0.width // 8), -(-c0.height // 8)
+        total = bw * bh
+
+        def blocks(mcu):
+            yield (c0, *divmod(mcu, bw))
+    if f.progressive and ss > 0 and len(comps) != 1:
+        raise ValueError("progressive AC scans carry one component")
     per_seg = f.restart_interval or total
+    p1, m1 = 1 << al, -(1 << al)
     mcu = 0
     for seg in segs:
         br = _Bits(seg)
-        pred = {c.cid: 0 for c in f.comps}
+        pred = {c.cid: 0 for c in comps}
+        eobrun = 0
         for _ in range(min(per_seg, total - mcu)):
-            my, mx = divmod(mcu, f.mcus_x)
-            for c in f.comps:
-                dc, ac = huff[(0, c.td)], huff[(1, c.ta)]
-                for by in range(c.v):
-                    for bx in range(c.h):
-                        blk = c.coefs[my * c.v + by, mx * c.h + bx]
-                        s = _decode_symbol(br, dc)
-                        diff = _extend(br.bits(s), s) if s else 0
-                        pred[c.cid] += diff
-                        blk[0] = pred[c.cid]
-                        k = 1
-                        while k < 64:
-                            rs = _decode_symbol(br, ac)
-                            r, s = rs >> 4, rs & 15
-                            if s == 0:
-                                if r != 15:
-                                    break
-                                k += 16
-                                continue
+            for c, by, bx in blocks(mcu):
+                blk = c.coefs[by, bx]
+                if not f.progressive:
+                    dc, ac = huff[(0, c.td)], huff[(1, c.ta)]
+                    s = _decode_symbol(br, dc)
+                    pred[c.cid] += _extend(br.bits(s), s) if s else 0
+                    blk[0] = pred[c.cid]
+                    k = 1
+                    while k < 64:
+                        rs = _decode_symbol(br, ac)
+                        r, s = rs >> 4, rs & 15
+                        if s == 0:
+                            if r != 15:
+                                break
+                            k += 16
+                            continue
+                        k += r
+                        if k > 63:
+                            raise ValueError("AC coefficient index past 63")
+                        blk[ZIGZAG[k]] = _extend(br.bits(s), s)
+                        k += 1
+                elif ss == 0:
+                    if ah == 0:  # DC, first pass (decode_mcu_DC_first)
+                        s = _decode_symbol(br, huff[(0, c.td)])
+                        pred[c.cid] += _extend(br.bits(s), s) if s else 0
+                        blk[0] = pred[c.cid] * p1
+                    elif br.bit():  # DC refinement: one more bit
+                        blk[0] |= p1
+                elif ah == 0:  # AC, first pass (decode_mcu_AC_first)
+                    if eobrun > 0:
+                        eobrun -= 1
+                        continue
+                    ac = huff[(1, c.ta)]
+                    k = ss
+                    while k <= se:
+                        rs = _decode_symbol(br, ac)
+                        r, s = rs >> 4, rs & 15
+                        if s:
                             k += r
                             if k > 63:
                                 raise ValueError("AC coefficient index past 63")
-                            blk[ZIGZAG[k]] = _extend(br.bits(s), s)
+                            blk[ZIGZAG[k]] = _extend(br.bits(s), s) * p1
+                        elif r == 15:
+                            k += 15
+                        else:
+                            eobrun = (1 << r) + (br.bits(r) if r else 0) - 1
+                            break
+                        k += 1
+                else:  # AC refinement (decode_mcu_AC_refine)
+                    ac = huff[(1, c.ta)]
+                    k = ss
+                    if eobrun == 0:
+                        while k <= se:
+                            rs = _decode_symbol(br, ac)
+                            r, s = rs >> 4, rs & 15
+                            if s:
+                                s = p1 if br.bit() else m1
+                            elif r != 15:
+                                eobrun = (1 << r) + (br.bits(r) if r else 0)
+                                break
+                            while k <= se:  # over nonzero coefficients (one correction bit each) and r zero ones
+                                z = ZIGZAG[k]
+                                if blk[z] != 0:
+                                    if br.bit() and (int(blk[z]) & p1) == 0:
+                                        blk[z] += p1 if blk[z] >= 0 else m1
+                                else:
+                                    r -= 1
+                                    if r < 0:
+                                        break
+                                k += 1
+                            if s:
+                                if k > 63:
+                                    raise ValueError("AC coefficient index past 63")
+                                blk[ZIGZAG[k]] = s
                             k += 1
+                    if eobrun > 0:  # the rest of the band: correction bits only
+                        while k <= se:
+                            z = ZIGZAG[k]
+                            if blk[z] != 0 and br.bit() and (int(blk[z]) & p1) == 0:
+                                blk[z] += p1 if blk[z] >= 0 else m1
+                            k += 1
+                        eobrun -= 1
             mcu += 1
         if mcu >= total:
             break

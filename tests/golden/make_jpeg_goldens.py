@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Mint the JPEG fixtures of tests/golden/jpeg/ with Pillow (libjpeg-turbo), the decoder a PyTorch
 API container uses: small synthetic images saved with different chroma subsampling, quality,
-restart intervals and (optimised) Huffman tables, plus Pillow's decode of each as .npy.
+restart intervals, (optimised) Huffman tables and progressive scan scripts, plus Pillow's decode of each as .npy.
     python tests/golden/make_jpeg_goldens.py
 """
 import io
@@ -26,6 +26,13 @@ CASES = [  # name, (h, w), save kwargs
     ("q30_420_40x40", (40, 40), dict(quality=30, subsampling=2)),
     ("q92_gray_45x37", (45, 37), dict(quality=92)),
     ("q90_420_224x224", (224, 224), dict(quality=90, subsampling=2)),
+    # progressive (SOF2): spectral selection + successive approximation as libjpeg's default script writes them
+    ("prog_q85_420_ragged_61x83", (61, 83), dict(quality=85, subsampling=2, progressive=True)),
+    ("prog_q75_422_50x70", (50, 70), dict(quality=75, subsampling=1, progressive=True)),
+    ("prog_q95_444_33x47", (33, 47), dict(quality=95, subsampling=0, progressive=True)),
+    ("prog_q60_420_rst2_72x104", (72, 104), dict(quality=60, subsampling=2, progressive=True, restart_marker_blocks=2)),
+    ("prog_q92_gray_45x37", (45, 37), dict(quality=92, progressive=True)),
+    ("prog_q90_420_224x224", (224, 224), dict(quality=90, subsampling=2, progressive=True)),
 ]
 
 

@@ -1,4 +1,4 @@
-"""K0: baseline JPEG decode.  CPU part: the numpy oracle is pinned, bit for
+"""K0: baseline and progressive JPEG decode.  CPU part: the numpy oracle is pinned, bit for
 bit, to Pillow / libjpeg-turbo's output on the committed fixtures (and to Pillow itself when it is
 importable), and the library's host-side entropy decoder must produce the oracle's coefficients."""
 import glob
@@ -12,6 +12,7 @@ from oracle import jpeg_oracle as jo
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 FIXTURES = sorted(glob.glob(os.path.join(HERE, "golden", "jpeg", "*.jpg")))
+BASELINE0 = os.path.join(HERE, "golden", "jpeg", "q90_420_64x64.jpg")
 
 
 def _name(p):
@@ -32,6 +33,9 @@ def test_fixtures_cover_the_supported_formats():
         f = jo.parse(open(p, "rb").read())
         kinds.add((len(f.comps), f.hmax, f.vmax, f.restart_interval > 0))
     assert {(3, 2, 2, False), (3, 2, 2, True), (3, 2, 1, False), (3, 1, 1, False), (1, 1, 1, False)} <= kinds
+    prog = {(len(f.comps), f.hmax, f.vmax, f.restart_interval > 0)
+            for f in (jo.parse(open(p, "rb").read()) for p in FIXTURES) if f.progressive}
+    assert {(3, 2, 2, False), (3, 2, 2, True), (3, 2, 1, False), (3, 1, 1, False), (1, 1, 1, False)} <= prog
 
 
 def test_oracle_matches_live_pillow_when_available():
@@ -47,12 +51,45 @@ def test_oracle_matches_live_pillow_when_available():
         assert np.array_equal(jo.decode(buf.getvalue()), want), (h, w, kw)
 
 
-def test_oracle_rejects_progressive():
+def test_oracle_matches_live_pillow_progressive():
+    """SOF2: every scan kind of T.81 annex G as libjpeg's default script writes them (DC first + refinement,
+    AC first with end-of-band runs, AC refinement), with and without restart markers / optimised tables."""
+    PIL = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(6)
+    for (h, w), kw in (((37, 53), dict(quality=70, subsampling=2)), ((16, 24), dict(quality=99, subsampling=1)),
+                       ((9, 9), dict(quality=50, subsampling=0)), ((24, 130), dict(quality=88, subsampling=2, restart_marker_blocks=1)),
+                       ((40, 40), dict(quality=20, subsampling=2, optimize=True)), ((31, 17), dict(quality=90))):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        img = (img // 4 + np.linspace(0, 190, w, dtype=np.int32)[None, :, None]).astype(np.uint8)
+        pil = PIL.fromarray(img)
+        if "subsampling" not in kw:
+            pil = pil.convert("L")
+        buf = io.BytesIO()
+        pil.save(buf, format="JPEG", progressive=True, **kw)
+        f = jo.parse(buf.getvalue())
+        assert f.progressive and f.scans > 1
+        want = np.asarray(PIL.open(io.BytesIO(buf.getvalue())).convert("RGB"))
+        assert np.array_equal(jo.decode(buf.getvalue()), want), (h, w, kw)
+
+
+def _cmyk_jpeg():
     PIL = pytest.importorskip("PIL.Image")
     buf = io.BytesIO()
-    PIL.fromarray(np.zeros((16, 16, 3), np.uint8)).save(buf, format="JPEG", progressive=True)
+    PIL.fromarray(np.zeros((16, 16, 4), np.uint8), mode="CMYK").save(buf, format="JPEG")
+    return buf.getvalue()
+
+
+def _as_arithmetic(data):
+    """the same headers with the frame marker rewritten to SOF9 (arithmetic coding, sequential)"""
+    i = data.index(b"\xff\xc0")
+    return data[:i] + b"\xff\xc9" + data[i + 2:]
+
+
+def test_oracle_rejects_what_it_does_not_support():
     with pytest.raises(ValueError):
-        jo.decode(buf.getvalue())
+        jo.decode(_cmyk_jpeg())
+    with pytest.raises(ValueError):
+        jo.decode(_as_arithmetic(open(BASELINE0, "rb").read()))
 
 
 # ------------------------------------------------------------------ library, host side (no GPU needed)
@@ -78,16 +115,54 @@ def test_host_entropy_decoder_matches_oracle_coefficients(path):
 
 def test_host_decoder_rejects_what_it_does_not_support():
     from ai4e_b200 import ops, Ai4eError
-    PIL = pytest.importorskip("PIL.Image")
-    buf = io.BytesIO()
-    PIL.fromarray(np.zeros((16, 16, 3), np.uint8)).save(buf, format="JPEG", progressive=True)
-    with pytest.raises(Ai4eError, match="progressive"):
-        ops.jpeg_entropy_decode(buf.getvalue())
+    with pytest.raises(Ai4eError, match="4 components"):
+        ops.jpeg_entropy_decode(_cmyk_jpeg())
+    with pytest.raises(Ai4eError, match="arithmetic"):
+        ops.jpeg_entropy_decode(_as_arithmetic(open(BASELINE0, "rb").read()))
     with pytest.raises(Ai4eError, match="SOI"):
         ops.jpeg_entropy_decode(b"\x89PNG\r\n\x1a\n" + b"\0" * 32)
-    good = open(FIXTURES[0], "rb").read()
+    good = open(BASELINE0, "rb").read()
     with pytest.raises(Ai4eError):
         ops.jpeg_entropy_decode(good[:200])  # truncated inside the tables / scan
+
+
+def test_host_decoder_survives_mutated_streams():
+    """Random byte edits, bit flips, cuts and deletions over every fixture (baseline and progressive): each
+    stream is either decoded or refused with an error - never a crash, never a write outside the record
+    (the record is allocated exactly and followed by a canary)."""
+    import ctypes as C
+    from ai4e_b200 import _lib as L
+    lib = L.load()
+    rng = np.random.default_rng(77)
+    small = [open(p, "rb").read() for p in FIXTURES if os.path.getsize(p) < 4000]
+    decoded = refused = 0
+    for it in range(3000):
+        d = bytearray(small[it % len(small)])
+        kind = it % 4
+        if kind == 0:
+            for _ in range(int(rng.integers(1, 6))):
+                d[int(rng.integers(2, len(d)))] = int(rng.integers(256))
+        elif kind == 1:
+            d = d[:int(rng.integers(2, len(d)))]
+        elif kind == 2:
+            d[int(rng.integers(2, len(d)))] ^= 1 << int(rng.integers(8))
+        else:
+            i = int(rng.integers(2, len(d)))
+            del d[i:i + int(rng.integers(1, 40))]
+        buf = (C.c_uint8 * len(d)).from_buffer_copy(bytes(d))
+        info = L.JpegInfo()
+        if lib.ai4e_jpeg_entropy_decode(buf, len(d), None, 0, C.byref(info)) != 0:
+            refused += 1
+            continue
+        n = int(info.record_int16)
+        if n > (1 << 24):       # a mutated frame header can ask for a huge record: not this test's business
+            continue
+        rec = np.full(n + 64, 0x5A5A, np.int16)
+        rc = lib.ai4e_jpeg_entropy_decode(buf, len(d), rec.ctypes.data_as(C.c_void_p), n, C.byref(info))
+        assert np.all(rec[n:] == 0x5A5A)
+        decoded += rc == 0
+        refused += rc != 0
+    assert decoded > 300 and refused > 300
 
 
 def _dht_stream(counts, nsyms=None, tc_th=0x00):
@@ -121,7 +196,7 @@ def test_host_decoder_survives_malformed_segments():
         ops.jpeg_entropy_decode(_dht_stream([0, 0, 0, 0, 0, 0, 0, 255, 1], nsyms=10))
     with pytest.raises(Ai4eError):                       # a full, valid 256-symbol table alone: no frame header
         ops.jpeg_entropy_decode(_dht_stream([0, 0, 0, 0, 0, 0, 0, 255, 2][:9]))
-    good = open(FIXTURES[0], "rb").read()
+    good = open(BASELINE0, "rb").read()
     sos = good.index(b"\xff\xda")
     with pytest.raises(Ai4eError):                       # SOS as the last four bytes: header length 2, no payload
         ops.jpeg_entropy_decode(good[:sos] + b"\xff\xda\x00\x02")
@@ -193,6 +268,10 @@ def test_engine_submit_jpeg_equals_submit_of_decoded_pixels():
         buf = io.BytesIO()
         PIL.fromarray(imgs[i]).resize((hw[1], hw[0])).save(buf, format="JPEG", quality=88, subsampling=sub)
         cases.append(buf.getvalue())
+    for i, (hw, sub) in enumerate((((224, 224), 2), ((224, 224), 2), ((180, 240), 1))):  # progressive files among the baseline ones
+        buf = io.BytesIO()
+        PIL.fromarray(imgs[6 + i]).resize((hw[1], hw[0])).save(buf, format="JPEG", quality=85, subsampling=sub, progressive=True)
+        cases.append(buf.getvalue())
     decoded = [np.asarray(PIL.open(io.BytesIO(d)).convert("RGB")) for d in cases]
     with Engine(util.program_for("resnet50", 3, 224, False), device=0, max_batch=8, max_wait_us=3000) as e:
         want = [e.classify(d, want_logits=True) for d in decoded]
@@ -210,10 +289,8 @@ def test_engine_submit_jpeg_equals_submit_of_decoded_pixels():
             assert np.array_equal(gi, wi), k
             assert np.array_equal(gl, wl), (k, np.abs(gl - wl).max())  # same pixels -> same bits
         before = e.stats()["images"]
-        buf = io.BytesIO()
-        PIL.fromarray(imgs[0]).save(buf, format="JPEG", progressive=True)
-        with pytest.raises(Ai4eError, match="progressive"):
-            e.submit_jpeg(buf.getvalue())
+        with pytest.raises(Ai4eError, match="4 components"):
+            e.submit_jpeg(_cmyk_jpeg())
         e.flush()
         assert e.stats()["images"] == before and e.stats()["healthy"]
 

@@ -55,6 +55,8 @@ def test_probe_and_refusals():
     jpg = open(os.path.join(util.GOLDEN, "jpeg", "q90_420_64x64.jpg"), "rb").read()
     assert ops.image_probe(jpg) == ("jpeg", 64, 64)
     assert require_decodable(jpg) == ("jpeg", 64, 64)
+    prog = open(os.path.join(util.GOLDEN, "jpeg", "prog_q75_422_50x70.jpg"), "rb").read()
+    assert ops.image_probe(prog) == ("jpeg", 50, 70)    # progressive files are admitted (and decoded: test_jpeg.py)
     bad16 = open(os.path.join(PNG_DIR, "unsupported_gray16_8x8.png"), "rb").read()
     for payload in (bad16, b"GIF89a" + b"\0" * 64, b""):
         with pytest.raises(Ai4eError) as ei:
