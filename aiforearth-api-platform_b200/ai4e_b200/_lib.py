@@ -103,6 +103,9 @@ SIGNATURES = {
     "ai4e_pool_submit": (_i, [_vp, _vp, _i, _i, _i, _i, _u64, _u64p]),
     "ai4e_pool_submit_jpeg": (_i, [_vp, _vp, _u64, _u64, _u64p]),
     "ai4e_engine_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
+    "ai4e_engine_submit_tile_summary": (_i, [_vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_int32)]),
+    "ai4e_engine_wait_tile_summary": (_i, [_vp, C.c_uint64, _vp, _vp, _i, _vp, _vp, C.POINTER(C.c_int32)]),
+    "ai4e_tile_summary": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
     "ai4e_engine_wait_many": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ai4e_pool_wait": (_i, [_vp, _u64, _vp, _vp, _vp]),
     "ai4e_engine_submit_many": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
@@ -112,6 +115,8 @@ SIGNATURES = {
     "ai4e_pool_submit_many": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "ai4e_pool_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
     "ai4e_pool_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
+    "ai4e_pool_submit_tile_summary": (_i, [_vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_int32)]),
+    "ai4e_pool_wait_tile_summary": (_i, [_vp, C.c_uint64, _vp, _vp, _i, _vp, _vp, C.POINTER(C.c_int32)]),
     "ai4e_pool_wait_many": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ai4e_pool_poll": (_i, [_vp, _i, _i64, _vp, _vp, _vp, _vp, _vp, C.POINTER(C.c_int)]),
     "ai4e_pool_wait_for": (_i, [_vp, _u64, _i64, _vp, _vp, _vp]),

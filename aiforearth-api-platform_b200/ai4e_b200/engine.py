@@ -358,6 +358,35 @@ class _Base:
                                         _vp(tickets), tickets.size, C.byref(n)))
         return tickets[:n.value]
 
+    def submit_tile_summary(self, tile_u8_hwc: np.ndarray, chip: int = 256):
+        """tile -> chips -> classify -> aggregate with no host hop between the stages: like `submit_tile`, but
+        the chips' results are folded into one summary ON THE GPU and one ticket stands for the whole tile.
+        -> (tile_ticket, (gh, gw)); results with `wait_tile_summary`."""
+        a = np.asarray(tile_u8_hwc)
+        if a.dtype != np.uint8 or a.ndim != 3 or a.strides[2] != 1 or a.strides[1] != a.shape[2] or a.strides[0] < a.shape[1] * a.shape[2]:
+            raise ValueError("expected a uint8 [H, W, C] tile with dense pixels and forward rows")
+        t, n = C.c_uint64(), C.c_int32()
+        L.check(self._fn("submit_tile_summary")(self._h, _vp(a), a.shape[0], a.shape[1], a.shape[2], a.strides[0], chip,
+                                                C.byref(t), C.byref(n)))
+        gh, gw = a.shape[0] // chip, a.shape[1] // chip
+        assert n.value == gh * gw
+        return t.value, (gh, gw)
+
+    def wait_tile_summary(self, tile_ticket: int, grid: tuple[int, int]) -> dict:
+        """-> {"labels": int32 [gh, gw] top-1 class per chip, "label_prob": float32 [gh, gw], "hist": uint32
+        [classes] chips per top-1 class, "mass_q32": uint64 [classes] top-5 probability mass per class in 32.32
+        fixed point (exact integer sums), "mass": the same as float64}."""
+        gh, gw = grid
+        n = gh * gw
+        labels, prob = np.empty(n, np.int32), np.empty(n, np.float32)
+        hist, mass = np.empty(self.num_classes, np.uint32), np.empty(self.num_classes, np.uint64)
+        got = C.c_int32()
+        L.check(self._fn("wait_tile_summary")(self._h, C.c_uint64(int(tile_ticket)), _vp(labels), _vp(prob), n, _vp(hist),
+                                              _vp(mass), C.byref(got)))
+        assert got.value == n
+        return {"labels": labels.reshape(gh, gw), "label_prob": prob.reshape(gh, gw), "hist": hist, "mass_q32": mass,
+                "mass": mass.astype(np.float64) / 4294967296.0}
+
     def submit_batch(self, images_u8: np.ndarray):
         """dense [B,H,W,C] uint8 host array -> tickets (consecutive; a range for an Engine, an array
         for a Pool).  Page-locked arrays are read in place by the H2D copy: keep them unchanged until

@@ -37,3 +37,13 @@ def classify_tile(engine, tile_u8_hwc: np.ndarray, chip: int = 256):
     for (r, c), t in tickets:
         idx[r, c], prob[r, c] = engine.wait(t)
     return idx[:, :, 0].copy(), idx, prob
+
+
+def summarize_tile(engine, tile_u8_hwc: np.ndarray, chip: int = 256) -> dict:
+    """tile -> chips -> classify -> aggregate in one submission, the aggregate computed on the GPU(s) that
+    classified the chips (K7): the tile's label map, its class histogram and the per-class probability mass.
+    The reference would chain the aggregation as one more task (`AddPipelineTask`,
+    Common/task_management/distributed_api_task.py:67-100): one HTTP hop and one task-store write per stage.
+    Keys: labels [gh, gw], label_prob [gh, gw], hist [classes], mass_q32 / mass [classes]."""
+    ticket, grid = engine.submit_tile_summary(np.asarray(tile_u8_hwc), chip)
+    return engine.wait_tile_summary(ticket, grid)

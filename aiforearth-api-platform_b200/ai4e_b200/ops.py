@@ -239,3 +239,22 @@ def head_noalloc(x_nhwc: torch.Tensor, fc_w: torch.Tensor, fc_b: torch.Tensor, t
     L.check(lib.ai4e_head_noalloc(_ptr(x_nhwc), b, h * w, c, _ptr(fc_w), _ptr(fc_b), classes, _ptr(logits),
                                   _ptr(idx), _ptr(prob), topk, _stream_ptr(stream)))
     return logits, idx[:, :topk], prob[:, :topk]
+
+
+def tile_summary(top_idx5: torch.Tensor, top_prob5: torch.Tensor, num_classes: int, first: int = 0, out=None, stream=None):
+    """K7 stand-alone: folds the top-5 of `count` chips into (labels int32 [n], label_prob float32 [n], hist
+    int32-as-uint32 [classes], mass_q32 int64-as-uint64 [classes]) on the GPU.  `out` = a previous result to add
+    to (chips [first, first + count) of a larger summary); otherwise fresh zeroed tensors sized first + count."""
+    lib = L.load()
+    assert top_idx5.is_cuda and top_idx5.dtype == torch.int32 and top_idx5.is_contiguous() and top_idx5.shape[1] == L.TOPK
+    assert top_prob5.is_cuda and top_prob5.dtype == torch.float32 and top_prob5.is_contiguous() and top_prob5.shape == top_idx5.shape
+    count = top_idx5.shape[0]
+    if out is None:
+        dev = top_idx5.device
+        out = (torch.zeros(first + count, dtype=torch.int32, device=dev), torch.zeros(first + count, dtype=torch.float32, device=dev),
+               torch.zeros(num_classes, dtype=torch.int32, device=dev), torch.zeros(num_classes, dtype=torch.int64, device=dev))
+    labels, lprob, hist, mass = out
+    assert labels.numel() >= first + count and hist.numel() == num_classes and mass.numel() == num_classes
+    L.check(lib.ai4e_tile_summary(_ptr(top_idx5), _ptr(top_prob5), count, first, num_classes, _ptr(labels), _ptr(lprob),
+                                  _ptr(hist), _ptr(mass), _stream_ptr(stream)))
+    return out

@@ -63,6 +63,33 @@ struct TileBuf {
   cudaEvent_t ev_ready = nullptr;  // the H2D copy of the band has finished
   int users = 0;                   // batches that still read it (guarded by ai4e_engine::mu)
   bool busy = false;               // being filled by a submitter
+  // K7, summary submits only: the tile's aggregate is accumulated in d_sum by one small launch behind every batch's
+  // head and read back once, by the completer, when the tile's last batch has finished.
+  // Layout of d_sum / h_sum: labels int32[n] | label_prob float[n] | hist uint32[K] | (8-byte aligned) mass u64[K]
+  uint8_t* d_sum = nullptr;
+  uint8_t* h_sum = nullptr;        // page-locked
+  size_t sum_cap = 0;
+  bool summary = false;
+  int sum_chips = 0, sum_left = 0, sum_rc = 0;  // chips of the summary, batches not yet completed, first error
+  uint64_t sum_ticket = 0;
+};
+
+struct SumLayout {
+  size_t labels, prob, hist, mass, bytes;
+  SumLayout(int n, int K) {
+    labels = 0; prob = (size_t)n * 4; hist = prob + (size_t)n * 4;
+    mass = (hist + (size_t)K * 4 + 7) & ~(size_t)7;
+    bytes = mass + (size_t)K * 8;
+  }
+};
+
+// A finished (or pending) tile summary, kept until kSumRing newer ones have been submitted.
+constexpr int kSumRing = 64;
+struct TileSumRec {
+  uint64_t id = ~0ull;
+  int status = 1;  // 1 = pending, AI4E_OK, or the error that failed one of its batches
+  int n = 0;
+  std::vector<uint8_t> data;  // SumLayout(n, num_classes)
 };
 
 // One finished ticket that asked to be announced (submit_many with notify): what ai4e_*_poll returns.
@@ -101,6 +128,7 @@ struct BatchCtx {
   TileBuf* tile = nullptr;
   int tile_first = 0, tile_grid_w = 0, tile_chip = 0;
   long long tile_row_bytes = 0;
+  int sum_first = 0;                 // summary submits: where this batch's chips sit in the summary
 };
 
 }  // namespace
@@ -159,6 +187,9 @@ struct ai4e_engine {
   // device-resident tiles (K6)
   TileBuf tiles[kNumTileBufs];
   cudaStream_t copy_stream = nullptr;
+  cudaStream_t sum_stream = nullptr;          // the completer's read-back of a finished tile summary
+  TileSumRec sums[kSumRing];
+  uint64_t next_sum_ticket = 0;
 
   // announced completions (ai4e_engine_poll); a pool points all its replicas at one shared queue
   CompletionQueue own_cq;
@@ -365,6 +396,13 @@ int launch_batch(ai4e_engine* e, BatchCtx& c, bool want_logits) {
     rc = lane_done(ln, c.stream);
     if (rc) return rc;
   }
+  if (c.kind == kKindTile && c.tile->summary) {  // K7: this batch's chips into the tile's aggregate, still on the device
+    const SumLayout sl(c.tile->sum_chips, K);
+    uint8_t* d = c.tile->d_sum;
+    const int rc = tile_summary_launch(c.d_idx, c.d_prob, c.count, c.sum_first, K, (int32_t*)(d + sl.labels), (float*)(d + sl.prob),
+                                       (uint32_t*)(d + sl.hist), (unsigned long long*)(d + sl.mass), c.stream);
+    if (rc) return rc;
+  }
   AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_idx, c.d_idx, (size_t)c.count * AI4E_TOPK * sizeof(int32_t),
                                 cudaMemcpyDeviceToHost, c.stream));
   AI4E_CUDA_TRY(cudaMemcpyAsync(c.h_prob, c.d_prob, (size_t)c.count * AI4E_TOPK * sizeof(float),
@@ -475,6 +513,27 @@ void completer_main(ai4e_engine* e) {
     // a CUDA fault is sticky (the context is gone): the replica stops taking work.  Anything else
     // (bad geometry, a copy that never landed, no memory) fails this batch's tickets only.
     if (rc == AI4E_ERR_CUDA) e->healthy.store(0);
+    // K7: the last batch of a summarised tile brings the aggregate back (every earlier batch of the tile has been
+    // synchronised by this thread already; sum_left was set before the first of them was queued)
+    TileBuf* const stb = (c->tile && c->tile->summary) ? c->tile : nullptr;
+    bool sum_final = false;
+    if (stb) {
+      {
+        std::lock_guard<std::mutex> g(e->mu);  // a submitter that gave up half-way adjusts these under the lock
+        if (rc && !stb->sum_rc) stb->sum_rc = rc;
+        sum_final = stb->sum_left == 1;
+      }
+      if (sum_final && !stb->sum_rc) {
+        const SumLayout sl(stb->sum_chips, e->desc.num_classes);
+        cudaError_t ce = cudaMemcpyAsync(stb->h_sum, stb->d_sum, sl.bytes, cudaMemcpyDeviceToHost, e->sum_stream);
+        if (ce == cudaSuccess) ce = cudaStreamSynchronize(e->sum_stream);
+        if (ce != cudaSuccess) {
+          set_last_error("tile summary read-back failed on device %d: %s", e->device, cudaGetErrorString(ce));
+          stb->sum_rc = AI4E_ERR_CUDA;
+          e->healthy.store(0);
+        }
+      }
+    }
     const auto now = Clock::now();
     std::vector<DoneRec> announce;
     lk.lock();
@@ -504,6 +563,17 @@ void completer_main(ai4e_engine* e) {
     if (rc == AI4E_OK) account_batch(e, *c);
     e->done_upto = c->first_ticket + c->count;
     e->n_completed.fetch_add((uint64_t)c->count);
+    if (stb) {
+      stb->sum_left -= 1;
+      if (sum_final) {
+        TileSumRec& sr = e->sums[stb->sum_ticket % kSumRing];
+        if (sr.id == stb->sum_ticket) {
+          if (!stb->sum_rc) sr.data.assign(stb->h_sum, stb->h_sum + SumLayout(stb->sum_chips, K).bytes);
+          sr.status = stb->sum_rc;
+        }
+        stb->summary = false;
+      }
+    }
     if (c->tile) { c->tile->users -= 1; c->tile = nullptr; }
     c->count = 0;
     c->kind = 0;
@@ -854,6 +924,7 @@ int engine_create(int device, const ai4e_model_desc* desc, const void* blob, uin
   e->lat_ms.assign(kLatRing, 0.f);
   if (const char* v = getenv("AI4E_B200_WAIT_TIMEOUT_MS")) e->wait_timeout_ms = std::max(1, atoi(v));
   TRY_OR_FAIL(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+  TRY_OR_FAIL(cudaStreamCreateWithFlags(&e->sum_stream, cudaStreamNonBlocking));
   for (TileBuf& tb : e->tiles) TRY_OR_FAIL(cudaEventCreateWithFlags(&tb.ev_ready, cudaEventDisableTiming));
   e->batcher = std::thread(batcher_main, e);
   e->completer = std::thread(completer_main, e);
@@ -907,9 +978,12 @@ int ai4e_engine_destroy(ai4e_engine* e) {
   }
   for (TileBuf& tb : e->tiles) {
     if (tb.d) cudaFree(tb.d);
+    if (tb.d_sum) cudaFree(tb.d_sum);
+    if (tb.h_sum) cudaFreeHost(tb.h_sum);
     if (tb.ev_ready) cudaEventDestroy(tb.ev_ready);
   }
   if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+  if (e->sum_stream) cudaStreamDestroy(e->sum_stream);
   if (e->d_blob) cudaFree(e->d_blob);
   if (e->d_stem_w) cudaFree(e->d_stem_w);
   if (e->d_stem_pool_w) cudaFree(e->d_stem_pool_w);
@@ -1343,9 +1417,11 @@ int ai4e_engine_read_activation(ai4e_engine* e, int buf, void* h_dst, uint64_t b
 // chip grid).  The band of chip rows that holds them crosses PCIe ONCE (one 2-D copy on the copy
 // stream into a device tile buffer); the batches made from it carry only (first chip, count) and K1
 // reads every chip in place through the chip-grid strides - no per-chip host copy, no gather kernel.
+// With out_sum_ticket the chips' results are also aggregated on the device (K7) into one tile summary, waited for
+// with ai4e_engine_wait_tile_summary; out_tickets may then be null (nobody wants the per-chip records).
 static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
-                             int chip, int first_chip, int n_chips, uint64_t* out_tickets) {
-  AI4E_REQUIRE(e && h_tile && out_tickets, "submit_tile: null pointer");
+                             int chip, int first_chip, int n_chips, uint64_t* out_tickets, uint64_t* out_sum_ticket = nullptr) {
+  AI4E_REQUIRE(e && h_tile && (out_tickets || out_sum_ticket), "submit_tile: null pointer");
   AI4E_REQUIRE(c == e->desc.in_c, "submit_tile: tile has %d channels, model takes %d", c, e->desc.in_c);
   AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
   AI4E_REQUIRE(row_stride >= 0, "submit_tile: negative row stride");
@@ -1387,12 +1463,37 @@ static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, 
     if (ce != cudaSuccess) { set_last_error("submit_tile: %zu bytes of tile buffer: %s", band_bytes, cudaGetErrorString(ce)); cudaGetLastError(); return release(AI4E_ERR_NOMEM); }
     tb->bytes = band_bytes;
   }
+  if (out_sum_ticket) {  // K7: a zeroed aggregate next to the band, ready (like the band) when ev_ready fires
+    const SumLayout sl(n_chips, e->desc.num_classes);
+    if (tb->sum_cap < sl.bytes) {
+      if (tb->d_sum) cudaFree(tb->d_sum);
+      if (tb->h_sum) cudaFreeHost(tb->h_sum);
+      tb->d_sum = tb->h_sum = nullptr; tb->sum_cap = 0;
+      cudaError_t ce = cudaMalloc((void**)&tb->d_sum, sl.bytes);
+      if (ce == cudaSuccess) ce = cudaHostAlloc((void**)&tb->h_sum, sl.bytes, cudaHostAllocDefault);
+      if (ce != cudaSuccess) { set_last_error("submit_tile: %zu bytes of summary buffer: %s", sl.bytes, cudaGetErrorString(ce)); cudaGetLastError(); return release(AI4E_ERR_NOMEM); }
+      tb->sum_cap = sl.bytes;
+    }
+    cudaError_t ce = cudaMemsetAsync(tb->d_sum, 0, sl.bytes, e->copy_stream);
+    if (ce != cudaSuccess) { set_last_error("submit_tile: summary memset failed: %s", cudaGetErrorString(ce)); return release(AI4E_ERR_CUDA); }
+    std::lock_guard<std::mutex> lk(e->mu);
+    tb->summary = true; tb->sum_chips = n_chips; tb->sum_rc = 0;
+    tb->sum_left = (n_chips + e->max_batch - 1) / e->max_batch;
+    tb->sum_ticket = e->next_sum_ticket++;
+    TileSumRec& sr = e->sums[tb->sum_ticket % kSumRing];
+    sr.id = tb->sum_ticket; sr.status = 1; sr.n = n_chips; sr.data.clear();
+    *out_sum_ticket = tb->sum_ticket;
+  }
   // page-locked source: asynchronous, keep the tile unchanged until its tickets are done; pageable
   // source: the runtime stages it and the tile is free on return
   cudaError_t ce = cudaMemcpy2DAsync(tb->d, row_bytes, h_tile + (size_t)r0 * chip * row_stride, (size_t)row_stride,
                                      (size_t)gw * chip * c, band_rows, cudaMemcpyHostToDevice, e->copy_stream);
   if (ce == cudaSuccess) ce = cudaEventRecord(tb->ev_ready, e->copy_stream);
-  if (ce != cudaSuccess) { set_last_error("submit_tile: H2D copy failed: %s", cudaGetErrorString(ce)); return release(AI4E_ERR_CUDA); }
+  if (ce != cudaSuccess) {
+    set_last_error("submit_tile: H2D copy failed: %s", cudaGetErrorString(ce));
+    if (out_sum_ticket) { std::lock_guard<std::mutex> lk(e->mu); tb->summary = false; e->sums[tb->sum_ticket % kSumRing].status = AI4E_ERR_CUDA; }
+    return release(AI4E_ERR_CUDA);
+  }
 
   // ---- batches over the band
   int done = 0;
@@ -1402,7 +1503,14 @@ static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, 
     for (;;) {
       if (e->stopping || !e->healthy.load()) {
         tb->busy = false;
+        if (out_sum_ticket) {  // the batches that will never be queued: the summary fails instead of waiting for them
+          TileSumRec& sr = e->sums[tb->sum_ticket % kSumRing];
+          if (sr.id == tb->sum_ticket) sr.status = AI4E_ERR_STATE;
+          if (tb->users == 0) tb->summary = false;
+          else { tb->sum_rc = AI4E_ERR_STATE; tb->sum_left -= (n_chips - done + e->max_batch - 1) / e->max_batch; }
+        }
         e->cv_free.notify_all();
+        e->cv_done.notify_all();
         set_last_error("submit_tile: engine stopped or unhealthy");
         return AI4E_ERR_STATE;
       }
@@ -1423,6 +1531,7 @@ static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, 
     ctx->count = count; ctx->src_h = chip; ctx->src_w = chip; ctx->kind = kKindTile;
     ctx->tile = tb; ctx->tile_first = first_chip - r0 * gw + done; ctx->tile_grid_w = gw; ctx->tile_chip = chip;
     ctx->tile_row_bytes = (long long)row_bytes;
+    ctx->sum_first = done;
     ctx->ext_src = nullptr;
     ctx->t_first = Clock::now();
     ctx->first_ticket = e->next_ticket;
@@ -1431,7 +1540,7 @@ static int submit_tile_range(ai4e_engine* e, const uint8_t* h_tile, int tile_h, 
     for (int i = 0; i < count; ++i) {
       const uint64_t t = e->next_ticket++;
       const uint64_t r = t % kResultRing;
-      out_tickets[done + i] = t;
+      if (out_tickets) out_tickets[done + i] = t;
       e->r_submit[r] = ctx->t_first;
       e->r_status[r] = 1;
       e->r_notify[r] = 0;
@@ -1458,6 +1567,61 @@ int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, i
   return AI4E_OK;
 }
 
+int ai4e_engine_submit_tile_summary(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
+                                    int chip, uint64_t* out_tile_ticket, int* out_chips) {
+  AI4E_REQUIRE(e && h_tile && out_tile_ticket, "submit_tile_summary: null pointer");
+  AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "submit_tile_summary: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
+  const int total = (tile_h / chip) * (tile_w / chip);
+  int rc = submit_tile_range(e, h_tile, tile_h, tile_w, c, row_stride, chip, 0, total, nullptr, out_tile_ticket);
+  if (rc) return rc;
+  if (out_chips) *out_chips = total;
+  return AI4E_OK;
+}
+
+// The summary of one tile (or of one replica's chip range): any output may be null.  labels / label_prob hold
+// `capacity_chips` entries at least; hist / mass_q32 hold num_classes.
+static int wait_tile_summary(ai4e_engine* e, uint64_t ticket, int64_t timeout_us, int32_t* labels, float* label_prob,
+                             int capacity_chips, uint32_t* hist, uint64_t* mass_q32, bool accumulate, int* out_chips) {
+  AI4E_REQUIRE(e, "wait_tile_summary: null engine");
+  std::unique_lock<std::mutex> lk(e->mu);
+  AI4E_REQUIRE(ticket < e->next_sum_ticket, "wait_tile_summary: unknown tile ticket %llu", (unsigned long long)ticket);
+  TileSumRec& sr = e->sums[ticket % kSumRing];
+  AI4E_REQUIRE(sr.id == ticket, "wait_tile_summary: the summary of tile ticket %llu has been overwritten (%d are kept)",
+               (unsigned long long)ticket, kSumRing);
+  auto ready = [&] { return sr.id != ticket || sr.status != 1 || e->completer_done; };
+  if (timeout_us < 0) {
+    e->cv_done.wait(lk, ready);
+  } else if (!e->cv_done.wait_for(lk, std::chrono::microseconds(timeout_us), ready)) {
+    set_last_error("wait_tile_summary: tile ticket %llu not finished after %lld us", (unsigned long long)ticket, (long long)timeout_us);
+    return AI4E_ERR_TIMEOUT;
+  }
+  AI4E_REQUIRE(sr.id == ticket, "wait_tile_summary: the summary of tile ticket %llu has been overwritten", (unsigned long long)ticket);
+  if (sr.status == 1) { set_last_error("wait_tile_summary: engine shut down before the tile completed"); return AI4E_ERR_STATE; }
+  if (sr.status != AI4E_OK) {
+    set_last_error("wait_tile_summary: a batch of tile ticket %llu failed (%d)", (unsigned long long)ticket, sr.status);
+    return sr.status < 0 ? sr.status : AI4E_ERR_STATE;
+  }
+  const int K = e->desc.num_classes;
+  const SumLayout sl(sr.n, K);
+  AI4E_REQUIRE(sr.data.size() == sl.bytes, "wait_tile_summary: internal size mismatch");
+  if (out_chips) *out_chips = sr.n;
+  if (labels || label_prob) AI4E_REQUIRE(capacity_chips >= sr.n, "wait_tile_summary: %d chips, room for %d", sr.n, capacity_chips);
+  if (labels) memcpy(labels, sr.data.data() + sl.labels, (size_t)sr.n * 4);
+  if (label_prob) memcpy(label_prob, sr.data.data() + sl.prob, (size_t)sr.n * 4);
+  const uint32_t* h = (const uint32_t*)(sr.data.data() + sl.hist);
+  const uint64_t* m = (const uint64_t*)(sr.data.data() + sl.mass);
+  if (hist) for (int k = 0; k < K; ++k) hist[k] = (accumulate ? hist[k] : 0u) + h[k];
+  if (mass_q32) for (int k = 0; k < K; ++k) mass_q32[k] = (accumulate ? mass_q32[k] : 0ull) + m[k];
+  return AI4E_OK;
+}
+
+int ai4e_engine_wait_tile_summary(ai4e_engine* e, uint64_t tile_ticket, int32_t* labels, float* label_prob, int capacity_chips,
+                                  uint32_t* hist, uint64_t* mass_q32, int* out_chips) {
+  AI4E_REQUIRE(e, "wait_tile_summary: null engine");
+  return wait_tile_summary(e, tile_ticket, (int64_t)e->wait_timeout_ms * 1000, labels, label_prob, capacity_chips, hist,
+                           mass_q32, false, out_chips);
+}
+
 // results of `n` tickets in order: idx [n][5], prob [n][5]
 int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5) {
   AI4E_REQUIRE(e && tickets && top_idx5 && top_prob5 && n >= 0, "wait_many: bad arguments");
@@ -1471,10 +1635,21 @@ int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_
 // ---------------------------------------------------------------------------------------- pool
 // ticket = replica index in the top byte | replica-local ticket.  Routing: the healthy replica
 // with the shortest queue, round-robin among equals (the reference: Istio ROUND_ROBIN).
+// A tile summary dealt over the replicas: which replica summarises which chip range under which of its tickets.
+struct PoolTileRec {
+  uint64_t id = ~0ull;
+  int total = 0;
+  struct Part { int engine, first, n; uint64_t ticket; };
+  std::vector<Part> parts;
+};
+
 struct ai4e_pool {
   std::vector<ai4e_engine*> engines;
   std::atomic<uint64_t> rr{0};
   CompletionQueue cq;  // shared by the replicas: one reaper thread serves all GPUs
+  std::mutex sum_mu;
+  PoolTileRec sums[kSumRing];
+  uint64_t next_sum_ticket = 0;
 };
 
 static constexpr uint64_t kLocalMask = (1ull << 56) - 1;
@@ -1586,12 +1761,64 @@ int ai4e_pool_submit_batch(ai4e_pool* p, const uint8_t* h_images, int count, int
 
 // The chips of a tile in contiguous ranges, one range per healthy replica (256 chips on 8 GPUs: 32
 // each); every replica receives only the band of chip rows it needs.
+static int pool_submit_tile_any(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride, int chip,
+                                uint64_t* out_tickets, int capacity, int* out_count, PoolTileRec* rec);
+
 int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride, int chip,
                           uint64_t* out_tickets, int capacity, int* out_count) {
   AI4E_REQUIRE(p && h_tile && out_tickets && out_count, "pool_submit_tile: null pointer");
+  return pool_submit_tile_any(p, h_tile, tile_h, tile_w, c, row_stride, chip, out_tickets, capacity, out_count, nullptr);
+}
+
+// The same deal with the K7 aggregate: every replica summarises its own chip range on its GPU; the ranges are
+// put together on the host when the summary is waited for (labels side by side, histogram and mass added - integer
+// sums, so the result does not depend on how many replicas shared the tile).
+int ai4e_pool_submit_tile_summary(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride, int chip,
+                                  uint64_t* out_tile_ticket, int* out_chips) {
+  AI4E_REQUIRE(p && h_tile && out_tile_ticket, "pool_submit_tile_summary: null pointer");
+  PoolTileRec rec;
+  int count = 0;
+  const int rc = pool_submit_tile_any(p, h_tile, tile_h, tile_w, c, row_stride, chip, nullptr, 0, &count, &rec);
+  if (rc) return rc;
+  std::lock_guard<std::mutex> lk(p->sum_mu);
+  rec.id = p->next_sum_ticket++;
+  rec.total = count;
+  *out_tile_ticket = rec.id;
+  if (out_chips) *out_chips = count;
+  p->sums[rec.id % kSumRing] = std::move(rec);
+  return AI4E_OK;
+}
+
+int ai4e_pool_wait_tile_summary(ai4e_pool* p, uint64_t tile_ticket, int32_t* labels, float* label_prob, int capacity_chips,
+                                uint32_t* hist, uint64_t* mass_q32, int* out_chips) {
+  AI4E_REQUIRE(p, "pool_wait_tile_summary: null pool");
+  PoolTileRec rec;
+  {
+    std::lock_guard<std::mutex> lk(p->sum_mu);
+    AI4E_REQUIRE(tile_ticket < p->next_sum_ticket, "pool_wait_tile_summary: unknown tile ticket %llu", (unsigned long long)tile_ticket);
+    rec = p->sums[tile_ticket % kSumRing];
+  }
+  AI4E_REQUIRE(rec.id == tile_ticket, "pool_wait_tile_summary: the summary of tile ticket %llu has been overwritten (%d are kept)",
+               (unsigned long long)tile_ticket, kSumRing);
+  if (labels || label_prob) AI4E_REQUIRE(capacity_chips >= rec.total, "pool_wait_tile_summary: %d chips, room for %d", rec.total, capacity_chips);
+  const int K = p->engines[0]->desc.num_classes;
+  if (hist) memset(hist, 0, (size_t)K * sizeof(uint32_t));
+  if (mass_q32) memset(mass_q32, 0, (size_t)K * sizeof(uint64_t));
+  for (const PoolTileRec::Part& part : rec.parts) {
+    ai4e_engine* e = p->engines[part.engine];
+    const int rc = wait_tile_summary(e, part.ticket, (int64_t)e->wait_timeout_ms * 1000, labels ? labels + part.first : nullptr,
+                                     label_prob ? label_prob + part.first : nullptr, part.n, hist, mass_q32, true, nullptr);
+    if (rc) return rc;
+  }
+  if (out_chips) *out_chips = rec.total;
+  return AI4E_OK;
+}
+
+static int pool_submit_tile_any(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride, int chip,
+                                uint64_t* out_tickets, int capacity, int* out_count, PoolTileRec* rec) {
   AI4E_REQUIRE(chip > 0 && tile_h >= chip && tile_w >= chip, "pool_submit_tile: tile %d x %d smaller than a %d chip", tile_h, tile_w, chip);
   const int total = (tile_h / chip) * (tile_w / chip);
-  AI4E_REQUIRE(capacity >= total, "pool_submit_tile: %d tickets needed, room for %d", total, capacity);
+  AI4E_REQUIRE(rec || capacity >= total, "pool_submit_tile: %d tickets needed, room for %d", total, capacity);
   *out_count = 0;
   std::vector<int> alive;
   const uint64_t start = p->rr.fetch_add(1);
@@ -1604,13 +1831,16 @@ int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int t
   const int per = (total + parts - 1) / parts;
   std::vector<int> rcs(parts, AI4E_OK);
   std::vector<std::string> msgs(parts);
+  std::vector<uint64_t> sum_tickets(parts, 0);
   auto work = [&](int k) {  // one submitter per replica: the H2D copies of the bands run side by side
     const int first = k * per, n = std::min(per, total - first);
     if (n <= 0) return;
     const int i = alive[k];
-    const int rc = submit_tile_range(p->engines[i], h_tile, tile_h, tile_w, c, row_stride, chip, first, n, out_tickets + first);
+    const int rc = submit_tile_range(p->engines[i], h_tile, tile_h, tile_w, c, row_stride, chip, first, n,
+                                     out_tickets ? out_tickets + first : nullptr, rec ? &sum_tickets[k] : nullptr);
     if (rc) { rcs[k] = rc; msgs[k] = ai4e_last_error(); return; }
-    for (int j = 0; j < n; ++j) out_tickets[first + j] = ((uint64_t)i << 56) | (out_tickets[first + j] & kLocalMask);
+    if (out_tickets)
+      for (int j = 0; j < n; ++j) out_tickets[first + j] = ((uint64_t)i << 56) | (out_tickets[first + j] & kLocalMask);
   };
   std::vector<std::thread> th;
   for (int k = 1; k < parts; ++k) th.emplace_back(work, k);
@@ -1618,6 +1848,11 @@ int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int t
   for (auto& t : th) t.join();
   for (int k = 0; k < parts; ++k)
     if (rcs[k]) { set_last_error("%s", msgs[k].c_str()); return rcs[k]; }
+  if (rec)
+    for (int k = 0; k < parts; ++k) {
+      const int first = k * per, n = std::min(per, total - first);
+      if (n > 0) rec->parts.push_back({alive[k], first, n, sum_tickets[k]});
+    }
   *out_count = total;
   return AI4E_OK;
 }

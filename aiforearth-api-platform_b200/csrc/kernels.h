@@ -111,6 +111,11 @@ void stem_repack_weights(const uint16_t* w_krsc, uint16_t* w_sp);  // [64][7][7]
 int igemm_make_plan_stem(IgemmPlan* plan, const void* in, int N, int H, int W, const void* weight_sp,
                          const float* bias, int relu, void* out);
 
+// ---- K7 tile summary (tile_summary.cu): label map, class histogram and 32.32 fixed-point probability mass of a tile's chips
+int tile_summary_launch(const int32_t* d_idx5, const float* d_prob5, int count, int first, int num_classes,
+                        int32_t* d_labels, float* d_label_prob, uint32_t* d_hist, unsigned long long* d_mass_q32,
+                        cudaStream_t stream);
+
 // ---- K2 + K3 in one kernel (stem_pool.cu): 7x7/2 stem + bias + ReLU + 3x3/2 max-pool, NHWC4 in, pooled NHWC out
 struct StemPoolPlan {
   CUtensorMap tmap_a;  // input rows, [N][H][W/16][64 elements], nine rows per load

@@ -354,6 +354,28 @@ AI4E_API int ai4e_engine_submit_image(ai4e_engine* e, const uint8_t* data, uint6
 AI4E_API int ai4e_engine_submit_tile(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c,
                                      int row_stride, int chip, uint64_t* out_tickets, int capacity,
                                      int* out_count);
+/* K7.  tile -> chips -> classify -> AGGREGATE, all on the device (the reference would chain an
+ * aggregation stage as one more task through AddPipelineTask, Common/task_management/distributed_api_task.py:67-100).
+ * Like ai4e_engine_submit_tile, but behind every batch's head one small launch folds the chips' top-5 into the
+ * tile's summary in device memory, and ONE ticket stands for the whole tile:
+ *   labels[i], label_prob[i]  top-1 class / probability of chip i (row-major chip grid)  - the tile's label map
+ *   hist[k]                   chips whose top-1 class is k
+ *   mass_q32[k]               sum over chips and their top-5 entries of class k of round(p * 2^32): the probability
+ *                             mass in 32.32 fixed point (integer sums: independent of batch order and replica count)
+ * wait_tile_summary blocks like ai4e_engine_wait (AI4E_B200_WAIT_TIMEOUT_MS); any output may be NULL; labels /
+ * label_prob need capacity_chips >= the tile's chips, hist / mass_q32 num_classes entries.  The last kSumRing = 64
+ * summaries are kept.  No per-chip record crosses PCIe for such a tile except the 40-byte top-5 the head always
+ * returns. */
+AI4E_API int ai4e_engine_submit_tile_summary(ai4e_engine* e, const uint8_t* h_tile, int tile_h, int tile_w, int c,
+                                             int row_stride, int chip, uint64_t* out_tile_ticket, int* out_chips);
+AI4E_API int ai4e_engine_wait_tile_summary(ai4e_engine* e, uint64_t tile_ticket, int32_t* labels, float* label_prob,
+                                           int capacity_chips, uint32_t* hist, uint64_t* mass_q32, int* out_chips);
+/* The aggregate as a stand-alone device op: folds the top-5 of `count` chips (chips [first, first + count) of the
+ * summary) into labels / label_prob / hist / mass_q32, all device pointers; hist and mass_q32 are added to (zero
+ * them before the first call of a tile).  No reference counterpart: the reference has no arithmetic. */
+AI4E_API int ai4e_tile_summary(const int32_t* d_top_idx5, const float* d_top_prob5, int count, int first, int num_classes,
+                               int32_t* d_labels, float* d_label_prob, uint32_t* d_hist, uint64_t* d_mass_q32,
+                               void* stream);
 /* ai4e_engine_wait for n tickets: top_idx5 / top_prob5 are [n][5]. */
 AI4E_API int ai4e_engine_wait_many(ai4e_engine* e, const uint64_t* tickets, int n, int32_t* top_idx5,
                                    float* top_prob5);
@@ -410,6 +432,12 @@ AI4E_API int ai4e_pool_submit_batch(ai4e_pool* p, const uint8_t* h_images, int c
                            uint64_t* out_first_ticket);
 AI4E_API int ai4e_pool_submit_tile(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c, int row_stride,
                           int chip, uint64_t* out_tickets, int capacity, int* out_count);
+/* K7 behind the dispatcher: every replica summarises its own chip range on its GPU; wait puts the ranges together
+ * (labels side by side, hist and mass_q32 added - integer sums, the same result for any number of replicas). */
+AI4E_API int ai4e_pool_submit_tile_summary(ai4e_pool* p, const uint8_t* h_tile, int tile_h, int tile_w, int c,
+                                           int row_stride, int chip, uint64_t* out_tile_ticket, int* out_chips);
+AI4E_API int ai4e_pool_wait_tile_summary(ai4e_pool* p, uint64_t tile_ticket, int32_t* labels, float* label_prob,
+                                         int capacity_chips, uint32_t* hist, uint64_t* mass_q32, int* out_chips);
 AI4E_API int ai4e_pool_wait_many(ai4e_pool* p, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5);
 AI4E_API int ai4e_pool_poll(ai4e_pool* p, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
                    int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n);

@@ -21,20 +21,27 @@ sys.path[:0] = [ROOT, os.path.join(ROOT, "aiforearth-api-platform_b200")]
 import numpy as np  # noqa: E402
 
 
-def run(pool, tiles, seconds, in_flight, chips_per_tile):
+def run(pool, tiles, seconds, in_flight, chips_per_tile, summary=False):
+    """summary: tile -> chips -> classify -> aggregate (K7), one ticket and one small record per tile"""
+    if summary:
+        submit = lambda t: pool.submit_tile_summary(t, 256)
+        wait = lambda h: pool.wait_tile_summary(*h)
+    else:
+        submit = lambda t: pool.submit_tile(t, 256)
+        wait = pool.wait_many
     pending, n = [], 0
     for t in tiles[:2]:  # warm-up (tile buffers are allocated on first use)
-        pool.wait_many(pool.submit_tile(t, 256))
+        wait(submit(t))
     t0 = time.perf_counter()
     i = 0
     while time.perf_counter() - t0 < seconds:
-        pending.append(pool.submit_tile(tiles[i % len(tiles)], 256))
+        pending.append(submit(tiles[i % len(tiles)]))
         i += 1
         while len(pending) >= in_flight:
-            pool.wait_many(pending.pop(0))
+            wait(pending.pop(0))
             n += 1
     while pending:
-        pool.wait_many(pending.pop(0))
+        wait(pending.pop(0))
         n += 1
     dt = time.perf_counter() - t0
     return {"tiles": n, "seconds": dt, "tiles_per_s": n / dt, "chips_per_s": chips_per_tile * n / dt}
@@ -77,6 +84,20 @@ def main():
                     r["frac_of_conv_bound"] = r["chips_per_s"] / bound
                 rows.append(r)
                 print(json.dumps(r), flush=True)
+        # K7: the same tiles with the aggregate computed on the GPUs; parity in passing against the per-chip results
+        t_idx, t_prob = pool.wait_many(pool.submit_tile(tiles[0], 256))
+        got = pool.wait_tile_summary(*pool.submit_tile_summary(tiles[0], 256))
+        q = np.rint(t_prob.astype(np.float64) * 4294967296.0).astype(np.uint64)
+        mass = np.zeros(prog.num_classes, np.uint64)
+        np.add.at(mass, t_idx.ravel(), q.ravel())
+        same_sum = bool(np.array_equal(got["labels"].ravel(), t_idx[:, 0]) and np.array_equal(got["mass_q32"], mass)
+                        and np.array_equal(got["hist"], np.bincount(t_idx[:, 0], minlength=prog.num_classes)))
+        r = run(pool, pinned, a.seconds, 3, chips, summary=True)
+        r.update({"config": f"{a.tile}x{a.tile}x4 uint8 tile -> {chips} chips -> ResNet-50 -> tile summary (label map, histogram, mass)",
+                  "gpus": a.gpus, "source_memory": "page-locked", "tiles_in_flight": 3, "summary_equals_aggregate_of_chip_results": same_sum,
+                  "path": "Pool.submit_tile_summary: K6 + forward + K7 aggregate on each replica, one record per tile"})
+        rows.append(r)
+        print(json.dumps(r), flush=True)
     if a.out:
         with open(a.out, "a") as fh:
             for r in rows:
