@@ -34,6 +34,7 @@
 #include "igemm_tiles.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace ai4e {
 
@@ -65,6 +66,17 @@ struct FusedCfg {
   static constexpr bool kPackW3 = kKB2 == 2 && kBBytes == kABytes;
   static constexpr int kUnitsPerPass = kPackW3 ? 1 : kKB2;
 };
+
+// Order of the ring's units inside one iteration `st` of the persistent loop: the nk K blocks of tile st's first
+// GEMM and the nu units of tile st-1's second GEMM.  Plain order: all K blocks, then all units - the MMA warp
+// then sits in front of acc2 buffers the epilogue has not drained yet (a pass takes the epilogue ~2,400 cycles,
+// the tensor core ~540) with the ring full and no load in flight behind it.  Interleaved: unit u goes after K
+// block fused_unit_slot(u), evenly spread, so every pass finds its accumulator free and the ring keeps moving.
+// Both producers and the MMA warp walk the same sequence.  (slot <= 0 or no K blocks: the units follow at the end.)
+__device__ __forceinline__ int fused_unit_slot(int u, int nk, int nu, int interleave) {
+  if (interleave == 2) return ((2 * u + 3) * nk) / (2 * (nu + 1));  // half a step later: more room for the first epilogue step
+  return interleave ? ((u + 1) * nk) / (nu + 1) : 0;
+}
 
 template <int N1>
 __global__ void __launch_bounds__(kIgemmThreads, 1)
@@ -149,77 +161,82 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     uint32_t phase = 0;
     bool waited = false;
     for (int st = 0; st <= my_tiles; ++st) {
-      if (st < my_tiles) {
+      const int nk = st < my_tiles ? p.num_k_blocks : 0;
+      const int nu = st >= 1 ? units2 : 0;
+      int w_base = 0, h_base = 0, n_img = 0;
+      if (nk) {
         const int m0 = tile_row(st);
-        const int n_img = m0 / p.PQ;
+        n_img = m0 / p.PQ;
         const int rem = m0 - n_img * p.PQ;
         const int p0 = rem / p.Q;
         const int q0 = rem - p0 * p.Q;
-        const int w_base = q0 * p.stride - p.pad, h_base = p0 * p.stride - p.pad;
+        w_base = q0 * p.stride - p.pad; h_base = p0 * p.stride - p.pad;
         if (!waited) {  // x is the previous layer's output
           pdl_wait();
           waited = true;
         }
-        int r = 0, s = 0, cb = 0;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (elect_one()) {
-            mbar_expect_tx(full_bar(stage), kABytes);
-            tma_load_im2col_4d(smem_base + stage * Cfg::kStageBytes, &tmap_a, full_bar(stage), cb * kBlockK, w_base,
-                               h_base, n_img, (uint16_t)s, (uint16_t)r);
-          }
-          __syncwarp();
-          if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
-        }
       }
-      if (st >= 1) {
-        for (int u = 0; u < units2; ++u) {  // pass-major: w3 rows [128 * pass, +128), K block u % kKB2
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (elect_one()) {
-            mbar_expect_tx(full_bar(stage), kABytes);
-            if constexpr (Cfg::kPackW3)  // K block 0 of pass u here, K block 1 in the B slot (the other producer)
-              tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), 0, u * 128);
-            else
-              tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), (u % kKB2) * kBlockK,
-                          (u / kKB2) * 128);
-          }
-          __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      auto unit = [&](int u) {  // pass-major: w3 rows [128 * pass, +128), K block u % kKB2
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), kABytes);
+          if constexpr (Cfg::kPackW3)  // K block 0 of pass u here, K block 1 in the B slot (the other producer)
+            tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), 0, u * 128);
+          else
+            tma_load_2d(smem_base + stage * Cfg::kStageBytes, &tmap_w3, full_bar(stage), (u % kKB2) * kBlockK,
+                        (u / kKB2) * 128);
         }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      };
+      int u = 0;
+      int r = 0, s = 0, cb = 0;
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), kABytes);
+          tma_load_im2col_4d(smem_base + stage * Cfg::kStageBytes, &tmap_a, full_bar(stage), cb * kBlockK, w_base,
+                             h_base, n_img, (uint16_t)s, (uint16_t)r);
+        }
+        __syncwarp();
+        if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
       }
+      while (u < nu) unit(u++);
     }
   } else if (warp == 2 + kEpiWarps) {
     // ------------------- producer: w2 tiles; the w3 stages carry nothing in their B slot -------
     int stage = 0;
     uint32_t phase = 0;
     for (int st = 0; st <= my_tiles; ++st) {
-      if (st < my_tiles) {
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (elect_one()) {
+      const int nk = st < my_tiles ? p.num_k_blocks : 0;
+      const int nu = st >= 1 ? units2 : 0;
+      auto unit = [&](int u) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (elect_one()) {
+          if constexpr (Cfg::kPackW3) {
             mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
-            tma_load_2d(smem_base + stage * Cfg::kStageBytes + kABytes, &tmap_w2, full_bar(stage), kb * kBlockK, 0);
+            tma_load_2d(smem_base + stage * Cfg::kStageBytes + kABytes, &tmap_w3, full_bar(stage), kBlockK, u * 128);
+          } else {
+            mbar_arrive(full_bar(stage));
           }
-          __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-      }
-      if (st >= 1) {
-        for (int u = 0; u < units2; ++u) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (elect_one()) {
-            if constexpr (Cfg::kPackW3) {
-              mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
-              tma_load_2d(smem_base + stage * Cfg::kStageBytes + kABytes, &tmap_w3, full_bar(stage), kBlockK, u * 128);
-            } else {
-              mbar_arrive(full_bar(stage));
-            }
-          }
-          __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      };
+      int u = 0;
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(full_bar(stage), Cfg::kBBytes);
+          tma_load_2d(smem_base + stage * Cfg::kStageBytes + kABytes, &tmap_w2, full_bar(stage), kb * kBlockK, 0);
         }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
       }
+      while (u < nu) unit(u++);
     }
   } else if (warp == 1) {
     // ------------------- MMA issuer (convergent warp, one elected lane) -----------------------
@@ -229,66 +246,70 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     uint32_t phase = 0;
     uint32_t gp = 0;  // 128-channel passes issued so far: selects the acc2 buffer and its phase
     for (int st = 0; st <= my_tiles; ++st) {
-      if (st < my_tiles) {  // first GEMM of tile st
-        const uint32_t a = st & 1u;
-        mbar_wait(acc1_empty(a), ((st >> 1) & 1u) ^ 1u);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + a * N1;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(full_bar(stage), phase);
+      const int nk = st < my_tiles ? p.num_k_blocks : 0;
+      const int nu = st >= 1 ? units2 : 0;
+      // one unit of the second GEMM of tile st - 1 (its `mid` tile must be written before the first one)
+      auto unit = [&](int u) {
+        const int kb = u % Cfg::kUnitsPerPass;
+        const uint32_t b = gp & 1u;
+        if (u == 0) {
+          mbar_wait(mid_full, (uint32_t)(st - 1) & 1u);
           tc_fence_after();
-          const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
-          if (elect_one()) {
-            const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
-            const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc1, (kb | k) != 0 ? 1u : 0u);
-            umma_commit(empty_bar(stage));
-          }
-          __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        if (elect_one()) umma_commit(acc1_full(a));
-        __syncwarp();
-      }
-      if (st >= 1) {  // second GEMM of tile st - 1: its `mid` tile must be written
-        const int t = st - 1;
-        mbar_wait(mid_full, t & 1u);
-        tc_fence_after();
-        for (int ps = 0; ps < passes; ++ps, ++gp) {
-          const uint32_t b = gp & 1u;
+        if (kb == 0) {
           mbar_wait(acc2_empty(b), ((gp >> 1) & 1u) ^ 1u);
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + Cfg::kAcc2Col + b * 128;
-          for (int kb = 0; kb < Cfg::kUnitsPerPass; ++kb) {
-            mbar_wait(full_bar(stage), phase);
-            tc_fence_after();
-            if (elect_one()) {
-              if constexpr (Cfg::kPackW3) {
-#pragma unroll
-                for (int kk = 0; kk < 2; ++kk) {  // both K blocks of the pass sit in this stage
-                  const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kk * kChunkBytes, 128, 2);
-                  const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes + kk * kABytes, 128, 2);
-#pragma unroll
-                  for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kk | k) != 0 ? 1u : 0u);
-                }
-              } else {
-                const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kb * kChunkBytes, 128, 2);
-                const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes, 128, 2);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
-              }
-              umma_commit(empty_bar(stage));
-            }
-            __syncwarp();
-            if (++stage == kStages) { stage = 0; phase ^= 1u; }
-          }
-          if (elect_one()) umma_commit(acc2_full(b));
-          __syncwarp();
         }
-        if (elect_one()) umma_commit(mid_empty);  // `mid` may be overwritten once these MMAs retire
+        const uint32_t d_tmem = tmem_base + Cfg::kAcc2Col + b * 128;
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        if (elect_one()) {
+          if constexpr (Cfg::kPackW3) {
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {  // both K blocks of the pass sit in this stage
+              const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kk * kChunkBytes, 128, 2);
+              const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes + kk * kABytes, 128, 2);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kk | k) != 0 ? 1u : 0u);
+            }
+          } else {
+            const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kb * kChunkBytes, 128, 2);
+            const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes, 128, 2);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));
+          if (kb == Cfg::kUnitsPerPass - 1) umma_commit(acc2_full(b));
+          if (u == nu - 1) umma_commit(mid_empty);  // `mid` may be overwritten once these MMAs retire
+        }
         __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        if (kb == Cfg::kUnitsPerPass - 1) ++gp;
+      };
+      int u = 0;
+      const uint32_t a = st & 1u;
+      const uint32_t d_tmem1 = tmem_base + a * N1;
+      if (nk) {  // first GEMM of tile st
+        mbar_wait(acc1_empty(a), ((st >> 1) & 1u) ^ 1u);
+        tc_fence_after();
       }
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
+        if (elect_one()) {
+          const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
+          const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem1, adesc + 2u * k, bdesc + 2u * k, idesc1, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(empty_bar(stage));
+          if (kb == nk - 1) umma_commit(acc1_full(a));
+        }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
+      }
+      while (u < nu) unit(u++);
     }
   } else if (warp < 2 + kEpiWarps) {
     // ------------------- epilogue warps ------------------------------------------------------
@@ -440,6 +461,8 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   FusedParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cmid = Cmid; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0; q.reverse = 0;
+  q.interleave = 0;
+  if (const char* v = getenv("AI4E_B200_FUSED_INTERLEAVE")) q.interleave = atoi(v);  // 0 plain order, 1 / 2 interleaved (see fused_unit_slot)
   q.bias2 = bias2; q.bias3 = bias3;
   plan->max_batch = N;
   plan->grid_sms = 0;

@@ -78,6 +78,7 @@ struct FusedParams {
   int cin_blocks, num_k_blocks;
   int num_tiles;
   int reverse;  // walk the row tiles from the last to the first
+  int interleave;  // spread the second GEMM's passes of tile t-1 among the K blocks of tile t (see conv_fused.cu)
   const float* bias2;
   const float* bias3;
 };
