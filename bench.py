@@ -435,8 +435,8 @@ def main():
                 "api": f"Engine.submit_batch/wait, page-locked host batches, {E2E_INFLIGHT} batches in flight"},
         "gpu_launches": stats["launches_per_forward"] * K,
         "parity_checked": True, "parity": parity,
-        "roofline": {"bound": "tensor", "kernel": f"tcgen05 convolutions: conv_igemm_kernel + bottleneck_tail_kernel ({igemm_launches} layers in "
-                               f"{stats['launches_per_forward'] - 5} launches per step)", "achieved": achieved,
+        "roofline": {"bound": "tensor", "kernel": f"tcgen05 convolutions: stem_pool_kernel + conv_igemm_kernel + bottleneck_tail_kernel ({igemm_launches} layers in "
+                               f"{stats['launches_per_forward'] - 4} launches per step; the other 4: preprocess, avg-pool, FC, softmax/top-5)", "achieved": achieved,
                      "peak": peak_burst, "unit": "TFLOP/s", "frac": achieved / peak_burst, "traffic": traffic,
                      "traffic_source": traffic_src,
                      "peak_source": f"{peaks['source']} bf16 burst (launches timed alone, one by one)", "ms_per_step_in_kernel": igemm_ms,
