@@ -242,6 +242,22 @@ int ai4e_bottleneck_tail(const void* d_in_nhwc, int batch, int h, int w, int cin
   int rc = fused_tail_make_plan(&plan, d_in_nhwc, batch, h, w, cin, d_w2_krsc, d_bias2, cmid, kh, kw, stride, pad, d_w3_kc,
                                 d_bias3, cout, d_residual, d_out_nhwc);
   if (rc) return rc;
+  if (const char* trace = getenv("AI4E_B200_PIPE_TRACE")) {  // developer aid (needs a -DAI4E_PIPE_TRACE build): raw stamps of CTA 0
+    long long* d = nullptr;
+    AI4E_CUDA_TRY(cudaMalloc((void**)&d, 2048 * sizeof(long long)));
+    AI4E_CUDA_TRY(cudaMemset(d, 0, 2048 * sizeof(long long)));
+    plan.prm.dbg = d;
+    rc = fused_tail_launch(plan, batch, (cudaStream_t)stream);
+    AI4E_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    std::vector<long long> h(2048);
+    AI4E_CUDA_TRY(cudaMemcpy(h.data(), d, 2048 * sizeof(long long), cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    if (FILE* f = fopen(trace, "w")) {
+      for (int i = 0; i < 2048; ++i) fprintf(f, "%d %lld\n", i, h[i]);
+      fclose(f);
+    }
+    return rc;
+  }
   return fused_tail_launch(plan, batch, (cudaStream_t)stream);
 }
 

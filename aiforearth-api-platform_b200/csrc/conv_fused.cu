@@ -36,6 +36,18 @@
 #include <algorithm>
 #include <cstdlib>
 
+// Developer aid, as in conv_igemm.cu: -DAI4E_PIPE_TRACE makes CTA 0 stamp its pipeline into FusedParams::dbg
+// (dumped by ai4e_bottleneck_tail when AI4E_B200_PIPE_TRACE=<file> is set; tools/trace_decode_fused.py reads it).
+// [0,256) A producer: slot free for ring unit g | [256,512) MMA warp starts waiting for unit g | [512,768) data seen |
+// [768,1024) MMAs issued | 1024 + 16 * tile + j: MMA warp (0/1 acc1_empty wait, 2/3 mid_full wait, 4..7 acc2_empty of pass
+// 0..3 granted), epilogue warp 0 (8 acc1_full seen, 9 mid_empty seen, 10 step 2 done, 11..14 acc2_full of pass 0..3 seen,
+// 15 last store issued) | 1600.. kernel phases
+#ifdef AI4E_PIPE_TRACE
+#define FT(cond, slot) do { if (p.dbg && blockIdx.x == 0 && (cond) && (slot) < 2048) p.dbg[(slot)] = clock64(); } while (0)
+#else
+#define FT(cond, slot) do { } while (0)
+#endif
+
 namespace ai4e {
 
 template <int N1>  // Cmid: 64 or 128
@@ -109,6 +121,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  FT(threadIdx.x == 0, 1600);
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -143,6 +156,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
   pdl_launch_dependents();
+  FT(threadIdx.x == 0, 1601);
 
   // this CTA's tiles: blockIdx.x, + gridDim.x, ...
   const int my_tiles = p.num_tiles > (int)blockIdx.x ? (p.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
@@ -160,6 +174,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     int stage = 0;
     uint32_t phase = 0;
     bool waited = false;
+    [[maybe_unused]] int g = 0;  // ring units so far (trace)
     for (int st = 0; st <= my_tiles; ++st) {
       const int nk = st < my_tiles ? p.num_k_blocks : 0;
       const int nu = st >= 1 ? units2 : 0;
@@ -174,10 +189,12 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         if (!waited) {  // x is the previous layer's output
           pdl_wait();
           waited = true;
+          FT(lane == 0, 1602);
         }
       }
       auto unit = [&](int u) {  // pass-major: w3 rows [128 * pass, +128), K block u % kKB2
         mbar_wait(empty_bar(stage), phase ^ 1u);
+        FT(lane == 0 && g < 256, g); ++g;
         if (elect_one()) {
           mbar_expect_tx(full_bar(stage), kABytes);
           if constexpr (Cfg::kPackW3)  // K block 0 of pass u here, K block 1 in the B slot (the other producer)
@@ -193,6 +210,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       int r = 0, s = 0, cb = 0;
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
+        FT(lane == 0 && g < 256, g); ++g;
         if (elect_one()) {
           mbar_expect_tx(full_bar(stage), kABytes);
           tma_load_im2col_4d(smem_base + stage * Cfg::kStageBytes, &tmap_a, full_bar(stage), cb * kBlockK, w_base,
@@ -245,6 +263,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     int stage = 0;
     uint32_t phase = 0;
     uint32_t gp = 0;  // 128-channel passes issued so far: selects the acc2 buffer and its phase
+    [[maybe_unused]] int g = 0;
     for (int st = 0; st <= my_tiles; ++st) {
       const int nk = st < my_tiles ? p.num_k_blocks : 0;
       const int nu = st >= 1 ? units2 : 0;
@@ -253,16 +272,21 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         const int kb = u % Cfg::kUnitsPerPass;
         const uint32_t b = gp & 1u;
         if (u == 0) {
+          FT(lane == 0 && st - 1 < 32, 1024 + 16 * (st - 1) + 2);
           mbar_wait(mid_full, (uint32_t)(st - 1) & 1u);
           tc_fence_after();
+          FT(lane == 0 && st - 1 < 32, 1024 + 16 * (st - 1) + 3);
         }
         if (kb == 0) {
           mbar_wait(acc2_empty(b), ((gp >> 1) & 1u) ^ 1u);
           tc_fence_after();
+          FT(lane == 0 && st - 1 < 32 && u / Cfg::kUnitsPerPass < 4, 1024 + 16 * (st - 1) + 4 + u / Cfg::kUnitsPerPass);
         }
         const uint32_t d_tmem = tmem_base + Cfg::kAcc2Col + b * 128;
+        FT(lane == 0 && g < 256, 256 + g);
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
+        FT(lane == 0 && g < 256, 512 + g);
         if (elect_one()) {
           if constexpr (Cfg::kPackW3) {
 #pragma unroll
@@ -283,6 +307,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           if (u == nu - 1) umma_commit(mid_empty);  // `mid` may be overwritten once these MMAs retire
         }
         __syncwarp();
+        FT(lane == 0 && g < 256, 768 + g); ++g;
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
         if (kb == Cfg::kUnitsPerPass - 1) ++gp;
       };
@@ -290,12 +315,16 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       const uint32_t a = st & 1u;
       const uint32_t d_tmem1 = tmem_base + a * N1;
       if (nk) {  // first GEMM of tile st
+        FT(lane == 0 && st < 32, 1024 + 16 * st + 0);
         mbar_wait(acc1_empty(a), ((st >> 1) & 1u) ^ 1u);
         tc_fence_after();
+        FT(lane == 0 && st < 32, 1024 + 16 * st + 1);
       }
       for (int kb = 0; kb < nk; ++kb) {
+        FT(lane == 0 && g < 256, 256 + g);
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
+        FT(lane == 0 && g < 256, 512 + g);
         const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
         if (elect_one()) {
           const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
@@ -306,6 +335,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           if (kb == nk - 1) umma_commit(acc1_full(a));
         }
         __syncwarp();
+        FT(lane == 0 && g < 256, 768 + g); ++g;
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
         while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
       }
@@ -335,7 +365,9 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         const uint32_t a = i & 1u;
         mbar_wait(acc1_full(a), (i >> 1) & 1u);
         tc_fence_after();
+        FT(ew == 0 && lane == 0 && i < 32, 1024 + 16 * i + 8);
         if (i >= 1) mbar_wait(mid_empty, (i - 1) & 1u);  // the previous tile's second GEMM has read `mid`
+        FT(ew == 0 && lane == 0 && i < 32, 1024 + 16 * i + 9);
         for (int c = side; c < kKB2; c += 2) {
           const uint32_t t_addr = tmem_base + a * N1 + c * kChunkN + lane_tmem;
           tmem_ld_32x32b_x32(t_addr, vlo);
@@ -357,6 +389,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           mbar_arrive(acc1_empty(a));
           mbar_arrive(mid_full);
         }
+        FT(ew == 0 && lane == 0 && i < 32, 1024 + 16 * i + 10);
       }
       // ---- step 4: acc2 (+ b3 + residual, relu) -> z, one 64-channel chunk per pass and side
       for (int ps = 0; ps < passes; ++ps, ++gs) {
@@ -365,6 +398,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         const float2 bias2 = __ldg(reinterpret_cast<const float2*>(p.bias3 + n0c) + lane);
         mbar_wait(acc2_full(b), (gs >> 1) & 1u);
         tc_fence_after();
+        FT(ew == 0 && lane == 0 && i < 32 && ps < 4, 1024 + 16 * i + 11 + ps);
         const uint32_t t_addr = tmem_base + Cfg::kAcc2Col + b * 128 + side * kChunkN + lane_tmem;
         tmem_ld_32x32b_x32(t_addr, vlo);
         tmem_ld_32x32b_x32(t_addr + 32, vhi);
@@ -395,6 +429,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
             tma_store_2d(&tmap_out, res_base + rb * kChunkBytes + quad * kSliceBytes, n0c, m0 + quad * 32);
           bulk_commit_group();
         }
+        FT(ew == 0 && lane == 0 && i < 32 && ps == passes - 1, 1024 + 16 * i + 15);
         pending_buf = rb;
       }
     }
@@ -431,6 +466,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
 
   tc_fence_before();
   __syncthreads();
+  FT(threadIdx.x == 0, 1603);
   if (warp == 1) {
     __syncwarp();
     tc_fence_after();
@@ -462,6 +498,7 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cmid = Cmid; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0; q.reverse = 0;
   q.interleave = 0;
+  q.dbg = nullptr;
   if (const char* v = getenv("AI4E_B200_FUSED_INTERLEAVE")) q.interleave = atoi(v);  // 0 plain order, 1 / 2 interleaved (see fused_unit_slot)
   q.bias2 = bias2; q.bias3 = bias3;
   plan->max_batch = N;

@@ -79,6 +79,7 @@ struct FusedParams {
   int num_tiles;
   int reverse;  // walk the row tiles from the last to the first
   int interleave;  // spread the second GEMM's passes of tile t-1 among the K blocks of tile t (see conv_fused.cu)
+  long long* dbg;  // developer aid (-DAI4E_PIPE_TRACE): clock64 stamps of CTA 0's pipeline (2048 slots), null in production
   const float* bias2;
   const float* bias3;
 };
