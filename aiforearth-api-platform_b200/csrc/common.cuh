@@ -399,6 +399,15 @@ __device__ __forceinline__ uint64_t umma_smem_desc_kmajor(uint32_t saddr, uint32
   d |= static_cast<uint64_t>(layout_type) << 61;                  // layout type     [61,64)
   return d;
 }
+// The descriptors of a ring of K-major, 128-byte-swizzle tiles differ only in the start-address field.  An MMA loop
+// that keeps the low word in a register (advance it by bytes >> 4) and joins it with this constant high word issues
+// its tcgen05.mma from three integer adds per instruction instead of rebuilding both descriptors from the stage
+// index (a dozen dependent uniform-datapath operations per K block in front of the first MMA).
+constexpr uint32_t kUmmaDescHiK128 = ((8u * 128u) >> 4) | (1u << 14) | (2u << 29);  // SBO 1024 B, version 1, SWIZZLE_128B
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t saddr) { return ((saddr & 0x3FFFFu) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint64_t umma_desc_join(uint32_t lo) {
+  return (static_cast<uint64_t>(kUmmaDescHiK128) << 32) | lo;
+}
 // General form: explicit leading-dimension (K direction between 16-byte core-matrix columns)
 // and stride-dimension (M/N direction between 8-row groups) byte offsets.  With layout_type 0
 // (no swizzle) the operand is a grid of 8-row x 16-byte core matrices, each 128 contiguous bytes.

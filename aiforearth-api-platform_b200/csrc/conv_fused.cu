@@ -42,8 +42,10 @@
 // [768,1024) MMAs issued | 1024 + 16 * tile + j: MMA warp (0/1 acc1_empty wait, 2/3 mid_full wait, 4..7 acc2_empty of pass
 // 0..3 granted), epilogue warp 0 (8 acc1_full seen, 9 mid_empty seen, 10 step 2 done, 11..14 acc2_full of pass 0..3 seen,
 // 15 last store issued) | 1600.. kernel phases
+// (-DAI4E_PIPE_TRACE=1: the per-tile and phase stamps only; =2: also the per-unit stamps, which cost the MMA warp ~200
+// cycles per unit and so overstate the K loop.)
 #ifdef AI4E_PIPE_TRACE
-#define FT(cond, slot) do { if (p.dbg && blockIdx.x == 0 && (cond) && (slot) < 2048) p.dbg[(slot)] = clock64(); } while (0)
+#define FT(cond, slot) do { if (p.dbg && blockIdx.x == 0 && ((slot) >= 1024 || AI4E_PIPE_TRACE >= 2) && (cond) && (slot) < 2048) p.dbg[(slot)] = clock64(); } while (0)
 #else
 #define FT(cond, slot) do { } while (0)
 #endif
@@ -207,6 +209,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       };
       int u = 0;
+      int next_at = fused_unit_slot(0, nk, nu, p.interleave);  // the K block after which unit u goes (0: at the end)
       int r = 0, s = 0, cb = 0;
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -219,7 +222,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         __syncwarp();
         if (++cb == p.cin_blocks) { cb = 0; if (++s == p.S) { s = 0; ++r; } }
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
-        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
+        while (u < nu && next_at == kb + 1) { unit(u++); next_at = fused_unit_slot(u, nk, nu, p.interleave); }
       }
       while (u < nu) unit(u++);
     }
@@ -244,6 +247,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       };
       int u = 0;
+      int next_at = fused_unit_slot(0, nk, nu, p.interleave);  // the K block after which unit u goes (0: at the end)
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
         if (elect_one()) {
@@ -252,7 +256,7 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         }
         __syncwarp();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
-        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
+        while (u < nu && next_at == kb + 1) { unit(u++); next_at = fused_unit_slot(u, nk, nu, p.interleave); }
       }
       while (u < nu) unit(u++);
     }
@@ -262,6 +266,14 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
     constexpr uint32_t idesc2 = umma_idesc_bf16_f32(kBlockM, 128);
     int stage = 0;
     uint32_t phase = 0;
+    // descriptor low word and barrier address of the current stage, advanced with it (see umma_desc_join)
+    const uint32_t ring_lo0 = umma_desc_lo(smem_base), mid_lo = umma_desc_lo(mid_base);
+    uint32_t ring_lo = ring_lo0, fbar = full_bar(0);
+    constexpr uint32_t kALo = kABytes >> 4, kStageLo = Cfg::kStageBytes >> 4, kChunkLo = kChunkBytes >> 4, kEmptyOff = 8u * kMS;
+    auto advance = [&] {
+      ring_lo += kStageLo; fbar += 8u;
+      if (++stage == kStages) { stage = 0; phase ^= 1u; ring_lo = ring_lo0; fbar = full_bar(0); }
+    };
     uint32_t gp = 0;  // 128-channel passes issued so far: selects the acc2 buffer and its phase
     [[maybe_unused]] int g = 0;
     for (int st = 0; st <= my_tiles; ++st) {
@@ -284,34 +296,35 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         }
         const uint32_t d_tmem = tmem_base + Cfg::kAcc2Col + b * 128;
         FT(lane == 0 && g < 256, 256 + g);
-        mbar_wait(full_bar(stage), phase);
+        mbar_wait(fbar, phase);
         tc_fence_after();
         FT(lane == 0 && g < 256, 512 + g);
         if (elect_one()) {
           if constexpr (Cfg::kPackW3) {
 #pragma unroll
             for (int kk = 0; kk < 2; ++kk) {  // both K blocks of the pass sit in this stage
-              const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kk * kChunkBytes, 128, 2);
-              const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes + kk * kABytes, 128, 2);
 #pragma unroll
-              for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kk | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < 4; ++k)
+                umma_bf16_ss(d_tmem, umma_desc_join(mid_lo + kk * kChunkLo + 2u * k), umma_desc_join(ring_lo + kk * kALo + 2u * k),
+                             idesc2, (kk | k) != 0 ? 1u : 0u);
             }
           } else {
-            const uint64_t adesc = umma_smem_desc_kmajor(mid_base + kb * kChunkBytes, 128, 2);
-            const uint64_t bdesc = umma_smem_desc_kmajor(smem_base + stage * Cfg::kStageBytes, 128, 2);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc2, (kb | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < 4; ++k)
+              umma_bf16_ss(d_tmem, umma_desc_join(mid_lo + kb * kChunkLo + 2u * k), umma_desc_join(ring_lo + 2u * k), idesc2,
+                           (kb | k) != 0 ? 1u : 0u);
           }
-          umma_commit(empty_bar(stage));
+          umma_commit(fbar + kEmptyOff);
           if (kb == Cfg::kUnitsPerPass - 1) umma_commit(acc2_full(b));
           if (u == nu - 1) umma_commit(mid_empty);  // `mid` may be overwritten once these MMAs retire
         }
         __syncwarp();
         FT(lane == 0 && g < 256, 768 + g); ++g;
-        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        advance();
         if (kb == Cfg::kUnitsPerPass - 1) ++gp;
       };
       int u = 0;
+      int next_at = fused_unit_slot(0, nk, nu, p.interleave);  // the K block after which unit u goes (0: at the end)
       const uint32_t a = st & 1u;
       const uint32_t d_tmem1 = tmem_base + a * N1;
       if (nk) {  // first GEMM of tile st
@@ -322,22 +335,21 @@ bottleneck_tail_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       }
       for (int kb = 0; kb < nk; ++kb) {
         FT(lane == 0 && g < 256, 256 + g);
-        mbar_wait(full_bar(stage), phase);
+        mbar_wait(fbar, phase);
         tc_fence_after();
         FT(lane == 0 && g < 256, 512 + g);
-        const uint32_t a_addr = smem_base + stage * Cfg::kStageBytes;
         if (elect_one()) {
-          const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
-          const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem1, adesc + 2u * k, bdesc + 2u * k, idesc1, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(empty_bar(stage));
+          for (int k = 0; k < 4; ++k)
+            umma_bf16_ss(d_tmem1, umma_desc_join(ring_lo + 2u * k), umma_desc_join(ring_lo + kALo + 2u * k), idesc1,
+                         (kb | k) != 0 ? 1u : 0u);
+          umma_commit(fbar + kEmptyOff);
           if (kb == nk - 1) umma_commit(acc1_full(a));
         }
         __syncwarp();
         FT(lane == 0 && g < 256, 768 + g); ++g;
-        if (++stage == kStages) { stage = 0; phase ^= 1u; }
-        while (u < nu && fused_unit_slot(u, nk, nu, p.interleave) == kb + 1) unit(u++);
+        advance();
+        while (u < nu && next_at == kb + 1) { unit(u++); next_at = fused_unit_slot(u, nk, nu, p.interleave); }
       }
       while (u < nu) unit(u++);
     }
@@ -497,7 +509,9 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   FusedParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cmid = Cmid; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0; q.reverse = 0;
-  q.interleave = 0;
+  // measured (B200, micro-batch 64, launch by launch): Cmid 128 (layer2, four passes per tile) 46.0 -> 43.5 us per launch
+  // with the passes interleaved, Cmid 64 (layer1, two passes, six stages) 59 -> 63 us: interleaved only where it pays
+  q.interleave = Cmid == 128 ? 1 : 0;
   q.dbg = nullptr;
   if (const char* v = getenv("AI4E_B200_FUSED_INTERLEAVE")) q.interleave = atoi(v);  // 0 plain order, 1 / 2 interleaved (see fused_unit_slot)
   q.bias2 = bias2; q.bias3 = bias3;

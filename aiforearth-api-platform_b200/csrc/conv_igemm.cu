@@ -333,6 +333,11 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       uint32_t phase = 0;
       uint32_t it = 0;
       [[maybe_unused]] int mtrace = 0;
+      // generic mode: descriptor low word and full-barrier address of the current stage, advanced with it
+      // (umma_desc_join in common.cuh: three adds per MMA instead of rebuilding both descriptors from `stage`)
+      const uint32_t ring_lo0 = umma_desc_lo(smem_base);
+      [[maybe_unused]] uint32_t ring_lo = ring_lo0, fbar = full_bar(0);
+      constexpr uint32_t kALo = kABytes >> 4, kStageLo = Cfg::kStageBytes >> 4, kEmptyOff = 8u * kMS;
       if constexpr (kRows) mbar_wait(b_full_bar, 0);
       for (int tile = unit; tile < p.num_tiles; tile += unit_stride, ++it) {
         const uint32_t acc = it & 1u;
@@ -361,7 +366,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
         for (int kb = 0; !kRows && kb < p.num_k_blocks; ++kb) {
-          mbar_wait(full_bar(stage), phase);
+          mbar_wait(kStem ? full_bar(stage) : fbar, phase);
           // (the two trace stores cost ~140 cycles per K block: traced periods overstate the loop)
           AI4E_TRACE(lane == 0 && mtrace < 192, 384 + mtrace);  // data seen
           tc_fence_after();
@@ -377,23 +382,24 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
               }
             } else {
-              const uint64_t adesc = umma_smem_desc_kmajor(a_addr, 128, 2);
-              const uint64_t bdesc = umma_smem_desc_kmajor(a_addr + kABytes, 128, 2);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 // advancing 16 bf16 = 32 bytes along K inside the 128-byte swizzle row:
                 // +2 in the (addr >> 4) start-address field
-                if constexpr (kPair) umma_bf16_ss_pair(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
-                else umma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                const uint64_t adesc = umma_desc_join(ring_lo + 2u * k), bdesc = umma_desc_join(ring_lo + kALo + 2u * k);
+                if constexpr (kPair) umma_bf16_ss_pair(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                else umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
               }
             }
             // smem stage reusable once these MMAs retire (pair: in both CTAs)
-            if constexpr (kPair) umma_commit_pair(empty_bar(stage));
-            else umma_commit(empty_bar(stage));
+            const uint32_t ebar = kStem ? empty_bar(stage) : fbar + kEmptyOff;
+            if constexpr (kPair) umma_commit_pair(ebar);
+            else umma_commit(ebar);
           }
           __syncwarp();
           AI4E_TRACE(lane == 0 && mtrace < 192, 576 + mtrace); ++mtrace;  // MMAs issued
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          ring_lo += kStageLo; fbar += 8u;
+          if (++stage == kStages) { stage = 0; phase ^= 1u; ring_lo = ring_lo0; fbar = full_bar(0); }
         }
         if (elect_one()) {  // accumulator complete -> epilogue (pair: of both CTAs)
           if constexpr (kPair) umma_commit_pair(tmem_full_bar(acc));
