@@ -509,8 +509,9 @@ int fused_tail_make_plan(FusedPlan* plan, const void* in, int N, int H, int W, i
   FusedParams& q = plan->prm;
   q.M = 0; q.P = P; q.Q = Q; q.PQ = P * Q; q.Cmid = Cmid; q.Cout = Cout; q.S = S; q.stride = stride; q.pad = pad;
   q.cin_blocks = Cin / kBlockK; q.num_k_blocks = R * S * q.cin_blocks; q.num_tiles = 0; q.reverse = 0;
-  // measured (B200, micro-batch 64, launch by launch): Cmid 128 (layer2, four passes per tile) 46.0 -> 43.5 us per launch
-  // with the passes interleaved, Cmid 64 (layer1, two passes, six stages) 59 -> 63 us: interleaved only where it pays
+  // measured (B200, micro-batch 64, launch by launch, profiles/r02_k_mma_loop_ab.json): the four Cmid 128 tails of layer2
+  // (four passes per tile) 184 -> 174 us with the passes interleaved, the three Cmid 64 tails of layer1 (two passes, six
+  // stages) 178 -> 190 us: interleaved only where it pays
   q.interleave = Cmid == 128 ? 1 : 0;
   q.dbg = nullptr;
   if (const char* v = getenv("AI4E_B200_FUSED_INTERLEAVE")) q.interleave = atoi(v);  // 0 plain order, 1 / 2 interleaved (see fused_unit_slot)
