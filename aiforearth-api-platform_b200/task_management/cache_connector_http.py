@@ -1,4 +1,5 @@
-"""HTTP facade of the platform's two cache-connector functions over a `LocalTaskStore`, so that a
+"""HTTP facade of the platform's two cache-connector functions over a `LocalTaskStore` (state in this process) or a
+`RedisTaskStore` (state in a Redis-protocol store, the reference's keys), so that a
 container (this repo's client over `requests`, or the reference's own aiohttp client, unmodified)
 can be driven against the real wire contract without Azure:
 
@@ -9,7 +10,7 @@ Contract restated from the reference (citations relative to /root/reference):
   ProcessManager/CacheManager/CacheConnectorUpsert.cs:40-41 (POST, route = function name), :57-74 (empty body
   -> 400), :60-67 (array body -> first element), :76-82 (undeserialisable body -> 500), :212 (200 + the
   serialised task); ProcessManager/CacheManager/CacheConnectorGet.cs:26-27 (GET), :33-37 (query key
-  `taskId`), :56-66 (200 + JSON, 204 when unknown).  The state machine itself is `LocalTaskStore`.
+  `taskId`), :56-66 (200 + JSON, 204 when unknown).  The state machine itself is `LocalTaskStore` / `RedisTaskStore`.
 
     store = LocalTaskStore()
     with serve(store) as srv:                       # a thread with a Werkzeug server on 127.0.0.1
@@ -85,3 +86,31 @@ def serve(store: LocalTaskStore | None = None, host: str = "127.0.0.1", port: in
     thread = threading.Thread(target=server.serve_forever, daemon=True, name="ai4e-cache-connector")
     thread.start()
     return _Served(facade, server, thread)
+
+
+def main(argv=None):
+    """`python -m task_management.cache_connector_http [--port 7071] [--redis host:port]`: the two functions as a
+    process of their own, state in this process or in a Redis-protocol store (the reference's keys)."""
+    import argparse
+    import time
+    ap = argparse.ArgumentParser(description=main.__doc__)
+    ap.add_argument("--host", default="127.0.0.1")
+    ap.add_argument("--port", type=int, default=7071)
+    ap.add_argument("--redis", default=None, help="host:port of a Redis-protocol store; default: in-process state")
+    a = ap.parse_args(argv)
+    store = None
+    if a.redis:
+        from task_management.redis_task_store import RedisTaskStore
+        host, _, port = a.redis.rpartition(":")
+        store = RedisTaskStore(host or "127.0.0.1", int(port))
+    with serve(store, a.host, a.port) as srv:
+        print(f"CACHE_CONNECTOR_UPSERT_URI={srv.upsert_uri}\nCACHE_CONNECTOR_GET_URI={srv.get_uri}", flush=True)
+        try:
+            while True:
+                time.sleep(3600)
+        except KeyboardInterrupt:
+            pass
+
+
+if __name__ == "__main__":
+    main()

@@ -28,6 +28,29 @@ BACKEND_STATUSES = ("created", "running", "completed", "failed")
 ORIG_SUFFIX = "_ORIG"
 
 
+def prepare_upsert(task, path_cache: dict):
+    """what CacheConnectorUpsert does to the request before it touches the store (:92-127): new GUID for an empty
+    TaskId, Timestamp = UTC now, Body stripped from what is stored, EndpointPath from the Endpoint URI.
+    -> (task to store, the request's body, epoch seconds for the sorted-set score), or None for a task the
+    upstream function would throw on (no Endpoint / BackendStatus: its catch answers 500)."""
+    if not isinstance(task, dict) or not task.get("Endpoint") or not task.get("BackendStatus"):
+        return None  # upstream: Uri(null) / BackendStatus.Equals on null throw inside the try (:130-142, :204-210)
+    task = dict(task)
+    task_body = task.get("Body")
+    if not task.get("TaskId"):
+        task["TaskId"] = str(uuid.uuid4())
+    task["Timestamp"] = datetime.datetime.now(datetime.timezone.utc).strftime("%m/%d/%Y %H:%M:%S")
+    task["Body"] = None
+    task.setdefault("Status", None)
+    task.setdefault("PublishToGrid", False)
+    endpoint = task["Endpoint"]
+    path = path_cache.get(endpoint)
+    if path is None:
+        path = path_cache[endpoint] = urlparse(endpoint).path
+    task["EndpointPath"] = path  # a public getter of APITask, so the serialiser emits it (Classes/APITask.cs:20-27)
+    return task, task_body, int(time.time())
+
+
 class LocalTaskStore:
     def __init__(self, publisher=None):
         self._lock = threading.Lock()
@@ -59,24 +82,11 @@ class LocalTaskStore:
         """the same state machine for a caller in this process that already holds the task as a dict (no
         JSON round trip): -> (status, stored task dict)."""
         self.upserts += 1
-        if not isinstance(task, dict) or not task.get("Endpoint") or not task.get("BackendStatus"):
-            return 500, None  # upstream: Uri(null) / BackendStatus.Equals on null throw inside the try (:130-142, :204-210)
-        task = dict(task)
-        task_body = task.get("Body")
-        if not task.get("TaskId"):
-            task["TaskId"] = str(uuid.uuid4())
-        task["Timestamp"] = datetime.datetime.now(datetime.timezone.utc).strftime("%m/%d/%Y %H:%M:%S")
-        task["Body"] = None
-        task.setdefault("Status", None)
-        task.setdefault("PublishToGrid", False)
-        endpoint = task["Endpoint"]
-        path = self._paths.get(endpoint)
-        if path is None:
-            path = self._paths[endpoint] = urlparse(endpoint).path
-        task["EndpointPath"] = path  # a public getter of APITask, so the serialiser emits it (Classes/APITask.cs:20-27)
-        status = task["BackendStatus"]
-        tid = task["TaskId"]
-        now = int(time.time())
+        prepared = prepare_upsert(task, self._paths)
+        if prepared is None:
+            return 500, None
+        task, task_body, now = prepared
+        path, status, tid = task["EndpointPath"], task["BackendStatus"], task["TaskId"]
         publish = bool(task.get("PublishToGrid"))
         with self._lock:
             self.tasks[tid] = task

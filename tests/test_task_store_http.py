@@ -19,10 +19,19 @@ REF_CLIENT = "/root/reference/APIs/1.0/Common/task_management/distributed_api_ta
 ENDPOINT = "http://10.0.0.7/v1/org/classify"
 
 
-@pytest.fixture()
-def served(monkeypatch):
-    store = LocalTaskStore()
-    with serve(store) as srv:
+@pytest.fixture(params=["memory", "redis"])
+def served(monkeypatch, request):
+    """the facade over the in-process store and over the Redis-protocol store (tests/fake_redis.py on a socket)"""
+    import contextlib
+    with contextlib.ExitStack() as stack:
+        if request.param == "redis":
+            from task_management.redis_task_store import RedisTaskStore
+            from tests.fake_redis import FakeRedis
+            r = stack.enter_context(FakeRedis())
+            store = RedisTaskStore(r.host, r.port)
+        else:
+            store = LocalTaskStore()
+        srv = stack.enter_context(serve(store))
         monkeypatch.setenv("CACHE_CONNECTOR_UPSERT_URI", srv.upsert_uri)
         monkeypatch.setenv("CACHE_CONNECTOR_GET_URI", srv.get_uri)
         monkeypatch.delenv("AI4E_TASK_STORE", raising=False)
