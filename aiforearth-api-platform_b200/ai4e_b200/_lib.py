@@ -114,6 +114,9 @@ SIGNATURES = {
     "ai4e_engine_debug_inject_fault": (_i, [_vp, _i]),
     "ai4e_pool_submit_many": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "ai4e_pool_submit_batch": (_i, [_vp, _vp, _i, _i, _i, _i, _u64p]),
+    "ai4e_pool_openloop": (_i, [_vp, _vp, _i, _i, _i, _i, C.c_double, C.c_double, _i, C.c_uint64, _vp, C.c_int64,
+                                C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_double),
+                                C.POINTER(C.c_double)]),
     "ai4e_pool_submit_tile": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _i, C.POINTER(C.c_int32)]),
     "ai4e_pool_submit_tile_summary": (_i, [_vp, _vp, _i, _i, _i, _i, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_int32)]),
     "ai4e_pool_wait_tile_summary": (_i, [_vp, C.c_uint64, _vp, _vp, _i, _vp, _vp, C.POINTER(C.c_int32)]),

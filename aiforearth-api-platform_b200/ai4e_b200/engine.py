@@ -547,6 +547,26 @@ class Pool(_Base):
                                            self.max_batch, self.max_wait_us, C.byref(h)))
         self._h = h
 
+    def openloop(self, images_u8: np.ndarray, rate_per_s: float, seconds: float, feeders: int = 4, seed: int = 0) -> dict:
+        """Measurement aid (BASELINE.json configs[4]): Poisson arrivals at `rate_per_s` for `seconds`, generated by
+        `feeders` native threads through the pool's own submit_many / poll (no interpreter on the path; nobody else
+        may poll meanwhile).  images_u8: dense [N, H, W, C], cycled.  -> offered / completed / failed counts, achieved
+        rate, latency percentiles (scheduled arrival -> result announced, ms) and how late the feeders ran."""
+        a = np.ascontiguousarray(images_u8)
+        assert a.dtype == np.uint8 and a.ndim == 4
+        cap = int(rate_per_s * seconds) + 1
+        lat = np.empty(cap, np.float32)
+        offered, completed, failed = C.c_int64(), C.c_int64(), C.c_int64()
+        span, late = C.c_double(), C.c_double()
+        L.check(self._lib.ai4e_pool_openloop(self._h, _vp(a), a.shape[0], a.shape[1], a.shape[2], a.shape[3], float(rate_per_s),
+                                             float(seconds), int(feeders), int(seed), _vp(lat), cap, C.byref(offered),
+                                             C.byref(completed), C.byref(failed), C.byref(span), C.byref(late)))
+        ok = np.sort(lat[:offered.value][lat[:offered.value] >= 0])
+        q = lambda f: float(ok[int((len(ok) - 1) * f)]) if len(ok) else None  # noqa: E731
+        return {"offered_per_s": float(rate_per_s), "tasks": offered.value, "completed": completed.value, "failed": failed.value,
+                "achieved_per_s": completed.value / span.value if span.value > 0 else 0.0, "p50_ms": q(0.50), "p90_ms": q(0.90),
+                "p99_ms": q(0.99), "max_ms": q(1.0), "feeder_max_lateness_ms": late.value, "feeders": int(feeders)}
+
     def submit(self, image, tag: int = 0) -> int:
         a = _u8_hwc(image)
         t = C.c_uint64()

@@ -438,6 +438,15 @@ AI4E_API int ai4e_pool_submit_tile_summary(ai4e_pool* p, const uint8_t* h_tile, 
                                            int row_stride, int chip, uint64_t* out_tile_ticket, int* out_chips);
 AI4E_API int ai4e_pool_wait_tile_summary(ai4e_pool* p, uint64_t tile_ticket, int32_t* labels, float* label_prob,
                                          int capacity_chips, uint32_t* hist, uint64_t* mass_q32, int* out_chips);
+/* Measurement aid, no reference counterpart (BASELINE.json configs[4]: Poisson arrivals at a fraction of peak): `feeders`
+ * native threads offer `rate_per_s` arrivals for `seconds` through ai4e_pool_submit_many (every arrival of a feeder that
+ * is due per call, notify) and one thread drains ai4e_pool_poll - nobody else may poll this pool meanwhile.  h_images:
+ * n_images dense h x w x c images, cycled.  out_latency_ms[i] = announced - SCHEDULED time of arrival i in ms (-1: not
+ * completed or failed), i < *out_offered <= capacity; *out_span_s = when the last result arrived. */
+AI4E_API int ai4e_pool_openloop(ai4e_pool* p, const uint8_t* h_images, int n_images, int h, int w, int c, double rate_per_s,
+                                double seconds, int feeders, uint64_t seed, float* out_latency_ms, int64_t capacity,
+                                int64_t* out_offered, int64_t* out_completed, int64_t* out_failed, double* out_span_s,
+                                double* out_feeder_lateness_ms);
 AI4E_API int ai4e_pool_wait_many(ai4e_pool* p, const uint64_t* tickets, int n, int32_t* top_idx5, float* top_prob5);
 AI4E_API int ai4e_pool_poll(ai4e_pool* p, int capacity, int64_t timeout_us, uint64_t* tickets, uint64_t* tags,
                    int32_t* status, int32_t* top_idx5, float* top_prob5, int* out_n);

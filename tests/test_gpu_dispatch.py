@@ -198,6 +198,21 @@ def test_tile_submit_pageable_pinned_and_pool():
         assert np.array_equal(idx3, want)
 
 
+def test_native_open_loop_generator_completes_every_arrival():
+    """ai4e_pool_openloop (measurement aid): every scheduled arrival is submitted, announced once and timed."""
+    from ai4e_b200.engine import Pool
+    g, imgs = util.load_golden("resnet18")
+    with Pool(util.program_for("resnet18"), devices=[0, 0], max_batch=8, max_wait_us=500) as p:
+        r = p.openloop(np.ascontiguousarray(imgs[:16]), rate_per_s=3000.0, seconds=0.4, feeders=3, seed=5)
+        assert r["tasks"] == 1200 and r["completed"] == 1200 and r["failed"] == 0
+        assert 0.0 < r["p50_ms"] <= r["p99_ms"] <= r["max_ms"] < 2000.0
+        assert 2000.0 < r["achieved_per_s"] < 4000.0
+        assert sum(st["images"] for st in p.stats()) == 1200
+        # the pool is usable afterwards and its queue is empty
+        assert np.array_equal(p.classify(imgs[0])[0], g["top5_idx"][0])
+        assert len(p.poll(8, 0.0)[0]) == 0
+
+
 # ------------------------------------------------------------------ pool: bulk entry points, fault drill
 def test_pool_bulk_entry_points():
     import torch
