@@ -8,7 +8,8 @@
 using namespace ai4e;
 
 // variant bits: 1 = wait on an (already complete) mbarrier per unit, 2 = tcgen05.fence::after_thread_sync per unit,
-// 4 = commit per unit (else one at the end), 8 = two ALU-busy warps share the MMA warp's scheduler
+// 4 = commit per unit (else one at the end), 8 = two ALU-busy warps share the MMA warp's scheduler,
+// 16 = the wait is taken by the elected thread between its third and fourth MMA (for the next unit)
 template <int N, int kVariant>
 __global__ void __launch_bounds__(384, 1) probe(int units, long long* out, float* sink) {
   extern __shared__ uint8_t smem_raw[];
@@ -34,12 +35,19 @@ __global__ void __launch_bounds__(384, 1) probe(int units, long long* out, float
     constexpr uint32_t idesc = umma_idesc_bf16_f32(128, N);
     const long long t0 = clock64();
     for (int u = 0; u < units; ++u) {
-      if (kVariant & 1) mbar_wait(smem_u32(&bar_ready), 0);
+      if ((kVariant & 1) && !(kVariant & 16)) mbar_wait(smem_u32(&bar_ready), 0);
       if (kVariant & 2) tc_fence_after();
       const uint32_t d = tm + (u & 1) * N;
       if (elect_one()) {
+        if (kVariant & 16) {  // the elected thread takes the NEXT unit's wait between its third and fourth MMA
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_bf16_ss(d, umma_desc_join(a_lo + 2u * k), umma_desc_join(b_lo + 2u * k), idesc, k ? 1u : 0u);
+          for (int k = 0; k < 3; ++k) umma_bf16_ss(d, umma_desc_join(a_lo + 2u * k), umma_desc_join(b_lo + 2u * k), idesc, k ? 1u : 0u);
+          mbar_wait(smem_u32(&bar_ready), 0);
+          umma_bf16_ss(d, umma_desc_join(a_lo + 6u), umma_desc_join(b_lo + 6u), idesc, 1u);
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16_ss(d, umma_desc_join(a_lo + 2u * k), umma_desc_join(b_lo + 2u * k), idesc, k ? 1u : 0u);
+        }
         if (kVariant & 4) umma_commit(smem_u32(&bar_unit));
       }
       __syncwarp();
@@ -83,6 +91,8 @@ void all() {
   run<N, 5>("... + commit + barrier wait (complete)");
   run<N, 7>("... + commit + wait + tcgen05 fence  (= the kernels' loop)");
   run<N, 15>("the kernels' loop next to two ALU-busy warps");
+  run<N, 23>("next unit's wait by the elected thread before its last MMA");
+  run<N, 31>("... next to two ALU-busy warps");
 }
 int main() {
   all<64>(); all<128>(); all<256>();
