@@ -34,6 +34,8 @@ Printed keys (one JSON line, rank 0):
   async_path    (N = 1) BASELINE.json configs[2] in small: tasks through the drop-in APIService
                 async endpoint, in-process task store, p50/p99 AddTask -> CompleteTask
                 (tools/async_bench.py; `--gpus N` there runs one Pool over N GPUs in one process)
+  open_loop     (N = 1) p50 / p99 TASK latency under Poisson arrivals at 50 % and 80 % of async_path.native
+                (BASELINE.json configs[4]; native load generator, tools/openloop_bench.py --native runs it on N GPUs)
   cpu_baseline  the CPU oracle (torchvision fp32, preprocessing included) on the host cores,
                 bounded sample, rank 0 at N=1 only
 `--impl reference` times that CPU path alone (the reference's own arithmetic lives in a
@@ -473,6 +475,20 @@ def main():
             out["async_path"]["shell_only"] = async_bench.measure(1, "shell_only", min(2.0, args.async_seconds), 8)
         except Exception as err:  # noqa: BLE001 - the headline numbers above stand on their own
             out["async_path"] = {"error": repr(err)}
+        # the latency half of the metric (p50 / p99 TASK latency, BASELINE.json configs[4]): Poisson arrivals, one image per
+        # arrival, at 50 % and 80 % of the closed-loop rate just measured, generated by native threads through the pool's
+        # own submit_many / poll (ai4e_pool_openloop); latency = scheduled arrival -> result announced
+        try:
+            from ai4e_b200.engine import Pool
+            peak = float(out["async_path"]["native"]["images_per_s"])
+            imgs = np.ascontiguousarray(pool_np[:4].reshape(-1, HW, HW, IN_C))  # 256 distinct images, cycled
+            with Pool(prog, devices=[local_rank], max_batch=B, max_wait_us=2000) as pool:
+                pool.openloop(imgs, 0.2 * peak, 0.5, feeders=4, seed=1)  # warm-up
+                out["open_loop"] = {"peak_per_s": peak, "of": "one Pool on this GPU, max_wait_us 2000, 4 native feeder threads",
+                                    **{f"load_{int(f * 100)}": pool.openloop(imgs, f * peak, min(3.0, args.async_seconds), feeders=4, seed=int(f * 100))
+                                       for f in (0.5, 0.8)}}
+        except Exception as err:  # noqa: BLE001
+            out["open_loop"] = {"error": repr(err)}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
