@@ -331,7 +331,7 @@ class _Base:
         return self.wait(self.submit(image), want_logits)
 
     def submit_encoded(self, data: bytes, tag: int = 0) -> int:
-        """one encoded image (baseline / progressive JPEG or 8-bit PNG, sniffed from its first bytes) -> ticket.
+        """one encoded image (baseline / progressive JPEG or PNG, sniffed from its first bytes) -> ticket.
         The sequential part of the decode (Huffman / inflate + un-filter) runs on this thread with
         the GIL released.  Unsupported payloads raise Ai4eError(ERR_UNSUPPORTED) and queue nothing."""
         buf = (C.c_uint8 * len(data)).from_buffer_copy(data)

@@ -156,15 +156,17 @@ AI4E_API int ai4e_jpeg_decode(const uint8_t* jpeg, uint64_t len, uint8_t* d_rgb_
 /* PNG payloads.  PNG is lossless: chunk walk, zlib inflate and the scan-line filters
  * run on the calling thread's host core and there is no arithmetic for the GPU; the pixels then take
  * the ordinary submit path.  Output = `Image.open(BytesIO(data)).convert("RGB")` of Pillow, bit for
- * bit (the decode inside the callback at APIs/1.0/base-py/ai4e_service.py:203).  8-bit grey / RGB /
- * palette, with or without alpha, non-interlaced; anything else -> AI4E_ERR_UNSUPPORTED.
+ * bit (the decode inside the callback at APIs/1.0/base-py/ai4e_service.py:203).  Every image type of the PNG
+ * specification: grey (1 - 16 bits), RGB, palette (1 - 8 bits), with or without alpha, 8 or 16 bits per sample,
+ * plain or Adam7-interlaced; 16-bit samples are reduced the way Pillow reduces them.  Anything else ->
+ * AI4E_ERR_UNSUPPORTED.
  * h_rgb_hwc == NULL only reports the size. */
 AI4E_API int ai4e_png_decode(const uint8_t* png, uint64_t len, uint8_t* h_rgb_hwc, uint64_t capacity_bytes,
                              int32_t* out_height, int32_t* out_width);
 
 /* Admission check for an encoded payload, host only, headers only: AI4E_OK with the format and size
- * when the engine can decode it, AI4E_ERR_UNSUPPORTED otherwise (arithmetic-coded / CMYK JPEG, 16-bit or
- * interlaced PNG, any other format).  A request_processing_function calls it while the request is
+ * when the engine can decode it, AI4E_ERR_UNSUPPORTED otherwise (arithmetic-coded / CMYK JPEG, a file that is
+ * neither JPEG nor PNG).  A request_processing_function calls it while the request is
  * still open and answers 415 instead of accepting a task that could only fail - the content gate
  * of APIs/1.0/base-py/ai4e_service.py:127-129 only looks at the MIME type. */
 #define AI4E_IMAGE_UNKNOWN 0

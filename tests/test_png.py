@@ -21,7 +21,7 @@ def _name(p):
 
 def test_fixtures_cover_the_supported_flavours():
     names = " ".join(_name(p) for p in FIXTURES)
-    for flavour in ("rgb_", "rgba_", "gray_", "graya_", "palette_"):
+    for flavour in ("rgb_", "rgba_", "gray_", "graya_", "palette_", "adam7_", "rgb16_", "gray16_", "gray1_", "gray2_", "palette4_", "palette1_"):
         assert flavour in names
 
 
@@ -31,6 +31,62 @@ def test_host_png_decoder_matches_pillow_fixture(path):
     got = ops.png_decode(open(path, "rb").read())
     want = np.load(path[:-4] + ".npy")
     assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_every_png_image_type_plain_and_interlaced_matches_live_pillow():
+    """all fifteen colour type / bit depth combinations of the specification, plain and Adam7, sizes that leave some of
+    the seven passes empty, a random filter type on every line, IDAT cut into pieces, palettes shorter than the index
+    range, 16-bit grey around Pillow's clip at 255 - written by tests/png_writer.py, expected pixels from Pillow"""
+    Image = pytest.importorskip("PIL.Image")
+    from ai4e_b200 import ops
+    from tests import png_writer as pw
+    rng = np.random.default_rng(3)
+    n = 0
+    for ctype, depth in pw.VALID:
+        for interlace in (False, True):
+            for h, w in ((1, 1), (2, 3), (7, 5), (8, 8), (5, 1), (1, 9), (19, 33)):
+                samples, pal = pw.random_image(rng, h, w, depth, ctype)
+                data = pw.encode(samples, depth, ctype, interlace, pal, seed=n, idat_split=(97 if n % 3 == 0 else 0))
+                want = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+                got = ops.png_decode(data)
+                assert got.shape == want.shape and np.array_equal(got, want), (ctype, depth, interlace, h, w)
+                n += 1
+    assert n == 15 * 2 * 7
+
+
+def test_host_png_decoder_survives_mutated_streams():
+    """byte edits, cuts and deletions behind the IHDR chunk of every fixture: decoded or refused, never a crash and never
+    a write outside the output (a canary follows it)"""
+    import ctypes as C
+    from ai4e_b200 import _lib as L
+    lib = L.load()
+    rng = np.random.default_rng(5)
+    small = [open(p, "rb").read() for p in FIXTURES if os.path.getsize(p) < 6000]
+    decoded = refused = 0
+    for it in range(1500):
+        d = bytearray(small[it % len(small)])
+        kind = it % 3
+        lo = 33  # keep the header: a mutated IHDR only asks for another (possibly huge) size
+        if kind == 0:
+            for _ in range(int(rng.integers(1, 5))):
+                d[int(rng.integers(lo, len(d)))] = int(rng.integers(256))
+        elif kind == 1:
+            d = d[:int(rng.integers(lo, len(d)))]
+        else:
+            i = int(rng.integers(lo, len(d)))
+            del d[i:i + int(rng.integers(1, 30))]
+        buf = (C.c_uint8 * len(d)).from_buffer_copy(bytes(d))
+        h, w = C.c_int32(), C.c_int32()
+        if lib.ai4e_png_decode(buf, len(d), None, 0, C.byref(h), C.byref(w)) != 0:
+            refused += 1
+            continue
+        n = h.value * w.value * 3
+        out = np.full(n + 64, 0x5A, np.uint8)
+        rc = lib.ai4e_png_decode(buf, len(d), out.ctypes.data_as(C.c_void_p), n, C.byref(h), C.byref(w))
+        assert np.all(out[n:] == 0x5A)
+        decoded += rc == 0
+        refused += rc != 0
+    assert decoded > 30 and refused > 300
 
 
 def test_host_png_decoder_matches_live_pillow():
@@ -57,7 +113,7 @@ def test_probe_and_refusals():
     assert require_decodable(jpg) == ("jpeg", 64, 64)
     prog = open(os.path.join(util.GOLDEN, "jpeg", "prog_q75_422_50x70.jpg"), "rb").read()
     assert ops.image_probe(prog) == ("jpeg", 50, 70)    # progressive files are admitted (and decoded: test_jpeg.py)
-    bad16 = open(os.path.join(PNG_DIR, "unsupported_gray16_8x8.png"), "rb").read()
+    bad16 = open(os.path.join(PNG_DIR, "unsupported_rgb4_8x8.png"), "rb").read()   # 4-bit RGB: not a PNG image type
     for payload in (bad16, b"GIF89a" + b"\0" * 64, b""):
         with pytest.raises(Ai4eError) as ei:
             ops.image_probe(payload) if payload else ops.image_probe(b"\0")
