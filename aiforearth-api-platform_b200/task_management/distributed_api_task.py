@@ -20,6 +20,7 @@ Differences, all on the transport and none on the contract:
 from __future__ import annotations
 
 import datetime
+import time
 import json
 import queue
 import threading
@@ -133,9 +134,15 @@ class DistributedApiTaskManager:
             print("task store GET failed: " + str(e))
             return 599, None
 
-    @staticmethod
-    def _now():
-        return datetime.datetime.strftime(datetime.datetime.now(), "%Y-%m-%d %H:%M:%S")
+    _now_cache = (0, "")
+
+    @classmethod
+    def _now(cls):
+        """local "YYYY-MM-DD HH:MM:SS" (the reference's format, :33), formatted once per second"""
+        sec = int(time.time())
+        if cls._now_cache[0] != sec:
+            cls._now_cache = (sec, datetime.datetime.fromtimestamp(sec).strftime("%Y-%m-%d %H:%M:%S"))
+        return cls._now_cache[1]
 
     # ---- the reference's public methods
     def AddTask(self):

@@ -28,6 +28,19 @@ BACKEND_STATUSES = ("created", "running", "completed", "failed")
 ORIG_SUFFIX = "_ORIG"
 
 
+_stamp_cache = (0, "")
+
+
+def _utc_stamp(now: int) -> str:
+    """UTC "MM/DD/YYYY HH:MM:SS" of an epoch second; formatted once per second (strftime is a tenth of an upsert)"""
+    global _stamp_cache
+    sec, text = _stamp_cache
+    if sec != now:
+        text = datetime.datetime.fromtimestamp(now, datetime.timezone.utc).strftime("%m/%d/%Y %H:%M:%S")
+        _stamp_cache = (now, text)
+    return text
+
+
 def prepare_upsert(task, path_cache: dict):
     """what CacheConnectorUpsert does to the request before it touches the store (:92-127): new GUID for an empty
     TaskId, Timestamp = UTC now, Body stripped from what is stored, EndpointPath from the Endpoint URI.
@@ -39,7 +52,8 @@ def prepare_upsert(task, path_cache: dict):
     task_body = task.get("Body")
     if not task.get("TaskId"):
         task["TaskId"] = str(uuid.uuid4())
-    task["Timestamp"] = datetime.datetime.now(datetime.timezone.utc).strftime("%m/%d/%Y %H:%M:%S")
+    now = int(time.time())
+    task["Timestamp"] = _utc_stamp(now)
     task["Body"] = None
     task.setdefault("Status", None)
     task.setdefault("PublishToGrid", False)
@@ -48,7 +62,7 @@ def prepare_upsert(task, path_cache: dict):
     if path is None:
         path = path_cache[endpoint] = urlparse(endpoint).path
     task["EndpointPath"] = path  # a public getter of APITask, so the serialiser emits it (Classes/APITask.cs:20-27)
-    return task, task_body, int(time.time())
+    return task, task_body, now
 
 
 class LocalTaskStore:
