@@ -54,5 +54,23 @@ def main():
         print(name, len(data), "bytes", dec.shape)
 
 
+def transcoded():
+    """progressive files with the scan scripts OTHER encoders write (tests/jpeg_writer.py re-codes the coefficients of a
+    baseline fixture): Pillow must decode them to the pixels of the original, and so must this repo"""
+    from PIL import Image as _I
+    from tests import jpeg_writer as jw
+    for name, src, script, ri in (("progmoz_420_ragged_61x83", "q75_420_ragged_61x83", jw.SCRIPT_MOZ, 0),
+                                  ("progdeep_422_rst3_50x70", "q85_422_50x70", jw.SCRIPT_DEEP, 3),
+                                  ("progplain_444_33x47", "q95_444_33x47", jw.SCRIPT_PLAIN, 0),
+                                  ("proggray_rst3_45x37", "q92_gray_45x37", jw.SCRIPT_GRAY, 3)):
+        data = jw.transcode(open(os.path.join(OUT, src + ".jpg"), "rb").read(), script, ri)
+        open(os.path.join(OUT, name + ".jpg"), "wb").write(data)
+        dec = np.asarray(_I.open(io.BytesIO(data)).convert("RGB"))
+        assert np.array_equal(dec, np.load(os.path.join(OUT, src + ".npy")))  # same coefficients, same pixels
+        np.save(os.path.join(OUT, name + ".npy"), dec)
+        print(name, len(data), "bytes", dec.shape)
+
+
 if __name__ == "__main__":
     main()
+    transcoded()

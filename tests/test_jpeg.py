@@ -72,6 +72,35 @@ def test_oracle_matches_live_pillow_progressive():
         assert np.array_equal(jo.decode(buf.getvalue()), want), (h, w, kw)
 
 
+@pytest.mark.parametrize("src,script,restart", [
+    ("q75_420_ragged_61x83", "SCRIPT_MOZ", 0), ("q75_420_ragged_61x83", "SCRIPT_DEEP", 3), ("q85_422_50x70", "SCRIPT_DEEP", 0),
+    ("q85_422_50x70", "SCRIPT_PLAIN", 5), ("q95_444_33x47", "SCRIPT_MOZ", 3), ("q60_420_rst2_72x104", "SCRIPT_PLAIN", 0),
+    ("q92_gray_45x37", "SCRIPT_GRAY", 0), ("q92_gray_45x37", "SCRIPT_GRAY", 2)])
+def test_progressive_scan_scripts_of_other_encoders(src, script, restart):
+    """Pillow only writes libjpeg's default progression.  tests/jpeg_writer.py re-codes a baseline fixture's coefficients
+    with other legal scripts - spectral selection only, a mozjpeg-style script (bands split at 8, DC with one refinement),
+    three refinement rounds with DC scans of one and of two components - with and without restart markers: same
+    coefficients, so the pixels must be those of the original for Pillow (when importable), for the oracle, and the
+    library's host decoder must produce the oracle's coefficients."""
+    from ai4e_b200 import ops
+    from tests import jpeg_writer as jw
+    base = os.path.join(HERE, "golden", "jpeg", src)
+    data = jw.transcode(open(base + ".jpg", "rb").read(), getattr(jw, script), restart)
+    want = np.load(base + ".npy")
+    try:
+        from PIL import Image
+        assert np.array_equal(np.asarray(Image.open(io.BytesIO(data)).convert("RGB")), want)   # the writer itself
+    except ImportError:
+        pass
+    f = jo.parse(data)
+    assert f.progressive and f.scans == len(getattr(jw, script)) and f.restart_interval == restart
+    assert np.array_equal(jo.decode(data), want)
+    info, rec = ops.jpeg_entropy_decode(data)
+    for c, comp in enumerate(f.comps):
+        n = comp.blocks_w * comp.blocks_h * 64
+        assert np.array_equal(rec[info.coef_off[c]:info.coef_off[c] + n].reshape(comp.blocks_h, comp.blocks_w, 64), comp.coefs)
+
+
 def _cmyk_jpeg():
     PIL = pytest.importorskip("PIL.Image")
     buf = io.BytesIO()
