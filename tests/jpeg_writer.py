@@ -172,9 +172,16 @@ SCRIPT_GRAY = [((0,), 0, 0, 0, 2), ((0,), 1, 20, 0, 1), ((0,), 21, 63, 0, 1), ((
                ((0,), 1, 63, 1, 0)]
 
 
+SEQUENTIAL = "sequential, one scan per component"   # a `script` value: SOF0 with non-interleaved scans (jpegtran -scans style)
+
+
 def transcode(jpeg: bytes, script, restart_interval: int = 0) -> bytes:
-    """the same image (same quantised coefficients, tables, sampling) as a progressive file with this scan script"""
+    """the same image (same quantised coefficients, tables, sampling) as a progressive file with this scan script, or
+    (script = SEQUENTIAL) as a baseline file whose components come in scans of their own"""
     f = jo.parse(jpeg)
+    sequential = script == SEQUENTIAL
+    if sequential:
+        script = [((ci,), 0, 63, 0, 0) for ci in range(len(f.comps))]
     out = bytearray(b"\xff\xd8")
     for tq in sorted({c.tq for c in f.comps}):
         q = f.qt[tq]
@@ -187,7 +194,7 @@ def transcode(jpeg: bytes, script, restart_interval: int = 0) -> bytes:
     body = bytes([8]) + struct.pack(">HH", f.height, f.width) + bytes([len(f.comps)])
     for c in f.comps:
         body += bytes([c.cid, (c.h << 4) | c.v, c.tq])
-    out += _segment(0xC2, body)
+    out += _segment(0xC0 if sequential else 0xC2, body)
     out += _segment(0xC4, bytes([0x00]) + bytes(_DC_COUNTS) + bytes(_DC_SYMBOLS))
     out += _segment(0xC4, bytes([0x10]) + bytes(_AC_COUNTS) + bytes(_AC_SYMBOLS))
     if restart_interval:
@@ -202,7 +209,12 @@ def transcode(jpeg: bytes, script, restart_interval: int = 0) -> bytes:
 
         def block(ci, by, bx):
             blk = f.comps[ci].coefs[by, bx]
-            if ss == 0:
+            if sequential:                               # DC difference, then the block's AC run, closed by its own EOB
+                coder.dc_first(ci, blk)
+                coder.ss, coder.se = 1, 63
+                coder.ac_first(blk)
+                coder.emit_eobrun()
+            elif ss == 0:
                 coder.dc_first(ci, blk) if ah == 0 else coder.dc_refine(blk)
             else:
                 coder.ac_first(blk) if ah == 0 else coder.ac_refine(blk)

@@ -75,7 +75,8 @@ def test_oracle_matches_live_pillow_progressive():
 @pytest.mark.parametrize("src,script,restart", [
     ("q75_420_ragged_61x83", "SCRIPT_MOZ", 0), ("q75_420_ragged_61x83", "SCRIPT_DEEP", 3), ("q85_422_50x70", "SCRIPT_DEEP", 0),
     ("q85_422_50x70", "SCRIPT_PLAIN", 5), ("q95_444_33x47", "SCRIPT_MOZ", 3), ("q60_420_rst2_72x104", "SCRIPT_PLAIN", 0),
-    ("q92_gray_45x37", "SCRIPT_GRAY", 0), ("q92_gray_45x37", "SCRIPT_GRAY", 2)])
+    ("q92_gray_45x37", "SCRIPT_GRAY", 0), ("q92_gray_45x37", "SCRIPT_GRAY", 2),
+    ("q75_420_ragged_61x83", "SEQUENTIAL", 0), ("q85_422_50x70", "SEQUENTIAL", 4)])
 def test_progressive_scan_scripts_of_other_encoders(src, script, restart):
     """Pillow only writes libjpeg's default progression.  tests/jpeg_writer.py re-codes a baseline fixture's coefficients
     with other legal scripts - spectral selection only, a mozjpeg-style script (bands split at 8, DC with one refinement),
@@ -93,7 +94,11 @@ def test_progressive_scan_scripts_of_other_encoders(src, script, restart):
     except ImportError:
         pass
     f = jo.parse(data)
-    assert f.progressive and f.scans == len(getattr(jw, script)) and f.restart_interval == restart
+    if script == "SEQUENTIAL":       # a baseline file whose components come in scans of their own (jpegtran -scans style)
+        assert not f.progressive and f.scans == len(f.comps)
+    else:
+        assert f.progressive and f.scans == len(getattr(jw, script))
+    assert f.restart_interval == restart
     assert np.array_equal(jo.decode(data), want)
     info, rec = ops.jpeg_entropy_decode(data)
     for c, comp in enumerate(f.comps):
