@@ -146,8 +146,9 @@ struct ScanSpec {
 // does (DC first / refinement, AC first pass with end-of-band runs, AC refinement with correction bits).
 // A scan of one component walks that component's own blocks in raster order (without the padding to whole
 // MCUs); a scan of several walks the frame's MCUs.  Leaves br.p at (or before) the marker that ends it.
-int decode_scan(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, const int* td, const int* ta,
-                const std::vector<HuffTable>& dc, const std::vector<HuffTable>& ac, int16_t* record) {
+template <bool kProgressive>  // (the sequential loop, what nearly every file takes, compiled without the progressive branches)
+int decode_scan_t(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, const int* td, const int* ta,
+                  const std::vector<HuffTable>& dc, const std::vector<HuffTable>& ac, int16_t* record) {
   const int mcus_x = f.blocks_w[0] / f.h[0], mcus_y = f.blocks_h[0] / f.v[0];
   const bool inter = sc.ns > 1;
   const int c0 = sc.comp[0];
@@ -180,7 +181,7 @@ int decode_scan(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, cons
         for (int bx = 0; bx < nh; ++bx) {
           const int64_t brow = inter ? my * f.v[c] + by : mcu / bw0, bcol = inter ? mx * f.h[c] + bx : mcu % bw0;
           int16_t* blk = record + f.coef_off[c] + (brow * f.blocks_w[c] + bcol) * 64;
-          if (!sc.progressive) {
+          if (!kProgressive) {
             int s = decode_symbol(br, dc[td[c]]);
             AI4E_REQUIRE(s >= 0 && s <= 11, "jpeg: corrupt DC code");
             if (s) pred[c] += extend((int)getbits(br, s), s);
@@ -268,6 +269,11 @@ int decode_scan(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, cons
     }
   }
   return AI4E_OK;
+}
+
+int decode_scan(BitReader& br, const ai4e_jpeg_info& f, const ScanSpec& sc, const int* td, const int* ta,
+                const std::vector<HuffTable>& dc, const std::vector<HuffTable>& ac, int16_t* record) {
+  return sc.progressive ? decode_scan_t<true>(br, f, sc, td, ta, dc, ac, record) : decode_scan_t<false>(br, f, sc, td, ta, dc, ac, record);
 }
 
 }  // namespace
