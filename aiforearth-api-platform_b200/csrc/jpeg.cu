@@ -353,11 +353,11 @@ int jpeg_host_decode(const uint8_t* data, uint64_t len, int16_t* record, uint64_
       }
       for (int c = 0; c < out->components; ++c) {
         const int hr = out->hmax / out->h[c], vr = out->vmax / out->v[c];
-        const bool ok = out->hmax % out->h[c] == 0 && out->vmax % out->v[c] == 0 &&
-                        ((hr == 1 && vr == 1) || (hr == 2 && vr == 1) || (hr == 2 && vr == 2)) &&
-                        (c > 0 || (hr == 1 && vr == 1));
+        const bool ok = out->hmax % out->h[c] == 0 && out->vmax % out->v[c] == 0 && out->h[c] <= 4 && out->v[c] <= 2 &&
+                        (hr == 1 || hr == 2 || hr == 4) && (vr == 1 || vr == 2) && (c > 0 || (hr == 1 && vr == 1));
         if (!ok) {
-          set_last_error("jpeg: sampling %dx%d of component %d (max %dx%d) is not supported (4:4:4, 4:2:2, 4:2:0 are)",
+          set_last_error("jpeg: sampling %dx%d of component %d (max %dx%d) is not supported (horizontal ratios 1, 2, 4 and vertical "
+                         "ratios 1, 2 against a full-resolution first component are: 4:4:4, 4:2:2, 4:2:0, 4:4:0, 4:1:1, 4:1:0)",
                          out->h[c], out->v[c], c, out->hmax, out->vmax);
           return AI4E_ERR_UNSUPPORTED;
         }
@@ -558,12 +558,22 @@ jpeg_idct_kernel(const int16_t* __restrict__ records, uint8_t* __restrict__ plan
   }
 }
 
-// sample of component c at full-resolution pixel (y, x): jdsample.c fancy upsampling
+// sample of component c at full-resolution pixel (y, x): the upsampler jdsample.c's jinit_upsampler picks - the triangle
+// filters for 2:1 horizontally (alone or with 2:1 vertically) when the component is more than two samples wide and for
+// 2:1 vertically alone (libjpeg-turbo's h1v2), plain replication for everything else (ratio 4, narrow components)
 __device__ __forceinline__ int jpeg_sample(const uint8_t* __restrict__ pl, const JpegGeom& g, int c, int y, int x) {
   const int stride = g.blocks_w[c] * 8;
-  if (g.hr[c] == 1) return pl[(long long)y * stride + x];
-  const int cw = g.comp_w[c], cx = x >> 1;
-  if (g.vr[c] == 1) {  // h2v1: 3/4 nearer + 1/4 further; rounding 1 (even) / 2 (odd); edge columns copied
+  const int hr = g.hr[c], vr = g.vr[c];
+  if (hr == 1 && vr == 1) return pl[(long long)y * stride + x];
+  const int cw = g.comp_w[c];
+  if (hr == 1) {  // h1v2: 3/4 nearer row + 1/4 next nearest; bias 1 (upper) / 2 (lower); edge rows stand in for their neighbours
+    const int ch = g.comp_h[c], cy = y >> 1;
+    const int cyn = (y & 1) ? min(cy + 1, ch - 1) : max(cy - 1, 0);
+    return (3 * pl[(long long)cy * stride + x] + pl[(long long)cyn * stride + x] + ((y & 1) ? 2 : 1)) >> 2;
+  }
+  if (hr != 2 || cw <= 2) return pl[(long long)(vr == 2 ? y >> 1 : y) * stride + (hr == 4 ? x >> 2 : x >> 1)];
+  const int cx = x >> 1;
+  if (vr == 1) {  // h2v1: 3/4 nearer + 1/4 further; rounding 1 (even) / 2 (odd); edge columns copied
     const uint8_t* row = pl + (long long)y * stride;
     const int p = row[cx];
     if (x & 1) return cx == cw - 1 ? p : (3 * p + row[cx + 1] + 2) >> 2;

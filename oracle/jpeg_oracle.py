@@ -401,14 +401,28 @@ def component_plane(c: Component, q: np.ndarray) -> np.ndarray:
     return plane[:c.height, :c.width]
 
 
+def upsample_box(p: np.ndarray, hr: int, vr: int) -> np.ndarray:
+    """jdsample.c int_upsample / h2v1_upsample / h2v2_upsample: every sample replicated hr x vr times"""
+    return np.repeat(np.repeat(p, vr, axis=0), hr, axis=1)
+
+
+def upsample_h1v2(p: np.ndarray) -> np.ndarray:
+    """jdsample.c h1v2_fancy_upsample (libjpeg-turbo): 3/4 nearer row + 1/4 the next nearest, bias 1 (upper output row) /
+    2 (lower); the row above the first / below the last is that row itself"""
+    a = p.astype(np.int32)
+    above = np.concatenate([a[:1], a[:-1]], axis=0)
+    below = np.concatenate([a[1:], a[-1:]], axis=0)
+    out = np.empty((2 * a.shape[0], a.shape[1]), np.int32)
+    out[0::2] = (3 * a + above + 1) >> 2
+    out[1::2] = (3 * a + below + 2) >> 2
+    return out.astype(np.uint8)
+
+
 def upsample_h2v1(p: np.ndarray) -> np.ndarray:
     """jdsample.c h2v1_fancy_upsample: 3/4 nearer + 1/4 further, rounding alternates 1 / 2"""
     a = p.astype(np.int32)
     h, w = a.shape
     out = np.empty((h, 2 * w), np.int32)
-    if w == 1:
-        out[:, 0] = out[:, 1] = a[:, 0]
-        return out.astype(np.uint8)
     left = np.concatenate([a[:, :1], a[:, :-1]], axis=1)
     right = np.concatenate([a[:, 1:], a[:, -1:]], axis=1)
     out[:, 0::2] = (3 * a + left + 1) >> 2
@@ -428,10 +442,6 @@ def upsample_h2v2(p: np.ndarray) -> np.ndarray:
     out = np.empty((2 * h, 2 * w), np.int32)
     for v, other in ((0, above), (1, below)):
         colsum = 3 * a + other  # "thiscolsum"
-        if w == 1:
-            out[v::2, 0] = (colsum[:, 0] * 4 + 8) >> 4
-            out[v::2, 1] = (colsum[:, 0] * 4 + 7) >> 4
-            continue
         last = np.concatenate([colsum[:, :1], colsum[:, :-1]], axis=1)
         nxt = np.concatenate([colsum[:, 1:], colsum[:, -1:]], axis=1)
         even = (3 * colsum + last + 8) >> 4
@@ -464,14 +474,20 @@ def reconstruct(f: Frame) -> np.ndarray:
     for c in f.comps:
         p = component_plane(c, f.qt[c.tq])
         hr, vr = f.hmax // c.h, f.vmax // c.v
+        if f.hmax % c.h or f.vmax % c.v or hr not in (1, 2, 4) or vr not in (1, 2):
+            raise ValueError(f"sampling ratio {f.hmax}/{c.h} x {f.vmax}/{c.v} is not supported")
+        # the choice of jdsample.c jinit_upsampler: the triangle filters where libjpeg has them - and, for the two
+        # horizontal ones, only when the component is more than two samples wide - replication otherwise
         if (hr, vr) == (1, 1):
             pass
-        elif (hr, vr) == (2, 1):
+        elif (hr, vr) == (2, 1) and c.width > 2:
             p = upsample_h2v1(p)
-        elif (hr, vr) == (2, 2):
+        elif (hr, vr) == (1, 2):
+            p = upsample_h1v2(p)
+        elif (hr, vr) == (2, 2) and c.width > 2:
             p = upsample_h2v2(p)
         else:
-            raise ValueError(f"sampling ratio {hr}x{vr} is not supported")
+            p = upsample_box(p, hr, vr)
         planes.append(p[:f.height, :f.width])
     if len(planes) == 1:
         return np.repeat(planes[0][:, :, None], 3, axis=2)

@@ -71,6 +71,28 @@ def transcoded():
         print(name, len(data), "bytes", dec.shape)
 
 
+def other_samplings():
+    """chroma samplings Pillow does not write (4:4:0 - what a losslessly rotated 4:2:2 photo becomes -, 4:1:1, 4:1:0, the
+    two chroma components sampled differently) and components so narrow that libjpeg replicates instead of filtering:
+    synthetic coefficients (tests/jpeg_writer.py), expected pixels from Pillow"""
+    from PIL import Image as _I
+    from tests import jpeg_writer as jw
+    for name, samp, (h, w), script, ri in (
+            ("samp440_40x61", [(1, 2), (1, 1), (1, 1)], (40, 61), jw.BASELINE, 0),
+            ("samp440_prog_17x33", [(1, 2), (1, 1), (1, 1)], (17, 33), jw.SCRIPT_MOZ, 2),
+            ("samp411_40x61", [(4, 1), (1, 1), (1, 1)], (40, 61), jw.BASELINE, 3),
+            ("samp410_33x70", [(4, 2), (1, 1), (1, 1)], (33, 70), jw.BASELINE, 0),
+            ("sampmixed_24x40", [(2, 2), (2, 1), (1, 1)], (24, 40), jw.SEQUENTIAL, 0),
+            ("samp420_narrow_9x3", [(2, 2), (1, 1), (1, 1)], (9, 3), jw.BASELINE, 0),
+            ("samp422_narrow_5x4", [(2, 1), (1, 1), (1, 1)], (5, 4), jw.BASELINE, 0)):
+        data = jw.encode_frame(jw.synthetic_frame(w, h, samp, seed=len(name)), script, ri)
+        open(os.path.join(OUT, name + ".jpg"), "wb").write(data)
+        dec = np.asarray(_I.open(io.BytesIO(data)).convert("RGB"))
+        np.save(os.path.join(OUT, name + ".npy"), dec)
+        print(name, len(data), "bytes", dec.shape)
+
+
 if __name__ == "__main__":
     main()
     transcoded()
+    other_samplings()

@@ -173,15 +173,44 @@ SCRIPT_GRAY = [((0,), 0, 0, 0, 2), ((0,), 1, 20, 0, 1), ((0,), 21, 63, 0, 1), ((
 
 
 SEQUENTIAL = "sequential, one scan per component"   # a `script` value: SOF0 with non-interleaved scans (jpegtran -scans style)
+BASELINE = "sequential, one interleaved scan"       # a `script` value: the ordinary baseline layout
+
+
+def synthetic_frame(width: int, height: int, sampling, seed: int = 0, quality_scale: int = 4):
+    """a Frame of random (sparse, low-frequency) quantised coefficients with the given (h, v) sampling factors per component:
+    the files no encoder at hand writes (4:4:0, 4:1:1, ...); what they look like does not matter, Pillow decodes them too"""
+    rng = np.random.default_rng(seed)
+    comps = [jo.Component(ci + 1, h, v, 0 if ci == 0 else 1) for ci, (h, v) in enumerate(sampling)]
+    hmax, vmax = max(c.h for c in comps), max(c.v for c in comps)
+    mcus_x, mcus_y = -(-width // (8 * hmax)), -(-height // (8 * vmax))
+    for c in comps:
+        c.blocks_w, c.blocks_h = mcus_x * c.h, mcus_y * c.v
+        c.width, c.height = -(-width * c.h // hmax), -(-height * c.v // vmax)
+        coefs = np.zeros((c.blocks_h, c.blocks_w, 64), np.int16)
+        coefs[:, :, 0] = np.cumsum(rng.integers(-6, 7, (c.blocks_h, c.blocks_w)), axis=1) + rng.integers(-20, 20)
+        for k in range(1, 12):                           # a few low frequencies, most of them zero
+            mask = rng.random((c.blocks_h, c.blocks_w)) < 0.35
+            coefs[:, :, jo.ZIGZAG[k]] = np.where(mask, rng.integers(-9, 10, (c.blocks_h, c.blocks_w)), 0)
+        c.coefs = coefs
+    qt = {0: np.clip(np.arange(64, dtype=np.uint16) // 4 * quality_scale + 4, 1, 255).astype(np.uint16),
+          1: np.clip(np.arange(64, dtype=np.uint16) // 3 * quality_scale + 6, 1, 255).astype(np.uint16)}
+    return jo.Frame(width, height, comps, qt, 0, hmax, vmax, mcus_x, mcus_y)
+
 
 
 def transcode(jpeg: bytes, script, restart_interval: int = 0) -> bytes:
     """the same image (same quantised coefficients, tables, sampling) as a progressive file with this scan script, or
     (script = SEQUENTIAL) as a baseline file whose components come in scans of their own"""
-    f = jo.parse(jpeg)
-    sequential = script == SEQUENTIAL
-    if sequential:
+    return encode_frame(jo.parse(jpeg), script, restart_interval)
+
+
+def encode_frame(f, script, restart_interval: int = 0) -> bytes:
+    """a parsed (or synthetic) Frame as JPEG bytes: progressive with `script`, or SEQUENTIAL / BASELINE"""
+    sequential = script in (SEQUENTIAL, BASELINE)
+    if script == SEQUENTIAL:
         script = [((ci,), 0, 63, 0, 0) for ci in range(len(f.comps))]
+    elif script == BASELINE:
+        script = [(tuple(range(len(f.comps))), 0, 63, 0, 0)]
     out = bytearray(b"\xff\xd8")
     for tq in sorted({c.tq for c in f.comps}):
         q = f.qt[tq]

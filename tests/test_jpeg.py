@@ -106,6 +106,40 @@ def test_progressive_scan_scripts_of_other_encoders(src, script, restart):
         assert np.array_equal(rec[info.coef_off[c]:info.coef_off[c] + n].reshape(comp.blocks_h, comp.blocks_w, 64), comp.coefs)
 
 
+def test_other_chroma_samplings_and_narrow_components_match_live_pillow():
+    """4:4:0, 4:1:1, 4:1:0, differently sampled chroma components, baseline / progressive / one scan per component, and
+    sizes whose chroma is one or two samples wide (libjpeg replicates there instead of filtering): synthetic coefficients
+    from tests/jpeg_writer.py, expected pixels from Pillow; the library's host decoder must give the oracle's coefficients"""
+    Image = pytest.importorskip("PIL.Image")
+    from ai4e_b200 import ops
+    from tests import jpeg_writer as jw
+    samplings = {"440": [(1, 2), (1, 1), (1, 1)], "411": [(4, 1), (1, 1), (1, 1)], "410": [(4, 2), (1, 1), (1, 1)],
+                 "mixed": [(2, 2), (2, 1), (1, 1)], "mixed2": [(2, 2), (1, 2), (1, 1)], "420": [(2, 2), (1, 1), (1, 1)],
+                 "422": [(2, 1), (1, 1), (1, 1)]}
+    n = 0
+    for name, samp in samplings.items():
+        for h, w in ((1, 1), (3, 3), (5, 4), (17, 33), (24, 61)):
+            script = (jw.BASELINE, jw.SCRIPT_MOZ, jw.SEQUENTIAL)[n % 3]
+            data = jw.encode_frame(jw.synthetic_frame(w, h, samp, seed=n), script, restart_interval=(2 if n % 2 else 0))
+            n += 1
+            want = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+            assert np.array_equal(jo.decode(data), want), (name, h, w)
+            f = jo.parse(data)
+            info, rec = ops.jpeg_entropy_decode(data)
+            for c, comp in enumerate(f.comps):
+                m = comp.blocks_w * comp.blocks_h * 64
+                assert np.array_equal(rec[info.coef_off[c]:info.coef_off[c] + m].reshape(comp.blocks_h, comp.blocks_w, 64), comp.coefs)
+    # tiny images as Pillow itself writes them: every size from 1 x 1 to 6 x 6 in the three samplings it offers
+    rng = np.random.default_rng(2)
+    for sub in (0, 1, 2):
+        for h in range(1, 7):
+            for w in range(1, 7):
+                buf = io.BytesIO()
+                Image.fromarray(rng.integers(0, 256, (h, w, 3), dtype=np.uint8)).save(buf, format="JPEG", quality=90, subsampling=sub)
+                want = np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("RGB"))
+                assert np.array_equal(jo.decode(buf.getvalue()), want), (sub, h, w)
+
+
 def _cmyk_jpeg():
     PIL = pytest.importorskip("PIL.Image")
     buf = io.BytesIO()
