@@ -118,7 +118,8 @@ AI4E_API int ai4e_conv_layer(const void* d_in_nhwc, int batch, int h, int w, int
  * Split like a hybrid decoder: the entropy (Huffman) decode is sequential and runs on the
  * submitting thread's host core; dequantisation, IDCT, upsampling and colour conversion run on the
  * GPU.  8-bit baseline / extended sequential and progressive (SOF0, SOF1, SOF2) Huffman, 1 or 3
- * components, 4:4:4 / 4:2:2 / 4:2:0, restart intervals; a progressive file's scans accumulate into the
+ * components, 4:4:4 / 4:2:2 / 4:2:0 / 4:4:0 / 4:1:1 / 4:1:0 (chroma ratios 1, 2, 4 horizontally and 1, 2 vertically,
+ * each component its own), restart intervals; a progressive file's scans accumulate into the
  * same record on the host.  Anything else (arithmetic coding, lossless, CMYK, 12-bit)
  * -> AI4E_ERR_UNSUPPORTED.
  *
