@@ -140,6 +140,25 @@ def test_other_chroma_samplings_and_narrow_components_match_live_pillow():
                 assert np.array_equal(jo.decode(buf.getvalue()), want), (sub, h, w)
 
 
+def test_sixteen_bit_quantisation_tables():
+    """DQT with Pq = 1 (entries above 255), baseline and progressive: oracle == Pillow, the library's record carries the table"""
+    Image = pytest.importorskip("PIL.Image")
+    from ai4e_b200 import ops
+    from tests import jpeg_writer as jw
+    f = jw.synthetic_frame(33, 17, [(2, 2), (1, 1), (1, 1)], seed=5)
+    f.qt[0] = f.qt[0].copy()
+    f.qt[0][40:] = np.arange(300, 324, dtype=np.uint16)
+    for script in (jw.BASELINE, jw.SCRIPT_MOZ):
+        data = jw.encode_frame(f, script)
+        assert data[data.index(b"\xff\xdb") + 4] >> 4 == 1
+        want = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        assert np.array_equal(jo.decode(data), want)
+        info, rec = ops.jpeg_entropy_decode(data)
+        g = jo.parse(data)
+        for c, comp in enumerate(g.comps):
+            assert np.array_equal(rec[c * 64:(c + 1) * 64].astype(np.uint16), g.qt[comp.tq])
+
+
 def _cmyk_jpeg():
     PIL = pytest.importorskip("PIL.Image")
     buf = io.BytesIO()
